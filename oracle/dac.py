@@ -1,0 +1,59 @@
+"""DAC 44.1 kHz decoder on CPU, fp32 (test infrastructure; see oracle/__init__.py).
+
+Restates zonos/autoencoder.py:44-47 (DACAutoencoder.decode; fp32 on CPU) and the third-party arithmetic it
+calls -- transformers (pinned 4.48.3 in the reference's uv.lock:2063-2065; 5.5.0 installed here)
+models/dac/modeling_dac.py: DacResidualVectorQuantizer.from_codes (:345-369), DacDecoder.forward (:429-439),
+DacDecoderBlock.forward (:255-262), DacResidualUnit.forward (:187-207), Snake1d.forward (:94-99),
+DacModel.decode (:608-638).  Weights: plain dict with the HF key names.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+
+def snake(x, alpha):
+    """x + (alpha + 1e-9)^-1 * sin(alpha * x)^2, alpha [1,C,1]."""
+    return x + (alpha + 1e-9).reciprocal() * torch.sin(alpha * x).pow(2)
+
+
+def from_codes(W, codes):
+    """codes int64 [B,Q,T] -> z fp32 [B,latent,T] = sum_k (out_proj_k(codebook_k[codes_k]) ), k ascending."""
+    z = 0.0
+    for k in range(codes.shape[1]):
+        p = f"quantizer.quantizers.{k}."
+        lat = F.embedding(codes[:, k, :], W[p + "codebook.weight"]).transpose(1, 2)
+        z = z + F.conv1d(lat, W[p + "out_proj.weight"], W[p + "out_proj.bias"])
+    return z
+
+
+def _res_unit(W, p, x, dilation):
+    y = F.conv1d(snake(x, W[p + "snake1.alpha"]), W[p + "conv1.weight"], W[p + "conv1.bias"],
+                 dilation=dilation, padding=3 * dilation)
+    y = F.conv1d(snake(y, W[p + "snake2.alpha"]), W[p + "conv2.weight"], W[p + "conv2.bias"])
+    return x + y  # same length: the crop branch (modeling_dac.py:202-205) is never taken with pad = 3*dil
+
+
+def decoder(W, z, strides=(8, 8, 4, 2), taps=None):
+    """z [B,latent,T] -> [B,1,prod(strides)*T].  `taps` (dict) collects intermediate activations if given."""
+    x = F.conv1d(z, W["decoder.conv1.weight"], W["decoder.conv1.bias"], padding=3)
+    if taps is not None:
+        taps["conv1"] = x
+    for j, s in enumerate(strides):
+        p = f"decoder.block.{j}."
+        x = F.conv_transpose1d(snake(x, W[p + "snake1.alpha"]), W[p + "conv_t1.weight"], W[p + "conv_t1.bias"],
+                               stride=s, padding=math.ceil(s / 2))
+        if taps is not None:
+            taps[f"block{j}.convt"] = x
+        for r, dil in ((1, 1), (2, 3), (3, 9)):
+            x = _res_unit(W, p + f"res_unit{r}.", x, dil)
+        if taps is not None:
+            taps[f"block{j}"] = x
+    x = F.conv1d(snake(x, W["decoder.snake1.alpha"]), W["decoder.conv2.weight"], W["decoder.conv2.bias"], padding=3)
+    return torch.tanh(x)
+
+
+def decode(W, codes, strides=(8, 8, 4, 2), taps=None):
+    """codes int64 [B,9,T] -> fp32 [B,1,512*T]."""
+    assert codes.shape[1] == 9, f"Expected 9 codebooks, got {codes.shape[1]}"
+    return decoder(W, from_codes(W, codes), strides, taps).float()

@@ -1,0 +1,208 @@
+"""Generates tests/golden/*.pt by running the UNMODIFIED reference on CPU (test infrastructure).
+
+Run in the build container only (needs /root/reference):   python -m oracle.gen_golden
+The reference ships no golden vectors of its own, so these files are the parity pin for
+oracle/ and for the CUDA path.  Inputs are regenerated from seeds (oracle/shapes.py, oracle/scenarios.py); only
+outputs (and small inputs) are stored, plus a checksum of the synthetic weights to catch RNG drift.
+"""
+import os
+import sys
+
+import torch
+
+from . import scenarios as sc
+from . import shapes
+from .ref_import import import_reference
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def weights_checksum(W) -> float:
+    return float(sum(v.float().abs().sum().item() for v in W.values()))
+
+
+def build_reference_model(shape):
+    import zonos.config as zc
+    import zonos.model as zm
+    from zonos.backbone import BACKBONES
+
+    cfg = zc.ZonosConfig.from_dict(shapes.reference_config_dict(shape))
+    m = zm.Zonos(cfg, BACKBONES["torch"]).to("cpu", torch.bfloat16)
+    sd = m.state_dict()
+    sd.update(shapes.synth_transformer_weights(shape, seed=0, padded_heads=False))
+    m.load_state_dict(sd)  # post-hook pads heads 1025 -> 1026 (zonos/model.py:46-51)
+    return m.eval()
+
+
+def gen_delay():
+    import zonos.codebook_pattern as zcp
+
+    g = torch.Generator().manual_seed(3)
+    cases = []
+    for B, T in [(1, 1), (2, 5), (3, 9), (2, 40), (1, 300)]:
+        codes = torch.randint(-1, 1026, (B, 9, T), generator=g)
+        d = zcp.apply_delay_pattern(codes, 1025)
+        cases.append(dict(codes=codes, delayed=d, reverted=zcp.revert_delay_pattern(d)))
+    torch.save(cases, os.path.join(OUT, "delay.pt"))
+
+
+def gen_sampler():
+    import zonos.sampling as zs
+
+    logits, hist, rp, noise = sc.sampler_inputs()
+    out = dict(rep={}, tokens={}, filters={})
+    for w in (2, 8, 16):
+        out["rep"][w] = zs.modify_logit_for_repetition_penalty(logits.clone(), hist, rp.clone(), w)
+    probs = torch.softmax(out["rep"][2], dim=-1)
+    out["filters"]["softmax"] = probs
+    out["filters"]["unified"] = zs.apply_unified(probs.clone(), 0.55, 0.4, 0.1)
+    out["filters"]["top_p"] = zs.apply_top_p(probs.clone(), 0.9)
+    out["filters"]["top_k"] = zs.apply_top_k(probs.clone(), 50)
+    out["filters"]["min_p"] = zs.apply_min_p(probs.clone(), 0.1)
+    orig = torch.Tensor.exponential_
+
+    def patched(self, *a, **k):
+        self.copy_(noise)
+        return self
+
+    for name, kw in sc.SAMPLER_CASES.items():
+        torch.Tensor.exponential_ = patched
+        try:
+            out["tokens"][name] = zs.sample_from_logits(
+                logits.clone(), generated_tokens=hist, repetition_penalty=rp.clone(), repetition_penalty_window=2, **kw)
+        finally:
+            torch.Tensor.exponential_ = orig
+    torch.save(out, os.path.join(OUT, "sampler.pt"))
+
+
+def _with_noise_tape(tape, fn):
+    orig = torch.Tensor.exponential_
+
+    def patched(self, *a, **k):
+        self.copy_(tape(tuple(self.shape)))
+        return self
+
+    torch.Tensor.exponential_ = patched
+    try:
+        return fn()
+    finally:
+        torch.Tensor.exponential_ = orig
+
+
+def gen_eos(model):
+    out = {}
+    for name, s in sc.EOS_SCENARIOS.items():
+        script = sc.scripted_logits(s)
+        it = {"i": 0}
+
+        def fake_prefill(*a, **k):
+            it["i"] = 1
+            return script[0].clone()
+
+        def fake_step(*a, **k):
+            r = script[it["i"]].clone()
+            it["i"] += 1
+            return r
+
+        model._prefill, model._decode_one_token = fake_prefill, fake_step
+        frames = []
+
+        def cb(frame, step, max_steps):
+            frames.append(frame.clone())
+            return True
+
+        d = model.config.backbone.d_model
+        cond = torch.zeros(2 * s["B"], 4, d, dtype=torch.bfloat16)
+        res = _with_noise_tape(sc.NoiseTape(s["seed"]), lambda: model.generate(
+            cond, sc.scripted_prefix(s), max_new_tokens=s["max_new"], batch_size=s["B"],
+            sampling_params=dict(s["sampling"]), progress_bar=False, disable_torch_compile=True, callback=cb))
+        out[name] = dict(codes=res, frames=torch.cat(frames, dim=-1), steps_run=len(frames), script_used=it["i"])
+        del model._prefill, model._decode_one_token
+    torch.save(out, os.path.join(OUT, "eos_scenarios.pt"))
+
+
+MODEL_CASES = {
+    # name: (B, L_cond, P, max_new, sampling, cfg_scale)
+    "b1_greedy": (1, 23, 0, 24, sc.GREEDY, 2.0),
+    "b3_greedy_rp_prefix": (3, 17, 5, 24, sc.GREEDY_RP, 2.0),
+    "b2_minp": (2, 9, 9, 20, sc.MINP, 2.0),
+    "b2_unified_cfg3": (2, 12, 0, 20, sc.UNIFIED, 3.0),
+}
+
+
+def gen_model(model, shape):
+    """G2-G4 + G7: embed, prefill logits, teacher-forced decode logits, free-running generate."""
+    W = shapes.synth_transformer_weights(shape, seed=0)
+    d = shapes.SHAPES[shape]["d_model"]
+    out = dict(weights_checksum=weights_checksum(W), cases={})
+    g = torch.Generator().manual_seed(5)
+    ids = torch.randint(0, 1026, (2, 9, 6), generator=g)
+    out["embed"] = dict(ids=ids, out=model.embed_codes(ids))
+
+    for name, (B, Lc, P, N, sp, cfg) in MODEL_CASES.items():
+        cond = shapes.synth_conditioning(B, Lc, d, seed=1)
+        pre = None if P == 0 else torch.randint(0, 1024, (B, 9, P), generator=torch.Generator().manual_seed(2))
+        logit_log = []
+        orig_cl = model._compute_logits
+
+        def spy(hidden, params, scale):
+            r = orig_cl(hidden, params, scale)
+            logit_log.append(r.clone())
+            return r
+
+        model._compute_logits = spy
+        frames = []
+
+        def cb(frame, step, max_steps):
+            frames.append(frame.clone())
+            return True
+
+        res = _with_noise_tape(sc.NoiseTape(77), lambda: model.generate(
+            cond, pre, max_new_tokens=N, cfg_scale=cfg, batch_size=B, sampling_params=dict(sp),
+            progress_bar=False, disable_torch_compile=True, callback=cb))
+        del model._compute_logits
+        out["cases"][name] = dict(codes=res, frames=torch.cat(frames, dim=-1), logits=torch.stack(logit_log[:6]))
+    torch.save(out, os.path.join(OUT, f"model_{shape}.pt"))
+
+
+def gen_dac():
+    from transformers.models.dac import DacConfig, DacModel
+
+    out = {}
+    for arch_name, arch in (("tiny", shapes.DAC_TINY), ("real", shapes.DAC)):
+        cfg = DacConfig(sampling_rate=44100, hidden_size=arch["latent"], decoder_hidden_size=arch["dec_ch"])
+        m = DacModel(cfg).eval()
+        W = shapes.synth_dac_weights(seed=7, arch=arch)
+        sd = m.state_dict()
+        for k, v in W.items():
+            assert sd[k].shape == v.shape, (k, sd[k].shape, v.shape)
+        sd.update(W)
+        m.load_state_dict(sd)
+        g = torch.Generator().manual_seed(9)
+        cases = [(1, 1), (3, 7), (2, 86)] if arch_name == "tiny" else [(1, 1), (1, 40)]
+        res = []
+        for B, T in cases:
+            codes = torch.randint(0, 1024, (B, 9, T), generator=g)
+            with torch.no_grad():
+                wav = m.decode(audio_codes=codes).audio_values.unsqueeze(1).float()
+            res.append(dict(codes=codes, wav=wav))
+        out[arch_name] = dict(cases=res, weights_checksum=weights_checksum(W))
+    torch.save(out, os.path.join(OUT, "dac.pt"))
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    import_reference()
+    torch.set_grad_enabled(False)
+    gen_delay()
+    gen_sampler()
+    model = build_reference_model("tiny")
+    gen_eos(model)
+    gen_model(model, "tiny")
+    gen_dac()
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,113 @@
+"""Pins oracle/ (the CPU restatement) to golden vectors produced by the unmodified reference
+(oracle/gen_golden.py).  CPU only."""
+import pytest
+import torch
+
+from oracle import dac as odac
+from oracle import delay as odelay
+from oracle import generate as ogen
+from oracle import sampling as osmp
+from oracle import scenarios as sc
+from oracle import shapes
+from oracle.gen_golden import MODEL_CASES, weights_checksum
+
+
+def test_delay_pattern_bit_exact(golden):
+    for case in golden("delay.pt"):
+        d = odelay.apply_delay_pattern(case["codes"], 1025)
+        assert torch.equal(d, case["delayed"])
+        assert torch.equal(odelay.revert_delay_pattern(d), case["reverted"])
+
+
+def test_repetition_penalty_and_filters(golden):
+    g = golden("sampler.pt")
+    logits, hist, rp, noise = sc.sampler_inputs()
+    for w, ref in g["rep"].items():
+        assert torch.equal(osmp.repetition_penalty(logits.clone(), hist, rp, w), ref)
+    probs = g["filters"]["softmax"]
+    assert torch.equal(osmp.unified(probs.clone(), 0.55, 0.4, 0.1), g["filters"]["unified"])
+    assert torch.equal(osmp.top_p_filter(probs.clone(), 0.9), g["filters"]["top_p"])
+    assert torch.equal(osmp.top_k_filter(probs.clone(), 50), g["filters"]["top_k"])
+    assert torch.equal(osmp.min_p_filter(probs.clone(), 0.1), g["filters"]["min_p"])
+
+
+@pytest.mark.parametrize("name", list(sc.SAMPLER_CASES))
+def test_sample_tokens(golden, name):
+    g = golden("sampler.pt")
+    logits, hist, rp, noise = sc.sampler_inputs()
+    tok = osmp.sample(logits.clone(), history=hist, rp=rp, rp_window=2, noise=noise, **sc.SAMPLER_CASES[name])
+    assert torch.equal(tok, g["tokens"][name])
+
+
+@pytest.mark.parametrize("name", list(sc.EOS_SCENARIOS))
+def test_eos_state_machine(golden, name):
+    g = golden("eos_scenarios.pt")[name]
+    s = sc.EOS_SCENARIOS[name]
+    frames = []
+    res = ogen.generate(ogen.ScriptedLogits(sc.scripted_logits(s)), s["B"], 4, sc.scripted_prefix(s), s["max_new"],
+                        dict(s["sampling"]), noise_fn=sc.NoiseTape(s["seed"]),
+                        callback=lambda f, st, m: frames.append(f.clone()) or True)
+    assert len(frames) == g["steps_run"]
+    assert torch.equal(torch.cat(frames, -1), g["frames"])
+    assert len(res) == len(g["codes"])
+    for a, b in zip(res, g["codes"]):
+        assert torch.equal(a, b)
+
+
+def test_eos_scenarios_cover_the_policy(golden):
+    """The fixtures must actually exercise: early exit, ragged lengths, and full-length rows."""
+    g = golden("eos_scenarios.pt")
+    s = sc.EOS_SCENARIOS["all_stop_greedy_rp"]
+    assert g["all_stop_greedy_rp"]["steps_run"] < s["max_new"] + 9 - 1
+    lens = [c.shape[1] for c in g["mixed_greedy"]["codes"]]
+    assert len(set(lens)) == 3 and max(lens) == 40
+
+
+@pytest.mark.parametrize("name", list(MODEL_CASES))
+def test_generate_tiny_model(golden, name):
+    g = golden("model_tiny.pt")
+    W = shapes.synth_transformer_weights("tiny", seed=0)
+    assert weights_checksum(W) == pytest.approx(g["weights_checksum"], rel=1e-9)
+    B, Lc, P, N, sp, cfg = MODEL_CASES[name]
+    cond = shapes.synth_conditioning(B, Lc, shapes.SHAPES["tiny"]["d_model"], seed=1)
+    pre = None if P == 0 else torch.randint(0, 1024, (B, 9, P), generator=torch.Generator().manual_seed(2))
+    res = ogen.generate_with_model(W, "tiny", cond, pre, N, cfg, dict(sp), noise_fn=sc.NoiseTape(77))
+    for a, b in zip(res, g["cases"][name]["codes"]):
+        assert torch.equal(a, b)
+
+
+def test_embed_and_logits_tiny(golden):
+    from oracle import backbone as ob
+
+    g = golden("model_tiny.pt")
+    W = shapes.synth_transformer_weights("tiny", seed=0)
+    assert torch.equal(ob.embed_codes(W, g["embed"]["ids"]), g["embed"]["out"])
+    # teacher-forced logits: prefill + 5 decode steps of case b3_greedy_rp_prefix, fed with the golden frames
+    B, Lc, P, N, sp, cfg = MODEL_CASES["b3_greedy_rp_prefix"]
+    case = g["cases"]["b3_greedy_rp_prefix"]
+    cond = shapes.synth_conditioning(B, Lc, 512, seed=1)
+    pre = torch.randint(0, 1024, (B, 9, P), generator=torch.Generator().manual_seed(2))
+    codes = torch.full((B, 9, P + N), -1, dtype=torch.int64)
+    codes[..., :P] = pre
+    delayed = odelay.apply_delay_pattern(codes, 1025)
+    src = ogen.ModelLogits(W, "tiny", cond, Lc + P + N + 9, cfg)
+    assert torch.equal(src.prefill(delayed[..., :P + 1]), case["logits"][0])
+    # frames[.., s] is the frame written at loop step s+1 (offset P+2+s); step s+1 consumes the frame at P+1+s
+    first = torch.where(delayed[..., P + 1:P + 2] == -1, case["logits"][0].argmax(-1, keepdim=True),
+                        delayed[..., P + 1:P + 2])
+    ids = first
+    for s in range(1, 6):
+        assert torch.equal(src.step(ids), case["logits"][s])
+        ids = case["frames"][..., s - 1:s]
+
+
+def test_dac_decode(golden):
+    g = golden("dac.pt")
+    for arch_name, arch in (("tiny", shapes.DAC_TINY), ("real", shapes.DAC)):
+        W = shapes.synth_dac_weights(seed=7, arch=arch)
+        assert weights_checksum(W) == pytest.approx(g[arch_name]["weights_checksum"], rel=1e-9)
+        for case in g[arch_name]["cases"]:
+            wav = odac.decode(W, case["codes"])
+            assert wav.shape == case["wav"].shape == (case["codes"].shape[0], 1, 512 * case["codes"].shape[2])
+            assert float((wav - case["wav"]).abs().max()) < 2e-5  # fp32 conv summation order varies with threading
+            assert 0.05 < float(case["wav"].std()) < 0.9  # the fixture is not degenerate / saturated
