@@ -1,0 +1,63 @@
+/* zonos_b200 -- C ABI of the B200-native Zonos hot path (libzonos_b200.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.  Every device buffer is owned by the
+ * caller (the Python shim allocates torch tensors and passes data_ptr()); the library owns only opaque session
+ * handles.  Every entry point takes the CUDA stream (cudaStream_t as void*) it must run on, never synchronises
+ * unless documented, and returns 0 (ZB200_OK) or a negative status with a message in zb200_last_error().
+ *
+ * Each entry point names the reference (coezbek/Zonos) interface it replaces.
+ */
+#ifndef ZONOS_B200_H
+#define ZONOS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZB200_OK 0
+#define ZB200_ERR_INVALID (-1) /* bad argument / shape -> ValueError in the shim  */
+#define ZB200_ERR_CUDA (-2)    /* CUDA runtime error   -> RuntimeError            */
+#define ZB200_ERR_STATE (-3)   /* call order / overflow -> AssertionError (e.g. KV overflow, _torch.py:44-45) */
+
+#define ZB200_ABI_VERSION 1
+#define ZB200_PAGE 64        /* KV positions per page */
+#define ZB200_HEAD_DIM 128   /* head dim of every Zonos-v0.1 attention layer */
+#define ZB200_MAX_CODEBOOKS 9
+
+int zb200_version(void);
+const char* zb200_last_error(void);
+
+/* ---- zonos/codebook_pattern.py:5-7 apply_delay_pattern, :10-12 revert_delay_pattern (int64, bit-exact) ---- */
+int zb200_delay_apply(const int64_t* codes, int64_t* delayed, int batch, int n_q, int t, int64_t mask_token, void* stream);
+int zb200_delay_revert(const int64_t* delayed, int64_t* codes, int batch, int n_q, int t_delayed, void* stream);
+
+/* ---- weight repack (done once in Zonos.from_local, zonos/model.py:65-88) ----------------------------------
+ * src: row-major [n_rows, k] 16-bit.  dst: [n_tiles][k/64][tile_n*128 B] shared-memory images (SWIZZLE_128B).
+ * row_mode 0: tile row r of tile j <- src row j*tile_n + r (zero beyond n_rows)
+ * row_mode 1: gated-MLP pairing (fc1, _torch.py:151-152): first tile_n/2 rows <- value rows j*tile_n/2 + r,
+ *             last tile_n/2 rows <- gate rows n_rows/2 + j*tile_n/2 + r
+ * row_mode 2: per-head padding (heads, model.py:100-101): src is [n_heads_out][rows_per_head][k], every head is
+ *             padded to rows_per_head_padded rows (multiple of tile_n) with zeros. */
+int zb200_pack_weight(const void* src, void* dst, int n_rows, int k, int tile_n, int row_mode, int rows_per_head,
+                      int rows_per_head_padded, void* stream);
+int64_t zb200_packed_weight_bytes(int n_rows, int k, int tile_n, int row_mode, int rows_per_head, int rows_per_head_padded);
+
+/* ---- unit-test hooks for single kernels ------------------------------------------------------------------- */
+/* out[m, n] = bf16( sum_k a[m,k] * w[n,k] ), packed weights with tile_n = 64. splits >= 1 (split-K). ws/tickets
+ * may be NULL when splits == 1. */
+int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int splits,
+                    float* ws, int* tickets, void* stream);
+/* nn.LayerNorm(d, eps) with affine weight+bias on bf16 rows, fp32 statistics (_torch.py:62,88,90). */
+int zb200_layernorm(const void* x, const void* w, const void* b, void* out, int rows, int d, float eps, void* stream);
+/* Zonos.embed_codes (model.py:97-98): sum over codebooks in order, each add rounded to bf16.
+ * ids int32, element (b, q, s) at ids[b*ids_stride_b + q*ids_stride_q + s], s in [0, n_cols); emb bf16 [n_q][vocab][d];
+ * out row (b*out_stride_b + out_off + s), written again dup_rows_offset rows further when dup_rows_offset > 0. */
+int zb200_embed_sum(const int32_t* ids, int ids_stride_b, int ids_stride_q, int n_cols, const void* emb, void* out,
+                    int batch, int n_q, int vocab, int d, int out_stride_b, int out_off, int dup_rows_offset, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZONOS_B200_H */

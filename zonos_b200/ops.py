@@ -1,0 +1,90 @@
+"""Thin torch-tensor wrappers over the single-kernel entry points of the C ABI (include/zonos_b200.h).
+
+Used by the public API in zonos_b200/ (delay pattern, weight repack) and by the parity tests.  Nothing here computes
+on the host: every function launches CUDA kernels of libzonos_b200.so on the current torch stream.
+"""
+import ctypes
+
+import torch
+
+from ._lib import check, lib, ptr, stream_ptr
+
+TILE_N = 64
+HEAD_ROWS_PADDED = 1088  # 1026 logits per head padded to 17 tiles of 64
+
+
+def _cuda(t: torch.Tensor, dtype=None) -> torch.Tensor:
+    if not t.is_cuda:
+        raise ValueError("zonos_b200 kernels need CUDA tensors (there is no CPU fallback)")
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+def apply_delay_pattern(codes: torch.Tensor, mask_token: int) -> torch.Tensor:
+    """zonos/codebook_pattern.py:5-7.  int64 [B,Q,T] -> [B,Q,T+Q]."""
+    codes = _cuda(codes, torch.int64)
+    B, Q, T = codes.shape
+    out = torch.empty(B, Q, T + Q, dtype=torch.int64, device=codes.device)
+    check(lib().zb200_delay_apply(ptr(codes), ptr(out), B, Q, T, ctypes.c_int64(mask_token), stream_ptr()), "delay_apply")
+    return out
+
+
+def revert_delay_pattern(delayed: torch.Tensor) -> torch.Tensor:
+    """zonos/codebook_pattern.py:10-12.  int64 [B,Q,Tp] -> [B,Q,Tp-Q]."""
+    delayed = _cuda(delayed, torch.int64)
+    B, Q, Tp = delayed.shape
+    out = torch.empty(B, Q, Tp - Q, dtype=torch.int64, device=delayed.device)
+    check(lib().zb200_delay_revert(ptr(delayed), ptr(out), B, Q, Tp, stream_ptr()), "delay_revert")
+    return out
+
+
+def pack_weight(w: torch.Tensor, row_mode: int = 0, tile_n: int = TILE_N, rows_per_head: int = 0,
+                rows_per_head_padded: int = 0) -> torch.Tensor:
+    """Repack a 16-bit [N, K] (or [heads, rows, K] for row_mode 2) weight into per-stage shared-memory images."""
+    w = _cuda(w)
+    assert w.dtype in (torch.bfloat16, torch.float16)
+    K = w.shape[-1]
+    n_rows = w.numel() // K
+    nbytes = lib().zb200_packed_weight_bytes(n_rows, K, tile_n, row_mode, rows_per_head, rows_per_head_padded)
+    if nbytes <= 0:
+        raise ValueError(f"cannot pack weight of shape {tuple(w.shape)} (K must be a multiple of 64)")
+    out = torch.empty(nbytes // 2, dtype=w.dtype, device=w.device)
+    check(lib().zb200_pack_weight(ptr(w), ptr(out), n_rows, K, tile_n, row_mode, rows_per_head, rows_per_head_padded,
+                                  stream_ptr()), "pack_weight")
+    return out
+
+
+def gemm_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, splits: int = 1) -> torch.Tensor:
+    """Test hook: bf16 [M,K] x packed [N,K]^T -> bf16 [M,N] through the tcgen05 kernel."""
+    a = _cuda(a, torch.bfloat16)
+    M, K = a.shape
+    out = torch.empty(M, n, dtype=torch.bfloat16, device=a.device)
+    ws = tickets = None
+    if splits > 1:
+        tiles = ((n + 63) // 64) * ((M + 127) // 128)
+        ws = torch.empty(tiles * splits * 64 * 128, dtype=torch.float32, device=a.device)
+        tickets = torch.zeros(tiles, dtype=torch.int32, device=a.device)
+    check(lib().zb200_gemm_bf16(ptr(a), M, K, ptr(w_packed), n, K, ptr(out), n, splits, ptr(ws), ptr(tickets),
+                                stream_ptr()), "gemm_bf16")
+    return out
+
+
+def layernorm(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
+    x = _cuda(x, torch.bfloat16)
+    d = x.shape[-1]
+    out = torch.empty_like(x)
+    check(lib().zb200_layernorm(ptr(x), ptr(_cuda(w, torch.bfloat16)), ptr(_cuda(b, torch.bfloat16)), ptr(out),
+                                x.numel() // d, d, ctypes.c_float(eps), stream_ptr()), "layernorm")
+    return out
+
+
+def embed_codes(ids: torch.Tensor, emb: torch.Tensor) -> torch.Tensor:
+    """Zonos.embed_codes (zonos/model.py:97-98): ids [B,Q,S] -> bf16 [B,S,d]; emb bf16 [Q,V,d]."""
+    ids = _cuda(ids, torch.int32)
+    B, Q, S = ids.shape
+    _, V, d = emb.shape
+    out = torch.empty(B, S, d, dtype=torch.bfloat16, device=ids.device)
+    check(lib().zb200_embed_sum(ptr(ids), Q * S, S, S, ptr(_cuda(emb)), ptr(out), B, Q, V, d, S, 0, 0, stream_ptr()),
+          "embed_sum")
+    return out
