@@ -57,6 +57,22 @@ int zb200_layernorm(const void* x, const void* w, const void* b, void* out, int 
 int zb200_embed_sum(const int32_t* ids, int ids_stride_b, int ids_stride_q, int n_cols, const void* emb, void* out,
                     int batch, int n_q, int vocab, int d, int out_stride_b, int out_off, int dup_rows_offset, void* stream);
 
+/* Paged KV pool layout: [layer][page][kv][n_kv_heads][64 positions][128] bf16 (see csrc/kv.cuh).  Test hook that
+ * scatters k, v bf16 [n_seq, seq_len, n_kv_heads, 128] to positions pos0.. (the product path writes the cache from
+ * the in_proj epilogue; replaces _update_kv_cache, zonos/backbone/_torch.py:33-49). */
+int zb200_kv_write(const void* k, const void* v, void* pool, const int* block_table, int pages_per_seq, int num_pages,
+                   int n_kv_heads, int layer, int n_seq, int seq_len, int pos0, void* stream);
+/* Decode attention, one query per sequence over n_keys cached positions (non-causal over the visible keys,
+ * scale 1/sqrt(128), GQA): F.scaled_dot_product_attention at _torch.py:136 with S == 1.  q/out bf16 [n_seq, H*128].
+ * ws: n_seq*n_kv_heads*nsplit*520 floats, tickets: n_seq*n_kv_heads zeroed ints (both only for nsplit > 1). */
+int zb200_attn_decode(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,
+                      int n_heads, int n_kv_heads, int layer, int n_seq, int n_keys, int nsplit, float* ws, int* tickets,
+                      void* out, void* stream);
+/* Causal prefill attention (_torch.py:136 with S > 1): query s of a sequence sees keys 0..pos0+s.
+ * q/out bf16 [n_seq, seq_len, H*128]. */
+int zb200_attn_prefill(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,
+                       int n_heads, int n_kv_heads, int layer, int n_seq, int seq_len, int pos0, void* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

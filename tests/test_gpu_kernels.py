@@ -66,3 +66,49 @@ def test_embed_codes_bit_exact(ops, golden):
     emb = torch.stack([W[f"embeddings.{k}.weight"] for k in range(9)]).cuda()
     out = ops.embed_codes(g["embed"]["ids"].cuda(), emb)
     assert torch.equal(out.cpu(), g["embed"]["out"])
+
+
+def _ref_attention(q, k, v, causal_from=None):
+    """fp32 reference: q [n,Sq,H,128], k/v [n,T,Hkv,128] -> [n,Sq,H,128]; causal_from = position of q[0]."""
+    n, Sq, H, D = q.shape
+    Hkv = k.shape[2]
+    kk = k.float().repeat_interleave(H // Hkv, dim=2)
+    vv = v.float().repeat_interleave(H // Hkv, dim=2)
+    s = torch.einsum("nqhd,nkhd->nhqk", q.float(), kk) / D ** 0.5
+    if causal_from is not None:
+        T = k.shape[1]
+        mask = torch.arange(T, device=q.device)[None, :] > (causal_from + torch.arange(Sq, device=q.device))[:, None]
+        s = s.masked_fill(mask, float("-inf"))
+    return torch.einsum("nhqk,nkhd->nqhd", s.softmax(-1), vv)
+
+
+@pytest.mark.parametrize("n_seq,H,Hkv,n_keys,nsplit", [(2, 16, 4, 1, 1), (2, 16, 4, 63, 1), (2, 16, 4, 64, 2), (3, 4, 2, 65, 1),
+                                                        (2, 16, 4, 700, 1), (2, 16, 4, 700, 5), (8, 16, 4, 2729, 3),
+                                                        (2, 16, 4, 130, 8)])
+def test_attn_decode_paged(ops, n_seq, H, Hkv, n_keys, nsplit):
+    g = torch.Generator(device="cuda").manual_seed(n_keys)
+    q = torch.randn(n_seq, 1, H, 128, device="cuda", generator=g).bfloat16()
+    k = torch.randn(n_seq, n_keys, Hkv, 128, device="cuda", generator=g).bfloat16()
+    v = torch.randn(n_seq, n_keys, Hkv, 128, device="cuda", generator=g).bfloat16()
+    kv = ops.PagedKV(2, n_seq, n_keys + 7, Hkv, "cuda", shuffle_seed=n_keys)
+    ops.kv_write(kv, 1, k, v, 0)
+    out = ops.attn_decode(q.view(n_seq, H * 128), kv, 1, n_keys, H, nsplit).view(n_seq, 1, H, 128)
+    ref = _ref_attention(q, k, v)
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2, err
+    out2 = ops.attn_decode(q.view(n_seq, H * 128), kv, 1, n_keys, H, nsplit).view(n_seq, 1, H, 128)
+    assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("n_seq,H,Hkv,S,pos0", [(2, 16, 4, 24, 0), (3, 4, 2, 70, 0), (2, 16, 4, 5, 130)])
+def test_attn_prefill_causal(ops, n_seq, H, Hkv, S, pos0):
+    g = torch.Generator(device="cuda").manual_seed(S)
+    T = pos0 + S
+    q = torch.randn(n_seq, S, H, 128, device="cuda", generator=g).bfloat16()
+    k = torch.randn(n_seq, T, Hkv, 128, device="cuda", generator=g).bfloat16()
+    v = torch.randn(n_seq, T, Hkv, 128, device="cuda", generator=g).bfloat16()
+    kv = ops.PagedKV(1, n_seq, T, Hkv, "cuda", shuffle_seed=3)
+    ops.kv_write(kv, 0, k, v, 0)
+    out = ops.attn_prefill(q.view(n_seq, S, H * 128), kv, 0, pos0, H).view(n_seq, S, H, 128)
+    ref = _ref_attention(q, k, v, causal_from=pos0)
+    assert (out.float() - ref).abs().max().item() < 2e-2

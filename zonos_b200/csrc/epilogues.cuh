@@ -5,6 +5,7 @@
 #pragma once
 #include "common.cuh"
 #include "gemm_tc.cuh"
+#include "kv.cuh"
 
 namespace zb {
 
@@ -93,20 +94,6 @@ struct EpiSwiGLU {
       v.z = pack_bf16x2(r[c + 4], r[c + 5]), v.w = pack_bf16x2(r[c + 6], r[c + 7]);
       *reinterpret_cast<uint4*>(o + c) = v;
     }
-  }
-};
-
-// Paged KV pool: [layer][page][kv(2)][n_kv_heads][ZB200_PAGE positions][128 dims] bf16; inside a position row the
-// sixteen 16-byte chunks are XOR-swizzled with (pos & 7) so that a page lands in shared memory (1-D TMA bulk copy)
-// already bank-conflict-free for ldmatrix.
-struct KvLayout {
-  bf16* pool;
-  const int* block_table;  // [n_seq][pages_per_seq]
-  int pages_per_seq, num_pages, n_kv_heads, layer;
-  __device__ __forceinline__ bf16* row(int seq, int pos, int kv, int head) const {
-    const int page = block_table[seq * pages_per_seq + (pos >> 6)];
-    const size_t idx = ((((size_t)layer * num_pages + page) * 2 + kv) * n_kv_heads + head) * 64 + (pos & 63);
-    return pool + idx * 128;
   }
 };
 

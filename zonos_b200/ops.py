@@ -88,3 +88,59 @@ def embed_codes(ids: torch.Tensor, emb: torch.Tensor) -> torch.Tensor:
     check(lib().zb200_embed_sum(ptr(ids), Q * S, S, S, ptr(_cuda(emb)), ptr(out), B, Q, V, d, S, 0, 0, stream_ptr()),
           "embed_sum")
     return out
+
+
+class PagedKV:
+    """Paged KV pool + block table (replaces InferenceParams.key_value_memory_dict, zonos/config.py:8-25).
+
+    pool bf16 [n_layer, num_pages, 2, n_kv_heads, 64, 128]; block_table int32 [n_seq, pages_per_seq].  Pages are handed
+    out from a free list so that a sequence's pages are in general NOT contiguous.
+    """
+
+    PAGE = 64
+
+    def __init__(self, n_layer, n_seq, max_seq, n_kv_heads, device, shuffle_seed=None):
+        self.n_layer, self.n_seq, self.n_kv_heads = n_layer, n_seq, n_kv_heads
+        self.pages_per_seq = (max_seq + self.PAGE - 1) // self.PAGE
+        self.num_pages = n_seq * self.pages_per_seq
+        self.max_seq = self.pages_per_seq * self.PAGE
+        # zero-filled: masked-out tail positions of a page are multiplied by P == 0 and must be finite
+        self.pool = torch.zeros(n_layer, self.num_pages, 2, n_kv_heads, self.PAGE, 128, dtype=torch.bfloat16, device=device)
+        if shuffle_seed is None:
+            # interleave sequences so consecutive pages of one sequence are far apart (a realistic allocation order)
+            ids = torch.arange(self.num_pages, dtype=torch.int32).view(self.pages_per_seq, n_seq).t().contiguous()
+        else:
+            g = torch.Generator().manual_seed(shuffle_seed)
+            ids = torch.randperm(self.num_pages, generator=g).to(torch.int32).view(n_seq, self.pages_per_seq)
+        self.block_table = ids.to(device)
+
+
+def kv_write(kv: PagedKV, layer: int, k: torch.Tensor, v: torch.Tensor, pos0: int):
+    """Test hook: scatter k, v bf16 [n_seq, S, n_kv, 128] into the pool at positions pos0.."""
+    k, v = _cuda(k, torch.bfloat16), _cuda(v, torch.bfloat16)
+    n_seq, S = k.shape[:2]
+    check(lib().zb200_kv_write(ptr(k), ptr(v), ptr(kv.pool), ptr(kv.block_table), kv.pages_per_seq, kv.num_pages,
+                               kv.n_kv_heads, layer, n_seq, S, pos0, stream_ptr()), "kv_write")
+
+
+def attn_decode(q: torch.Tensor, kv: PagedKV, layer: int, n_keys: int, n_heads: int, nsplit: int = 1) -> torch.Tensor:
+    q = _cuda(q, torch.bfloat16)
+    n_seq = q.shape[0]
+    out = torch.empty_like(q)
+    ws = tickets = None
+    if nsplit > 1:
+        ws = torch.empty(n_seq * kv.n_kv_heads * nsplit * 520, dtype=torch.float32, device=q.device)
+        tickets = torch.zeros(n_seq * kv.n_kv_heads, dtype=torch.int32, device=q.device)
+    check(lib().zb200_attn_decode(ptr(q), ptr(kv.pool), ptr(kv.block_table), kv.pages_per_seq, kv.num_pages, n_heads,
+                                  kv.n_kv_heads, layer, n_seq, n_keys, nsplit, ptr(ws), ptr(tickets), ptr(out),
+                                  stream_ptr()), "attn_decode")
+    return out
+
+
+def attn_prefill(q: torch.Tensor, kv: PagedKV, layer: int, pos0: int, n_heads: int) -> torch.Tensor:
+    q = _cuda(q, torch.bfloat16)
+    n_seq, S = q.shape[:2]
+    out = torch.empty_like(q)
+    check(lib().zb200_attn_prefill(ptr(q), ptr(kv.pool), ptr(kv.block_table), kv.pages_per_seq, kv.num_pages, n_heads,
+                                   kv.n_kv_heads, layer, n_seq, S, pos0, ptr(out), stream_ptr()), "attn_prefill")
+    return out
