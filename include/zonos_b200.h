@@ -73,6 +73,33 @@ int zb200_attn_decode(const void* q, const void* pool, const int* block_table, i
 int zb200_attn_prefill(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,
                        int n_heads, int n_kv_heads, int layer, int n_seq, int seq_len, int pos0, void* out, void* stream);
 
+/* ---- zonos/sampling.py:232-328 sample_from_logits + the per-step bookkeeping of zonos/model.py:345-424 -------------
+ * A decode step calls pass 1 then pass 2 (pass 2 re-draws every row only if some utterance produced its first EOS in
+ * pass 1, model.py:380-393; otherwise it only runs the bookkeeping).  All state lives on the device:
+ * state[]: int32[16] {0 offset (column written this step), 1 pos, 2 done, 3 final_offset, 4 draws, 5 any_fresh,
+ * 6 steps, 7/8 tickets}.  loop_mode 0 = first frame after the prefill (model.py:304-314). */
+typedef struct {
+  const float* logits;   /* [batch, n_q, vocab] fp32, CFG-mixed, pad slot -inf (model.py:111-115) */
+  const float* noise;    /* optional injected Exp(1) noise [n_draws][batch, n_q, vocab]; NULL -> Philox4x32-10 */
+  int32_t* delayed;      /* [batch, n_q, t_delayed] delayed codes, -1 = unknown */
+  int32_t* tok1;         /* [batch, n_q] */
+  int32_t* tok2;         /* [batch, n_q] */
+  int32_t* state;        /* [16] */
+  int32_t* remaining;    /* [batch] remaining_steps */
+  int32_t* grace;        /* [batch] steps_after_eos */
+  uint8_t* stopping;     /* [batch] */
+  uint8_t* eos_mode;     /* [batch] */
+  uint8_t* mask2;        /* [batch] scratch */
+  uint8_t* eos_old;      /* [batch] scratch */
+  int32_t* host_flags;   /* optional pinned host int32[2] {done, steps} */
+  int32_t batch, n_q, vocab, t_delayed;
+  int32_t loop_mode, first_offset, row_base;
+  uint64_t seed;
+  float temperature, top_p, min_p, linear, conf, quad, rep_penalty;
+  int32_t top_k, rep_window;
+} zb200_sampler_args;
+int zb200_sample(const zb200_sampler_args* args, int pass, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
