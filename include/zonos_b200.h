@@ -100,6 +100,48 @@ typedef struct {
 } zb200_sampler_args;
 int zb200_sample(const zb200_sampler_args* args, int pass, void* stream);
 
+/* ---- engine: the transformer backbone + heads behind Zonos._prefill / _decode_one_token / generate ------------------
+ * Replaces TorchZonosBackbone.forward (zonos/backbone/_torch.py:73-80), Zonos.embed_codes/apply_heads/_compute_logits
+ * (zonos/model.py:97-116), _decode_one_token (:118-179, incl. the CUDA-graph replay) and _prefill (:181-202).
+ * All buffers are caller-owned device memory; the handle stores the description and a captured CUDA graph. */
+typedef struct {
+  int32_t d_model, n_layer, n_heads, n_kv_heads, d_ff, n_q, vocab, head_rows_padded;
+  float ln_eps, cfg_scale;
+  int32_t batch;                 /* utterances B; the backbone runs 2B rows (cond | uncond) */
+  int32_t rows_max;              /* capacity (rows) of x/xn/q/att/h */
+  int32_t pages_per_seq, num_pages, t_delayed, attn_nsplit;
+  const void* emb;               /* bf16 [n_q][vocab][d_model] */
+  const void *ln1_w, *ln1_b, *ln2_w, *ln2_b; /* bf16 [n_layer][d_model] */
+  const void *lnf_w, *lnf_b;     /* bf16 [d_model] */
+  const void *w_qkv, *w_out, *w_fc1, *w_fc2; /* packed (zb200_pack_weight, tile 64; fc1 row_mode 1), layers contiguous */
+  int64_t qkv_stride, out_stride, fc1_stride, fc2_stride; /* bytes between layers */
+  const void* w_heads;           /* packed row_mode 2, rows_per_head_padded = head_rows_padded */
+  const float* rope;             /* fp32 [n_pos][64][2] (cos, sin), precompute_freqs_cis (_torch.py:9-15) */
+  void* kv_pool;                 /* bf16 [n_layer][num_pages][2][n_kv_heads][64][128] */
+  const int32_t* block_table;    /* [2B][pages_per_seq] */
+  void *x, *xn, *q, *att, *h;    /* bf16 [rows_max][d_model | d_model | H*128 | H*128 | d_ff] */
+  float* logits;                 /* fp32 [B][n_q][vocab] */
+  float* gemm_ws; int64_t gemm_ws_floats; int32_t* gemm_tickets; int32_t n_gemm_tickets;
+  float* attn_ws; int32_t* attn_tickets;
+  int32_t* state;                /* int32[16], see zb200_sampler_args */
+  int32_t* delayed;              /* int32 [B][n_q][t_delayed] */
+} zb200_engine_desc;
+typedef struct zb200_engine zb200_engine;
+int zb200_engine_create(const zb200_engine_desc* desc, zb200_engine** out);
+void zb200_engine_destroy(zb200_engine* e);
+/* x holds the hidden states [2B*seq_len, d_model] (prefix conditioning ++ embedded prefix codes); writes the KV cache
+ * for positions [0, seq_len) and the CFG logits of the last position. */
+int zb200_engine_prefill(zb200_engine* e, int seq_len, void* stream);
+/* One decode step up to the logits: embeds column state[offset]-1 of `delayed`, position state[pos]. */
+int zb200_engine_decode_logits(zb200_engine* e, void* stream);
+/* decode_logits + sampler pass 1 + pass 2 (one loop iteration of model.py:345-424), no host synchronisation. */
+int zb200_engine_step(zb200_engine* e, const zb200_sampler_args* smp, void* stream);
+/* Captures one step into a CUDA graph (stream capture on `stream`); zb200_engine_run replays it n_steps times. */
+int zb200_engine_capture(zb200_engine* e, const zb200_sampler_args* smp, void* stream);
+int zb200_engine_run(zb200_engine* e, int n_steps, void* stream);
+/* number of kernel launches in one step (for the bench's gpu_launches claim) */
+int zb200_engine_launches_per_step(const zb200_engine* e);
+
 #ifdef __cplusplus
 }
 #endif

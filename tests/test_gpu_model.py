@@ -1,0 +1,140 @@
+"""End-to-end parity of zonos_b200.Zonos (GPU) against golden outputs of the reference and against the CPU oracle."""
+import pytest
+import torch
+
+from oracle import scenarios as sc
+from oracle import shapes
+from oracle.gen_golden import MODEL_CASES
+
+pytestmark = pytest.mark.gpu
+
+# Tolerances.  Both implementations round every head output to bf16 before the fp32 CFG mix u + (c - u) * s
+# (model.py:111-114); a different fp32 accumulation order can move c and u by one bf16 ulp each, which the mix turns
+# into (|s| + |s-1|) ulps.  So: max|d| <= (|s| + |s-1|) * ulp_bf16(max|logit|), and rel-RMS <= 1e-2.
+def logit_max_abs(cfg_scale, ref_logits):
+    import math
+
+    top = float(ref_logits[torch.isfinite(ref_logits)].abs().max())
+    ulp = 2.0 ** (math.floor(math.log2(top)) - 7)
+    return (abs(cfg_scale) + abs(cfg_scale - 1)) * ulp
+
+
+LOGIT_REL_RMS = 1e-2
+
+
+@pytest.fixture(scope="module")
+def tiny_model():
+    from zonos_b200.config import ZonosConfig
+    from zonos_b200.model import Zonos
+
+    cfg = ZonosConfig.from_dict(shapes.reference_config_dict("tiny"))
+    W = shapes.synth_transformer_weights("tiny", seed=0)
+    return Zonos.from_state_dict(cfg, W, "cuda")
+
+
+def _case_inputs(name):
+    B, Lc, P, N, sp, cfg = MODEL_CASES[name]
+    cond = shapes.synth_conditioning(B, Lc, shapes.SHAPES["tiny"]["d_model"], seed=1)
+    pre = None if P == 0 else torch.randint(0, 1024, (B, 9, P), generator=torch.Generator().manual_seed(2))
+    return B, Lc, P, N, sp, cfg, cond, pre
+
+
+def _noise(seed, n, B):
+    tape = sc.NoiseTape(seed)
+    return torch.stack([tape((B, 9, 1026)) for _ in range(n)]).cuda()
+
+
+def test_heads_are_padded_like_the_reference(tiny_model):
+    assert tiny_model.heads[0].weight.shape[0] == 1026 and tiny_model.packed().vocab == 1026
+
+
+@pytest.mark.parametrize("name", list(MODEL_CASES))
+def test_prefill_logits_vs_reference(tiny_model, golden, name):
+    """Prefill logits of the reference (CPU, bf16) vs the CUDA engine, same weights and inputs."""
+    g = golden("model_tiny.pt")["cases"][name]
+    B, Lc, P, N, sp, cfg, cond, pre = _case_inputs(name)
+    ref = g["logits"][0]
+    got = tiny_model._debug_prefill_logits(cond.cuda(), None if pre is None else pre.cuda(), cfg).cpu()
+    finite = torch.isfinite(ref)
+    assert torch.equal(finite, torch.isfinite(got))
+    diff = (got[finite] - ref[finite])
+    assert diff.abs().max() <= logit_max_abs(cfg, ref), diff.abs().max()
+    assert diff.pow(2).mean().sqrt() / ref[finite].pow(2).mean().sqrt() < LOGIT_REL_RMS
+
+
+def _teacher_forced_oracle(name, first_frame, frames, n_steps):
+    """CPU oracle logits for every frame when fed the GPU's own token history (teacher forcing)."""
+    from oracle import delay as od
+    from oracle import generate as og
+
+    B, Lc, P, N, sp, cfg, cond, pre = _case_inputs(name)
+    W = shapes.synth_transformer_weights("tiny", seed=0)
+    codes = torch.full((B, 9, P + N), -1, dtype=torch.int64)
+    if pre is not None:
+        codes[..., :P] = pre
+    delayed = od.apply_delay_pattern(codes, 1025)
+    src = og.ModelLogits(W, "tiny", cond, Lc + P + N + 9, cfg)
+    out = [src.prefill(delayed[..., :P + 1])]
+    ids = first_frame
+    for s in range(n_steps):  # the last iteration's frame is an empty slice (column T+9): it only consumes
+        out.append(src.step(ids))
+        ids = frames[..., s:s + 1]
+    return torch.stack(out)  # [n_steps+1, B, 9, V]
+
+
+@pytest.mark.parametrize("name", list(MODEL_CASES))
+def test_generate_teacher_forced_vs_oracle(tiny_model, golden, name):
+    """Free-running generate on the GPU; every frame's logits are compared with the CPU oracle run on the same token
+    history, and every token the GPU picked must be the oracle's pick or lie within the logit tolerance of it
+    (random-init weights give near-uniform logits, so bf16 near-ties legitimately flip greedy tokens: SURVEY 8(c))."""
+    from oracle import sampling as osmp
+
+    g = golden("model_tiny.pt")["cases"][name]
+    B, Lc, P, N, sp, cfg, cond, pre = _case_inputs(name)
+    taps = []
+    out = tiny_model.generate(cond.cuda(), None if pre is None else pre.cuda(), max_new_tokens=N, cfg_scale=cfg,
+                              batch_size=B, sampling_params=dict(sp), progress_bar=False,
+                              _noise=_noise(77, 2 * (N + 9) + 2, B), _tap=lambda s, l, f: taps.append((l.cpu(), f.cpu())))
+    first_frame = taps[0][1]
+    frames = torch.cat([f for _, f in taps[1:]], -1)
+    gpu_logits = torch.stack([l for l, _ in taps])
+    assert frames.shape == g["frames"].shape
+    ref_logits = _teacher_forced_oracle(name, first_frame, frames, len(taps) - 1)
+    assert len(taps) - 1 == N + P + 9 - (P + 1)  # max_steps iterations, like the reference's while loop
+    finite = torch.isfinite(ref_logits)
+    assert torch.equal(finite, torch.isfinite(gpu_logits))
+    diff = gpu_logits[finite] - ref_logits[finite]
+    tol = logit_max_abs(cfg, ref_logits)
+    assert diff.abs().max() <= tol, diff.abs().max()
+    assert diff.pow(2).mean().sqrt() / ref_logits[finite].pow(2).mean().sqrt() < LOGIT_REL_RMS
+    # token check (greedy cases): replay the oracle's pick on its own logits and the shared history
+    identical = int((frames == g["frames"]).all(dim=1).all(dim=0).long().cumprod(0).sum())
+    print(f"{name}: free-running tokens identical to the reference for {identical}/{frames.shape[-1]} frames; "
+          f"max|dlogit| {diff.abs().max():.4f}")
+    if sp.get("temperature", 1.0) == 0.0:
+        rp, win = sp["repetition_penalty"], sp.get("repetition_penalty_window", 2)
+        codes = torch.full((B, 9, P + N), -1, dtype=torch.int64)
+        if pre is not None:
+            codes[..., :P] = pre
+        from oracle import delay as od
+
+        delayed = od.apply_delay_pattern(codes, 1025)
+        delayed[..., P + 1:P + 2] = torch.where(delayed[..., P + 1:P + 2] == -1, first_frame, delayed[..., P + 1:P + 2])
+        flips = 0
+        for s in range(frames.shape[-1]):
+            col = P + 2 + s
+            lg = ref_logits[s + 1].clone()
+            lg[:, 1:, 1024] = -torch.inf
+            lg[:, 0, 1024] -= torch.log(torch.tensor(1024.0))
+            pen = osmp.repetition_penalty(lg, delayed[..., :col], torch.full((B,), rp), win) if rp != 1.0 else lg
+            want = pen.argmax(-1)
+            cell = delayed[..., col]
+            got = torch.where(cell == -1, frames[..., s], cell)
+            free = cell == -1
+            bad = (want != frames[..., s]) & free
+            if bad.any():
+                margin = pen.max(-1).values - pen.gather(-1, frames[..., s:s + 1]).squeeze(-1)
+                assert float(margin[bad].max()) <= 2 * tol, f"step {s}: token differs with margin {float(margin[bad].max())}"
+                flips += int(bad.sum())
+            delayed[..., col] = got
+        print(f"{name}: {flips} near-tie flips over {frames.shape[-1]} frames")

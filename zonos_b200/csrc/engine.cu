@@ -1,0 +1,260 @@
+// Session engine: sequences the kernels of the prefill and of one decode step, and owns the captured CUDA graph.
+// Reference control flow being replaced: zonos/model.py:103-116 (_compute_logits), :118-179 (_decode_one_token),
+// :181-202 (_prefill); zonos/backbone/_torch.py:73-80,99-102 (backbone / block forward).
+#include "../../include/zonos_b200.h"
+#include "attention.cuh"
+#include "common.cuh"
+#include "epilogues.cuh"
+#include "gemm_tc.cuh"
+#include "ops.cuh"
+#include "sampler.cuh"
+
+using namespace zb;
+
+struct zb200_engine {
+  zb200_engine_desc d;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int launches = 0;  // kernels launched by the last step
+};
+
+namespace {
+
+constexpr int NT = 64;
+constexpr int STAGES = 6;
+constexpr int SM_COUNT = 148;
+
+struct SplitPlan {
+  int splits, kb_per_split;
+};
+// Fill the 148 SMs: n_tiles x splits CTAs, each split at least 4 k-blocks deep, workspace permitting.
+SplitPlan plan_splits(const zb200_engine_desc& d, int n_tiles, int m_tiles, int k_blocks) {
+  int s = 1;
+  if (m_tiles == 1 && n_tiles < SM_COUNT) {
+    s = SM_COUNT / n_tiles;
+    if (s < 1) s = 1;
+    while (s > 1 && k_blocks / s < 4) --s;
+    while (s > 1 && ((int64_t)n_tiles * s * NT * 128 > d.gemm_ws_floats || n_tiles > d.n_gemm_tickets)) --s;
+  }
+  SplitPlan p;
+  p.kb_per_split = ceil_div(k_blocks, s);
+  p.splits = ceil_div(k_blocks, p.kb_per_split);
+  return p;
+}
+
+GemmCore make_core(const zb200_engine_desc& d, const void* w, int n_tiles, int m_rows, int k) {
+  GemmCore g{};
+  const int m_tiles = ceil_div(m_rows, GEMM_BM);
+  const SplitPlan sp = plan_splits(d, n_tiles, m_tiles, k / 64);
+  g.Wp = w, g.k_blocks = k / 64, g.kb_per_split = sp.kb_per_split, g.splits = sp.splits, g.m_valid = m_rows;
+  g.partial_ws = d.gemm_ws, g.tickets = d.gemm_tickets, g.stream_weights = (m_tiles == 1);
+  return g;
+}
+
+KvLayout kv_of(const zb200_engine_desc& d, int layer) {
+  KvLayout kv;
+  kv.pool = (bf16*)d.kv_pool, kv.block_table = d.block_table, kv.pages_per_seq = d.pages_per_seq;
+  kv.num_pages = d.num_pages, kv.n_kv_heads = d.n_kv_heads, kv.layer = layer;
+  return kv;
+}
+
+#define ZB_TRY(expr)                                         \
+  do {                                                       \
+    cudaError_t _e = (expr);                                 \
+    if (_e != cudaSuccess) return zb::cuda_fail(_e, #expr);  \
+    ++e->launches;                                           \
+  } while (0)
+
+// All transformer layers on `rows` rows of x (seq_len positions per sequence), then norm_f + heads + CFG.
+int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream_t st) {
+  const zb200_engine_desc& d = e->d;
+  const int dm = d.d_model, hd = d.n_heads * ZB200_HEAD_DIM, kvd = d.n_kv_heads * ZB200_HEAD_DIM;
+  const int m_tiles = ceil_div(rows, GEMM_BM);
+  const int n_seq = 2 * d.batch;
+  const int* pos_ptr = decode ? d.state + ST_POS : nullptr;
+  bf16 *x = (bf16*)d.x, *xn = (bf16*)d.xn, *q = (bf16*)d.q, *att = (bf16*)d.att, *h = (bf16*)d.h;
+  for (int l = 0; l < d.n_layer; ++l) {
+    const bf16* ln1w = (const bf16*)d.ln1_w + (size_t)l * dm;
+    const bf16* ln1b = (const bf16*)d.ln1_b + (size_t)l * dm;
+    const bf16* ln2w = (const bf16*)d.ln2_w + (size_t)l * dm;
+    const bf16* ln2b = (const bf16*)d.ln2_b + (size_t)l * dm;
+    ZB_TRY(launch_layernorm(x, ln1w, ln1b, xn, rows, dm, d.ln_eps, 1, 0, st));
+    {  // in_proj + RoPE + KV page write
+      const int n_tiles = (hd + 2 * kvd) / NT;
+      GemmCore g = make_core(d, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, n_tiles, rows, dm);
+      ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+      EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, seq_len, d.n_heads};
+      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+    }
+    if (decode) {
+      AttnDecodeArgs a;
+      a.q = q, a.out = att, a.kv = kv_of(d, l), a.pos_ptr = pos_ptr, a.pos_add = 0;
+      a.n_heads = d.n_heads, a.n_kv_heads = d.n_kv_heads, a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
+      a.partial_ws = d.attn_ws, a.tickets = d.attn_tickets;
+      ZB_TRY(launch_attn_decode(a, n_seq, d.attn_nsplit, st));
+    } else {
+      AttnPrefillArgs a;
+      a.q = q, a.out = att, a.kv = kv_of(d, l), a.seq_len = seq_len, a.pos0 = 0, a.n_heads = d.n_heads;
+      a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
+      ZB_TRY(launch_attn_prefill(a, n_seq, st));
+    }
+    {  // out_proj + residual
+      const int n_tiles = dm / NT;
+      GemmCore g = make_core(d, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, n_tiles, rows, hd);
+      ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
+      EpiResidual<NT> epi{x, dm};
+      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+    }
+    ZB_TRY(launch_layernorm(x, ln2w, ln2b, xn, rows, dm, d.ln_eps, 1, 0, st));
+    {  // fc1 + SiLU gate
+      const int n_tiles = d.d_ff / (NT / 2);
+      GemmCore g = make_core(d, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, n_tiles, rows, dm);
+      ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+      EpiSwiGLU<NT> epi{h, d.d_ff};
+      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+    }
+    {  // fc2 + residual
+      const int n_tiles = dm / NT;
+      GemmCore g = make_core(d, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, n_tiles, rows, d.d_ff);
+      ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
+      EpiResidual<NT> epi{x, dm};
+      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+    }
+  }
+  // norm_f on the last position of every sequence, heads + CFG (model.py:110-115)
+  ZB_TRY(launch_layernorm(x, (const bf16*)d.lnf_w, (const bf16*)d.lnf_b, xn, n_seq, dm, d.ln_eps, seq_len, seq_len - 1, st));
+  {
+    const int tiles_per_head = d.head_rows_padded / NT;
+    const int n_tiles = d.n_q * tiles_per_head;
+    GemmCore g = make_core(d, d.w_heads, n_tiles, n_seq, dm);
+    g.m_valid = n_seq;
+    ARowCfgPairs al{(const uint8_t*)xn, (size_t)dm * 2, d.batch};
+    EpiHeadsCfg<NT> epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
+    ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, ceil_div(n_seq, GEMM_BM), st)));
+  }
+  return ZB200_OK;
+}
+
+}  // namespace
+
+static int validate(const zb200_engine_desc& d) {
+  ZB_REQUIRE(d.d_model > 0 && d.d_model % 256 == 0 && d.d_model <= 4096, "engine: d_model=%d must be a multiple of 256 (<= 4096)", d.d_model);
+  ZB_REQUIRE(d.n_heads > 0 && d.n_kv_heads > 0 && d.n_heads % d.n_kv_heads == 0 && d.n_heads / d.n_kv_heads <= 4,
+             "engine: unsupported head layout H=%d Hkv=%d (GQA group <= 4)", d.n_heads, d.n_kv_heads);
+  ZB_REQUIRE(d.d_model == d.n_heads * ZB200_HEAD_DIM, "engine: head_dim must be 128 (d_model=%d, H=%d)", d.d_model, d.n_heads);
+  ZB_REQUIRE(d.d_ff > 0 && d.d_ff % 64 == 0, "engine: d_ff=%d must be a multiple of 64", d.d_ff);
+  ZB_REQUIRE(d.n_q > 0 && d.n_q <= ZB200_MAX_CODEBOOKS && d.vocab > 1025 && d.vocab <= d.head_rows_padded && d.head_rows_padded % 64 == 0,
+             "engine: bad codebook/vocab layout");
+  ZB_REQUIRE(d.batch > 0 && d.rows_max >= 2 * d.batch, "engine: rows_max=%d < 2*batch", d.rows_max);
+  ZB_REQUIRE(d.attn_nsplit >= 1 && d.pages_per_seq > 0 && d.num_pages > 0, "engine: bad KV paging");
+  ZB_REQUIRE(d.emb && d.ln1_w && d.ln1_b && d.ln2_w && d.ln2_b && d.lnf_w && d.lnf_b && d.w_qkv && d.w_out && d.w_fc1 &&
+                 d.w_fc2 && d.w_heads && d.rope && d.kv_pool && d.block_table && d.x && d.xn && d.q && d.att && d.h &&
+                 d.logits && d.gemm_ws && d.gemm_tickets && d.state && d.delayed,
+             "engine: null buffer in descriptor");
+  ZB_REQUIRE(d.attn_nsplit == 1 || (d.attn_ws && d.attn_tickets), "engine: split-KV attention needs workspace");
+  return ZB200_OK;
+}
+
+extern "C" int zb200_engine_create(const zb200_engine_desc* desc, zb200_engine** out) {
+  ZB_REQUIRE(desc && out, "engine_create: null argument");
+  const int rc = validate(*desc);
+  if (rc != ZB200_OK) return rc;
+  zb200_engine* e = new zb200_engine();
+  e->d = *desc;
+  *out = e;
+  return ZB200_OK;
+}
+
+extern "C" void zb200_engine_destroy(zb200_engine* e) {
+  if (!e) return;
+  if (e->exec) cudaGraphExecDestroy(e->exec);
+  if (e->graph) cudaGraphDestroy(e->graph);
+  delete e;
+}
+
+extern "C" int zb200_engine_prefill(zb200_engine* e, int seq_len, void* stream) {
+  ZB_REQUIRE(e && seq_len > 0, "engine_prefill: bad arguments");
+  const int rows = 2 * e->d.batch * seq_len;
+  ZB_REQUIRE(rows <= e->d.rows_max, "engine_prefill: %d rows exceed the workspace (%d)", rows, e->d.rows_max);
+  if (seq_len > e->d.pages_per_seq * ZB200_PAGE) {
+    set_error("engine_prefill: sequence length %d exceeds the KV cache (%d)", seq_len, e->d.pages_per_seq * ZB200_PAGE);
+    return ZB200_ERR_STATE;
+  }
+  e->launches = 0;
+  return run_backbone(e, rows, seq_len, false, (cudaStream_t)stream);
+}
+
+static int decode_logits(zb200_engine* e, cudaStream_t st) {
+  const zb200_engine_desc& d = e->d;
+  // embed the previous frame (column offset-1) for the B conditional rows and duplicate for the unconditional ones
+  ZB_TRY(launch_embed_sum(d.delayed, d.n_q * d.t_delayed, d.t_delayed, d.state + ST_OFFSET, -1, 1, (const bf16*)d.emb,
+                          (bf16*)d.x, d.batch, d.n_q, d.vocab, d.d_model, 1, 0, d.batch, st));
+  return run_backbone(e, 2 * d.batch, 1, true, st);
+}
+
+extern "C" int zb200_engine_decode_logits(zb200_engine* e, void* stream) {
+  ZB_REQUIRE(e, "engine_decode_logits: null engine");
+  e->launches = 0;
+  return decode_logits(e, (cudaStream_t)stream);
+}
+
+static SamplerArgs to_args(const zb200_sampler_args* u) {
+  SamplerArgs a;
+  a.logits = u->logits, a.noise = u->noise, a.delayed = u->delayed, a.tok1 = u->tok1, a.tok2 = u->tok2;
+  a.state = u->state, a.remaining = u->remaining, a.grace = u->grace;
+  a.stopping = u->stopping, a.eos_mode = u->eos_mode, a.mask2 = u->mask2, a.eos_old = u->eos_old;
+  a.host_flags = u->host_flags;
+  a.batch = u->batch, a.n_q = u->n_q, a.vocab = u->vocab, a.t_delayed = u->t_delayed;
+  a.loop_mode = u->loop_mode, a.first_offset = u->first_offset, a.row_base = u->row_base;
+  a.seed = u->seed, a.temperature = u->temperature, a.top_p = u->top_p, a.top_k = u->top_k, a.min_p = u->min_p;
+  a.linear = u->linear, a.conf = u->conf, a.quad = u->quad, a.rep_penalty = u->rep_penalty, a.rep_window = u->rep_window;
+  return a;
+}
+
+static int step(zb200_engine* e, const zb200_sampler_args* smp, cudaStream_t st) {
+  e->launches = 0;
+  const int rc = decode_logits(e, st);
+  if (rc != ZB200_OK) return rc;
+  const SamplerArgs a = to_args(smp);
+  ZB_TRY(launch_sampler(a, 1, st));
+  ZB_TRY(launch_sampler(a, 2, st));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_engine_step(zb200_engine* e, const zb200_sampler_args* smp, void* stream) {
+  ZB_REQUIRE(e && smp && smp->loop_mode == 1, "engine_step: needs loop-mode sampler arguments");
+  ZB_REQUIRE(smp->state == e->d.state && smp->delayed == e->d.delayed && smp->logits == e->d.logits,
+             "engine_step: sampler buffers differ from the engine's");
+  return step(e, smp, (cudaStream_t)stream);
+}
+
+extern "C" int zb200_engine_capture(zb200_engine* e, const zb200_sampler_args* smp, void* stream) {
+  ZB_REQUIRE(e && smp && smp->loop_mode == 1, "engine_capture: needs loop-mode sampler arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (e->exec) cudaGraphExecDestroy(e->exec), e->exec = nullptr;
+  if (e->graph) cudaGraphDestroy(e->graph), e->graph = nullptr;
+  ZB_CHECK_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+  const int rc = step(e, smp, st);
+  cudaGraph_t g = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(st, &g);
+  if (rc != ZB200_OK) {
+    if (g) cudaGraphDestroy(g);
+    return rc;
+  }
+  if (ce != cudaSuccess) return cuda_fail(ce, "cudaStreamEndCapture");
+  e->graph = g;
+  ZB_CHECK_CUDA(cudaGraphInstantiate(&e->exec, e->graph, 0));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_engine_run(zb200_engine* e, int n_steps, void* stream) {
+  ZB_REQUIRE(e && n_steps >= 0, "engine_run: bad arguments");
+  if (!e->exec) {
+    set_error("engine_run: no captured graph (call zb200_engine_capture first)");
+    return ZB200_ERR_STATE;
+  }
+  for (int i = 0; i < n_steps; ++i) ZB_CHECK_CUDA(cudaGraphLaunch(e->exec, (cudaStream_t)stream));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_engine_launches_per_step(const zb200_engine* e) { return e ? e->launches : 0; }

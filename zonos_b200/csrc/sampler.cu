@@ -262,8 +262,11 @@ __device__ void finalize_step(const SamplerArgs& a, int offset) {
     for (int q = 0; q < Q; ++q) {
       int tk = tok[b * Q + q];
       if (stop) tk = (q < diag) ? MASK_ID : (q == diag ? EOS_ID : tk);
-      int32_t* cell = a.delayed + ((size_t)b * Q + q) * a.t_delayed + offset;
-      if (*cell == UNKNOWN_ID) *cell = tk;
+      // the reference's last iteration addresses column T+Q, an empty slice (model.py:417-418): nothing is written
+      if (offset < a.t_delayed) {
+        int32_t* cell = a.delayed + ((size_t)b * Q + q) * a.t_delayed + offset;
+        if (*cell == UNKNOWN_ID) *cell = tk;
+      }
     }
     rem -= 1;
     a.remaining[b] = rem;
