@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""Benchmark of the Zonos batched speech-generation hot path on B200 (contract: see DESIGN.md, "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+  torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...        (one rank per GPU, batch-sharded)
+
+A "step" is one Zonos.generate() call over one batch of synthetic utterances (BASELINE.json configs[2] / SURVEY 8(d)
+C3: batch 64 per GPU, L_cond 128, 9 prefix frames, 2580 new frames = 30 s, min-p 0.1 + repetition penalty 3.0,
+cfg 2.0, random-init Zonos-v0.1-transformer weights).  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+FRAME_RATE = 44100 / 512  # 86.1328 frames per audio second
+C3_SAMPLING = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0,
+                   repetition_penalty_window=2, temperature=1.0)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="utterances per GPU")
+    ap.add_argument("--max-new-tokens", type=int, default=2580)
+    ap.add_argument("--l-cond", type=int, default=128)
+    ap.add_argument("--prefix-frames", type=int, default=9)
+    ap.add_argument("--shape", default="real", choices=["real", "tiny"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--cpu-frames", type=int, default=32, help="decode frames in the CPU baseline sample")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        busy = [s for s in sm if s > 0.5 * max(sm)] if sm else []
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        backend = "nccl" if (args.impl == "b200" and torch.cuda.is_available()) else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
+    elif torch.cuda.is_available():
+        torch.cuda.set_device(0)
+    return world, rank, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+
+
+def max_over_ranks(x: float, world: int, device) -> float:
+    if world == 1:
+        return x
+    import torch.distributed as dist
+
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(x: float, world: int, device) -> float:
+    if world == 1:
+        return x
+    import torch.distributed as dist
+
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+# ---------------------------------------------------------------------------------------------------- B200 arm
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def build_model(args, device):
+    from zonos_b200 import synth
+    from zonos_b200.config import ZonosConfig
+    from zonos_b200.model import Zonos
+
+    shape = synth.REAL if args.shape == "real" else synth.TINY
+    cfg = ZonosConfig.from_dict(synth.config_dict(shape))
+    sd = synth.transformer_state_dict(shape, device=device, seed=0)
+    model = Zonos.from_state_dict(cfg, sd, device)
+    del sd
+    model.packed()
+    return model, shape
+
+
+def step_bytes(shape, batch, ctx):
+    """Algorithmic HBM bytes of one decode step at context `ctx`."""
+    d, L, H, Hkv, F = shape["d_model"], shape["n_layer"], shape["n_heads"], shape["n_kv_heads"], shape["d_ff"]
+    per_layer = ((H + 2 * Hkv) * 128 * d + H * 128 * d + 2 * F * d + F * d + 4 * d) * 2
+    weights = L * per_layer + 2 * d * 2 + 9 * 1026 * d * 2
+    kv_per_pos = L * 2 * Hkv * 128 * 2  # bytes per cached position per sequence
+    b2 = 2 * batch
+    return weights + b2 * kv_per_pos * ctx + b2 * kv_per_pos + batch * 9 * d * 2 + batch * 9 * 1026 * 4
+
+
+def run_generate(model, cond, prefix, args, rank, seed):
+    return model.generate(cond, prefix, max_new_tokens=args.max_new_tokens, cfg_scale=2.0, batch_size=args.batch,
+                          sampling_params=dict(C3_SAMPLING), progress_bar=False, seed=seed, row_base=rank * args.batch)
+
+
+def attn_roofline(shape, batch, ctx, device, hbm_peak):
+    """Dominant kernel of the batch-64 decode step: paged GQA decode attention (KV bytes are ~75 % of the step).
+    Timed alone with CUDA events on the launching stream over a pool larger than L2, at the mean context."""
+    from zonos_b200 import ops
+
+    H, Hkv = shape["n_heads"], shape["n_kv_heads"]
+    n_seq, layers = 2 * batch, 4
+    kv = ops.PagedKV(layers, n_seq, ctx + 64, Hkv, device)
+    kv.pool.normal_()
+    q = torch.randn(n_seq, H * 128, device=device).bfloat16()
+    import math
+
+    nsplit = max(1, min(16, math.ceil(2 * 148 * 2 / (n_seq * Hkv)), kv.pages_per_seq))
+    for l in range(layers):
+        ops.attn_decode(q, kv, l, ctx, H, nsplit)
+    torch.cuda.synchronize()
+    reps = 6
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        for l in range(layers):
+            ops.attn_decode(q, kv, l, ctx, H, nsplit)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / (reps * layers)
+    algo = n_seq * Hkv * ctx * 128 * 2 * 2 + 2 * n_seq * H * 128 * 2  # K+V rows read once, q in, out
+    achieved = algo / (ms * 1e-3) / 1e9
+    return {"kernel": "attn_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
+            "frac": round(achieved / hbm_peak, 4), "traffic": None, "bytes_per_launch": algo, "ms_per_launch": round(ms, 5),
+            "ctx": ctx, "nsplit": nsplit}
+
+
+def latency_batch1(model, shape, args, device, hbm_peak):
+    """BASELINE configs[1]: batch 1, L_cond 23, greedy, 30 s: per-frame latency of the graph-replayed decode step."""
+    from zonos_b200 import synth
+
+    cond = synth.conditioning(1, 23, shape["d_model"], device=device, seed=1)
+    n = min(args.max_new_tokens, 2580)
+    side = torch.cuda.Stream(device=device)  # stream capture is not allowed on the legacy default stream
+    side.wait_stream(torch.cuda.current_stream(device))
+    with torch.cuda.stream(side):
+        loop, eng, delayed = model._open_session(cond, None, n, 2.0, 1, dict(temperature=0.0, repetition_penalty=1.0), 0, 0, None)
+        try:
+            loop.sample_first(eng.logits)
+            a = loop.args(eng.logits, True)
+            eng.step(a)
+            eng.capture(a)
+            side.synchronize()
+            steps = loop.max_steps - 1
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+            evs[0].record(side)
+            for i in range(steps):
+                eng.run(1)
+                evs[i + 1].record(side)
+            side.synchronize()
+            t = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(3, steps))
+            launches = eng.launches_per_step()
+        finally:
+            eng.close()
+    torch.cuda.current_stream(device).wait_stream(side)
+    q = lambda f: t[min(len(t) - 1, int(f * len(t)))]
+    mean_ctx = 23 + 1 + steps / 2
+    algo = step_bytes(shape, 1, mean_ctx)
+    p50 = q(0.5)
+    return {"p50_ms": round(p50, 4), "p90_ms": round(q(0.9), 4), "p99_ms": round(q(0.99), 4), "frames": len(t),
+            "launches_per_frame": launches, "algorithmic_bytes_per_frame": int(algo),
+            "hbm_frac_at_p50": round(algo / (p50 * 1e-3) / 1e9 / hbm_peak, 4)}
+
+
+# ---------------------------------------------------------------------------------------------------- CPU arm
+def cpu_reference_sample(frames: int, shape_name: str = "real", threads=None):
+    """The reference's CPU path restated in oracle/ (the reference itself is Python source that cannot travel to the
+    GPU box; oracle/ is pinned to it bit-for-bit by tests/test_oracle_golden.py): BASELINE configs[0] shape -- batch 1,
+    L_cond 23, greedy -- on a bounded sample: prefill + `frames` decode frames.  Returns (audio-s/s, seconds, cores)."""
+    from oracle import generate as og
+    from oracle import shapes
+
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    W = shapes.synth_transformer_weights(shape_name, seed=0)
+    cond = shapes.synth_conditioning(1, 23, shapes.SHAPES[shape_name]["d_model"], seed=1)
+    t0 = time.perf_counter()
+    with torch.inference_mode():
+        out = og.generate_with_model(W, shape_name, cond, None, frames, 2.0, dict(temperature=0.0, repetition_penalty=1.0))
+    dt = time.perf_counter() - t0
+    audio_s = sum(o.shape[1] for o in out) / FRAME_RATE
+    return audio_s / dt, dt, cores
+
+
+def main_reference(args, world, rank):
+    """--impl reference: the reference's own CPU implementation of the path on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    frames = args.cpu_frames
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_sample(4, args.shape)
+    vals, secs = [], []
+    for _ in range(args.steps):
+        v, dt, cores = cpu_reference_sample(frames, args.shape)
+        vals.append(v), secs.append(dt)
+    value = len(vals) * (frames / FRAME_RATE) / sum(secs)
+    sample = f"batch 1, L_cond 23, greedy, prefill + {frames + 8} decode frames ({frames} audio frames) per step"
+    line = {
+        "impl": "reference", "metric": "audio-sec/sec", "value": round(value, 5), "unit": "audio-s/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * sum(secs) / len(secs), 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "Zonos.generate, Zonos-v0.1-transformer shape, random-init, CPU reference path (oracle port)",
+                   "shape": args.shape, "sample": sample},
+        "cpu_baseline": {"value": round(value, 5), "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(value, 5), "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main_b200(args, world, rank, local):
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device (there is no CPU fallback)")
+    device = torch.device("cuda", local if world > 1 else 0)
+    hbm_peak, peak_src = peaks()
+    model, shape = build_model(args, device)
+    from zonos_b200 import synth
+
+    B, Lc, P = args.batch, args.l_cond, args.prefix_frames
+    cond = synth.conditioning(B, Lc, shape["d_model"], device=device, seed=1 + rank)
+    g = torch.Generator(device=device).manual_seed(2 + rank)
+    prefix = torch.randint(0, 1024, (B, 9, P), generator=g, device=device) if P > 0 else None
+    cond_host = cond.cpu().pin_memory()
+    prefix_host = None if prefix is None else prefix.cpu().pin_memory()
+
+    for i in range(args.warmup):
+        run_generate(model, cond, prefix, args, rank, 1234)
+    torch.cuda.synchronize()
+
+    clocks = ClockSampler(local if world > 1 else 0)
+    if rank == 0:
+        clocks.start()
+    # ---- device-resident inputs: `value`
+    barrier(world)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    frames_out, launches = 0, 0
+    e0.record()
+    for i in range(args.steps):
+        out = run_generate(model, cond, prefix, args, rank, 1234)
+        frames_out += sum(o.shape[1] for o in out)
+        st = model.last_generate_stats
+        launches += st["launches_per_step"] * (st["steps"] + 1) + 2 + 3  # frames + prefill(same kernel list) + first sample + setup
+    e1.record()
+    torch.cuda.synchronize()
+    barrier(world)
+    ms_dev = max_over_ranks(e0.elapsed_time(e1), world, device)
+    total_frames = sum_over_ranks(frames_out, world, device)
+    steps_per_gen = model.last_generate_stats["steps"]
+
+    # ---- end to end through the public API with HOST buffers: pinned conditioning in, codes out
+    barrier(world)
+    torch.cuda.synchronize()
+    h2d = cond_host.numel() * cond_host.element_size() + (0 if prefix_host is None else prefix_host.numel() * 8)
+    d2h, frames_e2e = 0, 0
+    e0.record()
+    for i in range(args.steps):
+        c = cond_host.to(device, non_blocking=True)
+        pfx = None if prefix_host is None else prefix_host.to(device, non_blocking=True)
+        out = run_generate(model, c, pfx, args, rank, 1234)
+        host_codes = [o.cpu() for o in out]
+        frames_e2e += sum(o.shape[1] for o in host_codes)
+        d2h = sum(o.numel() * 8 for o in host_codes)
+    e1.record()
+    torch.cuda.synchronize()
+    barrier(world)
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world, device)
+    total_frames_e2e = sum_over_ranks(frames_e2e, world, device)
+    clk = clocks.stop() if rank == 0 else None
+
+    if rank != 0:
+        return
+    value = total_frames / FRAME_RATE / (ms_dev * 1e-3)
+    e2e = total_frames_e2e / FRAME_RATE / (ms_e2e * 1e-3)
+    mean_ctx = Lc + P + 1 + steps_per_gen / 2
+    ms_per_frame = ms_dev / args.steps / max(1, steps_per_gen + 1)
+    algo_step = step_bytes(shape, B, mean_ctx)
+    roof = attn_roofline(shape, B, int(mean_ctx), device, hbm_peak)
+    roof["peak_source"] = peak_src
+    line = {
+        "metric": "audio-sec/sec", "value": round(value, 2), "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 2), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "Zonos.generate C3: Zonos-v0.1-transformer shape, random-init, batch %d/GPU, L_cond %d, "
+                               "%d prefix frames, %d new frames, min_p 0.1 + rep. penalty 3.0, cfg 2.0" % (B, Lc, P, args.max_new_tokens),
+                   "shape": args.shape, "global_batch": B * world, "parallelism": f"batch-sharded x{world}, no collectives",
+                   "l2": "inputs larger than L2 (3.2 GB weights + paged KV per step)", "dac_decode": "not in the timed region"},
+        "e2e": {"value": round(e2e, 2), "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches,
+        "clocks": clk,
+        "roofline": roof,
+        "decode_step": {"ms_per_frame": round(ms_per_frame, 4), "algorithmic_bytes": int(algo_step),
+                        "hbm_frac": round(algo_step / (ms_per_frame * 1e-3) / 1e9 / hbm_peak, 4), "mean_ctx": mean_ctx,
+                        "launches_per_frame": model.last_generate_stats["launches_per_step"]},
+    }
+    if not args.no_latency:
+        line["latency_batch1"] = latency_batch1(model, shape, args, device, hbm_peak)
+    if world == 1 and not args.no_cpu_baseline:
+        del model
+        torch.cuda.empty_cache()
+        frames = args.cpu_frames
+        v, dt, cores = cpu_reference_sample(frames, args.shape)
+        line["cpu_baseline"] = {"value": round(v, 5), "unit": "audio-s/s", "cores": cores, "kind": "port",
+                                "sample": f"batch 1, L_cond 23, greedy, prefill + {frames + 8} decode frames on the host "
+                                          f"cores ({dt:.1f} s); oracle/ port of the reference's CPU path"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    world, rank, local = dist_setup(args)
+    if args.impl == "reference":
+        main_reference(args, world, rank)
+    else:
+        main_b200(args, world, rank, local)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
