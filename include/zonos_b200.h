@@ -142,6 +142,35 @@ int zb200_engine_run(zb200_engine* e, int n_steps, void* stream);
 /* number of kernel launches in one step (for the bench's gpu_launches claim) */
 int zb200_engine_launches_per_step(const zb200_engine* e);
 
+/* ---- DACAutoencoder.decode (zonos/autoencoder.py:44-47 -> transformers DacModel.decode, modeling_dac.py:608-638) ---
+ * The decoder is described as a list of implicit-GEMM layers over five caller-owned fp16 work regions (channels-last
+ * [batch][time][pitch]); the host shim (zonos_b200/dac.py) builds the list from the HF state dict once. */
+typedef struct {
+  int32_t taps;          /* 7, 1, or 2 (transposed conv) */
+  int32_t shift0, shift_step; /* time shift of tap i = shift0 + i*shift_step */
+  int32_t up;            /* 0 = Conv1d; s > 0 = ConvTranspose1d with stride s, kernel 2s, padding s/2 */
+  int32_t pitch_in;      /* channel pitch of the input region (multiple of 64) */
+  int32_t c_out, pitch_out, tile_n; /* output channels, output pitch, N tile (64 or 96) */
+  int32_t t_mul_in;      /* input rows per code frame (T_in = t_mul_in * T) */
+  int32_t in_region, resid_region, raw_region, act_region; /* region index or -1 */
+  const void* w;         /* packed fp16 [n_total][taps*pitch_in], n_total = c_out * max(up,1) */
+  const float* bias;     /* [n_total] */
+  const float* alpha;    /* [c_out] Snake alpha of the consumer (NULL when act_region < 0) */
+  const float* inv_alpha;/* [c_out] 1/(alpha + 1e-9) */
+} zb200_dac_layer;
+typedef struct {
+  int32_t n_q, n_codes, latent, n_layers;
+  const float* code_table;       /* fp32 [n_q][n_codes][latent]: out_proj_k(codebook_k) + bias_k */
+  const zb200_dac_layer* layers; /* host array */
+  int32_t z_region;              /* region receiving from_codes output (pitch = latent) */
+  int32_t final_region, final_c, final_pitch, final_t_mul; /* input of the last conv (k7 -> 1 channel) + tanh */
+  const float* final_w;          /* fp32 [7][final_c] */
+  float final_bias;
+} zb200_dac_plan;
+/* codes int64 [batch][n_q][t]  ->  wav fp32 [batch][final_t_mul * t].  regions: 5 device buffers of region_halves fp16. */
+int zb200_dac_decode(const zb200_dac_plan* plan, const int64_t* codes, int batch, int t, void* const* regions,
+                     int64_t region_halves, float* wav, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

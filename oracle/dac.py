@@ -57,3 +57,31 @@ def decode(W, codes, strides=(8, 8, 4, 2), taps=None):
     """codes int64 [B,9,T] -> fp32 [B,1,512*T]."""
     assert codes.shape[1] == 9, f"Expected 9 codebooks, got {codes.shape[1]}"
     return decoder(W, from_codes(W, codes), strides, taps).float()
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# fp16-storage model of the same decoder: what the reference computes on CUDA under torch.autocast(fp16)
+# (zonos/autoencoder.py:46): conv weights and conv inputs are fp16, conv outputs are rounded to fp16, Snake runs in
+# fp32 on the fp16 conv output and is rounded to fp16 when the next conv consumes it, residual adds are fp16 + fp16.
+# Accumulation stays fp32 here (CPU), so this isolates the rounding POINTS; used to separate "fp16 storage error"
+# (this model vs fp32) from kernel error (CUDA vs this model).
+def _h(x):
+    return x.half().float()
+
+
+def decode_fp16_storage(W, codes, strides=(8, 8, 4, 2)):
+    Wh = {k: (_h(v) if k.endswith("weight") and "codebook" not in k and "quantizer" not in k else v) for k, v in W.items()}
+    x = _h(from_codes(W, codes))
+    x = _h(F.conv1d(x, Wh["decoder.conv1.weight"], W["decoder.conv1.bias"], padding=3))
+    for j, s in enumerate(strides):
+        p = f"decoder.block.{j}."
+        x = _h(F.conv_transpose1d(_h(snake(x, W[p + "snake1.alpha"])), Wh[p + "conv_t1.weight"], W[p + "conv_t1.bias"],
+                                  stride=s, padding=math.ceil(s / 2)))
+        for r, dil in ((1, 1), (2, 3), (3, 9)):
+            q = p + f"res_unit{r}."
+            y = _h(F.conv1d(_h(snake(x, W[q + "snake1.alpha"])), Wh[q + "conv1.weight"], W[q + "conv1.bias"],
+                            dilation=dil, padding=3 * dil))
+            y = _h(F.conv1d(_h(snake(y, W[q + "snake2.alpha"])), Wh[q + "conv2.weight"], W[q + "conv2.bias"]))
+            x = _h(x + y)
+    x = _h(F.conv1d(_h(snake(x, W["decoder.snake1.alpha"])), _h(W["decoder.conv2.weight"]), W["decoder.conv2.bias"], padding=3))
+    return torch.tanh(x).float()

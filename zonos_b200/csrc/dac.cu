@@ -1,0 +1,237 @@
+// DAC 44.1 kHz decoder (zonos/autoencoder.py:44-47 -> transformers DacModel.decode, modeling_dac.py:608-638).
+//
+// Every convolution is an implicit GEMM on the tcgen05 core (gemm_tc.cuh) over channels-last fp16 activations
+// [batch][time][channels]:  out[t, co] = sum_tap sum_ci x[t + shift(tap), ci] * W[co][tap][ci]
+//   * Conv1d k=7, dilation d : 7 taps, shift = (tap-3)*d, zero padding outside [0,T)     (modeling_dac.py:181-186,417,426)
+//   * Conv1d k=1             : 1 tap
+//   * ConvTranspose1d k=2s, stride s, padding s/2 (:243-249): each output phase r has exactly two taps, so it is a
+//     2-tap conv with N = s*C_out columns (n = r*C_out + co) over rows j = 0..T_in, scattered to t = s*j + r - s/2.
+// The A operand of tap `tap` is the same activation tile shifted in time, gathered by cp.async with zero fill.
+// Fused epilogue: + bias, (+ residual), store raw fp16 and/or Snake(alpha of the CONSUMER layer) fp16, so Snake1d
+// (:94-99) never makes its own pass over memory.  fp16 storage / fp32 accumulate mirrors the reference's CUDA autocast.
+#include "../../include/zonos_b200.h"
+#include "common.cuh"
+#include "gemm_tc.cuh"
+
+namespace zb {
+
+typedef __half f16;
+
+// ------------------------------------------------------------------------------------------------ A loader
+struct AConvTaps {
+  const uint8_t* base;  // fp16 [B][T][pitch]
+  int T;                // input rows per batch element
+  int m_rows;           // GEMM rows per batch element (T, or T+1 for the transposed conv)
+  int tiles_per_seq;    // ceil(m_rows / 128)
+  int cblocks;          // pitch / 64 : k-blocks per tap
+  int row_bytes;        // pitch * 2
+  int shift0, shift_step;  // time shift of tap i = shift0 + i*shift_step
+  __device__ int rows(int m_tile, int) const { return min(GEMM_BM, m_rows - (m_tile % tiles_per_seq) * GEMM_BM); }
+  __device__ const void* src(int r, int m_tile, int kb, int c, bool& valid) const {
+    const int b = m_tile / tiles_per_seq, tl = m_tile - b * tiles_per_seq;
+    const int tap = kb / cblocks, cb = kb - tap * cblocks;
+    const int t = tl * GEMM_BM + r + shift0 + tap * shift_step;
+    valid = (t >= 0) && (t < T);
+    const int tc = valid ? t : 0;
+    return base + ((size_t)b * T + tc) * row_bytes + cb * 128 + c * 16;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------ epilogue
+__device__ __forceinline__ float snake_f(float x, float alpha, float inv_alpha) {
+  const float s = sinf(alpha * x);
+  return x + inv_alpha * (s * s);
+}
+
+template <int NT>
+struct EpiDac {
+  const float* bias;       // [n_total] (per output column; for the transposed conv: bias[co] repeated per phase)
+  const f16* resid;        // optional [B][T_out][pitch_out]
+  f16* out_raw;            // optional
+  f16* out_act;            // optional: Snake with the consumer's alpha
+  const float* alpha;      // [C_out]
+  const float* inv_alpha;  // [C_out] = 1/(alpha + 1e-9)
+  int T_out, tiles_per_seq, pitch_out, C_out, n_total;
+  int up, pad;             // transposed conv: stride and padding (up == 0: plain conv)
+  __device__ void operator()(int row, bool valid, int m_tile, int n_tile, float* acc) const {
+    if (!valid) return;
+    const int b = m_tile / tiles_per_seq, j = (m_tile - b * tiles_per_seq) * GEMM_BM + row;
+#pragma unroll
+    for (int c = 0; c < NT; c += 8) {
+      const int n = n_tile * NT + c;
+      if (n >= n_total) break;
+      int t = j, co = n;
+      if (up > 0) {
+        const int r = n / C_out;
+        co = n - r * C_out;
+        t = up * j + r - pad;
+      }
+      if (t < 0 || t >= T_out) continue;
+      const size_t off = ((size_t)b * T_out + t) * pitch_out + co;
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[c + i] + __ldg(bias + n + i)));
+      if (resid) {
+        const uint4 ru = *reinterpret_cast<const uint4*>(resid + off);
+        const __half2* rh = reinterpret_cast<const __half2*>(&ru);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 rf = __half22float2(rh[i]);
+          v[2 * i] = __half2float(__float2half_rn(v[2 * i] + rf.x));
+          v[2 * i + 1] = __half2float(__float2half_rn(v[2 * i + 1] + rf.y));
+        }
+      }
+      if (out_raw) {
+        uint4 o;
+        __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+        *reinterpret_cast<uint4*>(out_raw + off) = o;
+      }
+      if (out_act) {
+        uint4 o;
+        __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          oh[i] = __floats2half2_rn(snake_f(v[2 * i], __ldg(alpha + co + 2 * i), __ldg(inv_alpha + co + 2 * i)),
+                                    snake_f(v[2 * i + 1], __ldg(alpha + co + 2 * i + 1), __ldg(inv_alpha + co + 2 * i + 1)));
+        *reinterpret_cast<uint4*>(out_act + off) = o;
+      }
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------ from_codes
+// z[b,t,:] = sum_k table[k][codes[b,k,t]][:]  with table[k][c] = out_proj_k(codebook_k[c]) + bias_k precomputed in fp32
+// at load time (modeling_dac.py:345-369: embedding -> 1x1 conv, summed over the 9 codebooks in order).
+__global__ void dac_from_codes_kernel(const int64_t* __restrict__ codes, const float* __restrict__ table,
+                                      f16* __restrict__ z, int T, int n_q, int n_codes, int latent) {
+  const int t = blockIdx.x, b = blockIdx.y;
+  __shared__ int sc[ZB200_MAX_CODEBOOKS];
+  if (threadIdx.x < n_q) {
+    const long long c = (long long)codes[((size_t)b * n_q + threadIdx.x) * T + t];
+    sc[threadIdx.x] = (int)(c < 0 ? 0 : (c >= n_codes ? n_codes - 1 : c));
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < latent; c += blockDim.x) {
+    float acc = 0.f;
+    for (int k = 0; k < n_q; ++k) acc += __ldg(table + ((size_t)k * n_codes + sc[k]) * latent + c);
+    z[((size_t)b * T + t) * latent + c] = __float2half_rn(acc);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ last conv + tanh
+// wav[b,t] = tanh( sum_{tap<7, ci<C} x[b, t+tap-3, ci] * w[tap][ci] + bias )   (modeling_dac.py:426-427,436-437)
+constexpr int FIN_TILE = 256;
+__global__ void __launch_bounds__(FIN_TILE) dac_final_conv_kernel(const f16* __restrict__ x, const float* __restrict__ w,
+                                                                  float bias, float* __restrict__ wav, int T, int C,
+                                                                  int pitch) {
+  extern __shared__ uint8_t fin_smem[];
+  const int sp = C / 2 + 1;  // row pitch in half2 words (+1: conflict-free column walks)
+  __half2* xs = reinterpret_cast<__half2*>(fin_smem);
+  float* ws = reinterpret_cast<float*>(xs + (FIN_TILE + 6) * sp);
+  const int b = blockIdx.y, t0 = blockIdx.x * FIN_TILE;
+  for (int i = threadIdx.x; i < 7 * C; i += FIN_TILE) ws[i] = w[i];
+  const int words = C / 2;
+  for (int i = threadIdx.x; i < (FIN_TILE + 6) * words; i += FIN_TILE) {
+    const int r = i / words, cw = i - r * words, t = t0 + r - 3;
+    __half2 v = __floats2half2_rn(0.f, 0.f);
+    if (t >= 0 && t < T) v = *reinterpret_cast<const __half2*>(x + ((size_t)b * T + t) * pitch + 2 * cw);
+    xs[r * sp + cw] = v;
+  }
+  __syncthreads();
+  const int t = t0 + threadIdx.x;
+  if (t >= T) return;
+  float acc = bias;
+  for (int tap = 0; tap < 7; ++tap) {
+    const __half2* row = xs + (threadIdx.x + tap) * sp;
+    const float* wr = ws + tap * C;
+    for (int cw = 0; cw < words; ++cw) {
+      const float2 f = __half22float2(row[cw]);
+      acc = fmaf(f.x, wr[2 * cw], acc);
+      acc = fmaf(f.y, wr[2 * cw + 1], acc);
+    }
+  }
+  wav[(size_t)b * T + t] = tanhf(__half2float(__float2half_rn(acc)));
+}
+
+}  // namespace zb
+
+using namespace zb;
+
+template <int NT>
+static cudaError_t launch_dac_layer(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
+  const int T_in = L.t_mul_in * T;
+  const int m_rows = L.up > 0 ? T_in + 1 : T_in;
+  const int T_out = L.up > 0 ? T_in * L.up : T_in;
+  const int n_total = L.c_out * (L.up > 0 ? L.up : 1);
+  const int tiles_per_seq = ceil_div(m_rows, GEMM_BM);
+  AConvTaps al;
+  al.base = (const uint8_t*)regions[L.in_region], al.T = T_in, al.m_rows = m_rows, al.tiles_per_seq = tiles_per_seq;
+  al.cblocks = L.pitch_in / 64, al.row_bytes = L.pitch_in * 2, al.shift0 = L.shift0, al.shift_step = L.shift_step;
+  EpiDac<NT> epi;
+  epi.bias = L.bias;
+  epi.resid = L.resid_region >= 0 ? (const f16*)regions[L.resid_region] : nullptr;
+  epi.out_raw = L.raw_region >= 0 ? (f16*)regions[L.raw_region] : nullptr;
+  epi.out_act = L.act_region >= 0 ? (f16*)regions[L.act_region] : nullptr;
+  epi.alpha = L.alpha, epi.inv_alpha = L.inv_alpha;
+  epi.T_out = T_out, epi.tiles_per_seq = tiles_per_seq, epi.pitch_out = L.pitch_out, epi.C_out = L.c_out;
+  epi.n_total = n_total, epi.up = L.up, epi.pad = L.up / 2;
+  GemmCore g{};
+  g.Wp = L.w, g.k_blocks = L.taps * (L.pitch_in / 64), g.kb_per_split = g.k_blocks, g.splits = 1;
+  g.m_valid = batch * tiles_per_seq * GEMM_BM, g.partial_ws = nullptr, g.tickets = nullptr, g.stream_weights = 0;
+  // the pad columns of an A-operand region must be finite zeros (the matching weights are zero, but 0 * NaN = NaN)
+  if (L.pitch_out > L.c_out) {
+    const size_t rows = (size_t)batch * T_out;
+    for (int r : {L.raw_region, L.act_region})
+      if (r >= 0) {
+        cudaError_t e = cudaMemset2DAsync((f16*)regions[r] + L.c_out, (size_t)L.pitch_out * 2, 0,
+                                          (size_t)(L.pitch_out - L.c_out) * 2, rows, st);
+        if (e != cudaSuccess) return e;
+      }
+  }
+  return launch_gemm_tc<NT, 4, 0>(g, al, epi, ceil_div(n_total, NT), batch * tiles_per_seq, st);
+}
+
+extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, int batch, int t, void* const* regions,
+                                int64_t region_halves, float* wav, void* stream) {
+  ZB_REQUIRE(p && codes && regions && wav && batch > 0 && t > 0, "dac_decode: bad arguments");
+  ZB_REQUIRE(p->n_q > 0 && p->n_q <= ZB200_MAX_CODEBOOKS && p->latent % 64 == 0, "dac_decode: bad quantizer shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  // capacity check of every region use
+  for (int i = 0; i < p->n_layers; ++i) {
+    const zb200_dac_layer& L = p->layers[i];
+    ZB_REQUIRE(L.pitch_in % 64 == 0 && L.pitch_out % 8 == 0 && L.c_out % 8 == 0 && (L.tile_n == 64 || L.tile_n == 96),
+               "dac_decode: layer %d has an unsupported shape", i);
+    const int64_t T_in = (int64_t)L.t_mul_in * t, T_out = L.up > 0 ? T_in * L.up : T_in;
+    ZB_REQUIRE(batch * T_in * L.pitch_in <= region_halves && batch * T_out * L.pitch_out <= region_halves,
+               "dac_decode: layer %d does not fit the work regions (%lld halves)", i, (long long)region_halves);
+    ZB_REQUIRE((int64_t)batch * ceil_div((int)(L.up > 0 ? T_in + 1 : T_in), GEMM_BM) * ceil_div(L.c_out * (L.up > 0 ? L.up : 1), L.tile_n) < (1ll << 31),
+               "dac_decode: layer %d grid too large", i);
+  }
+  {
+    dim3 grid(t, batch);
+    dac_from_codes_kernel<<<grid, 256, 0, st>>>(codes, p->code_table, (f16*)regions[p->z_region], t, p->n_q, p->n_codes, p->latent);
+    ZB_CHECK_LAUNCH("dac_from_codes_kernel");
+  }
+  for (int i = 0; i < p->n_layers; ++i) {
+    const zb200_dac_layer& L = p->layers[i];
+    cudaError_t e = L.tile_n == 96 ? launch_dac_layer<96>(L, batch, t, regions, st) : launch_dac_layer<64>(L, batch, t, regions, st);
+    if (e != cudaSuccess) return cuda_fail(e, "dac layer launch");
+  }
+  {
+    const int T_out = p->final_t_mul * t;
+    const size_t smem = (size_t)(FIN_TILE + 6) * (p->final_c / 2 + 1) * 4 + (size_t)7 * p->final_c * 4;
+    static bool configured = false;
+    if (!configured) {
+      ZB_CHECK_CUDA(cudaFuncSetAttribute(dac_final_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      configured = true;
+    }
+    ZB_REQUIRE(smem <= 96 * 1024 && p->final_c % 2 == 0, "dac_decode: final conv too wide");
+    dim3 grid(ceil_div(T_out, FIN_TILE), batch);
+    dac_final_conv_kernel<<<grid, FIN_TILE, smem, st>>>((const f16*)regions[p->final_region], p->final_w, p->final_bias, wav,
+                                                        T_out, p->final_c, p->final_pitch);
+    ZB_CHECK_LAUNCH("dac_final_conv_kernel");
+  }
+  return ZB200_OK;
+}

@@ -31,6 +31,7 @@ struct GemmCore {
   float* partial_ws;     // [m_tiles*n_tiles][splits][NT/4][128] float4, only when splits > 1
   int* tickets;          // [m_tiles*n_tiles], zero-initialised, self-resetting
   int stream_weights;    // 1: weights are read once per launch -> L2 evict_first
+  int n_tiles;           // N tiles; blockIdx.x = m_tile * n_tiles + n_tile (set by launch_gemm_tc)
 };
 
 template <int NT, int STAGES>
@@ -62,7 +63,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(GemmCore g, AL
   __shared__ int s_is_last;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int n_tile = blockIdx.x, split = blockIdx.y, m_tile = blockIdx.z;
+  const int m_tile = blockIdx.x / g.n_tiles, n_tile = blockIdx.x - m_tile * g.n_tiles, split = blockIdx.y;
   const int kb0 = split * g.kb_per_split;
   const int kb1 = min(g.k_blocks, kb0 + g.kb_per_split);
   const int nkb = kb1 - kb0;
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(GemmCore g, AL
 
   if (warp < 4) {
     // ------------------------------------------------------------------ A producers (cp.async gather -> SW128 tile)
-    const int rows = min(GEMM_BM, g.m_valid - m_tile * GEMM_BM);
+    const int rows = aload.rows(m_tile, g.m_valid);
     int arrived = 0;
     for (int i = 0; i < nkb; ++i) {
       const int s = i % STAGES;
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(GemmCore g, AL
     const bool row_valid = row < rows;
 
     if (g.splits > 1) {
-      const int tile_id = m_tile * gridDim.x + n_tile;
+      const int tile_id = m_tile * g.n_tiles + n_tile;
       float4* ws = reinterpret_cast<float4*>(g.partial_ws) + (size_t)tile_id * g.splits * (NT / 4) * 128;
       if (row_valid) {
         float4* mine = ws + (size_t)split * (NT / 4) * 128;
@@ -207,6 +208,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(GemmCore g, AL
 struct ARowMajor {
   const uint8_t* base;
   size_t row_bytes;
+  __device__ int rows(int m_tile, int m_valid) const { return min(GEMM_BM, m_valid - m_tile * GEMM_BM); }
   __device__ const void* src(int r, int m_tile, int kb, int c, bool& valid) const {
     return base + (size_t)(m_tile * GEMM_BM + r) * row_bytes + (size_t)kb * 128 + c * 16;
   }
@@ -216,6 +218,7 @@ struct ARowStrided {
   const uint8_t* base;
   size_t row_bytes;
   int map_mul, map_add;
+  __device__ int rows(int m_tile, int m_valid) const { return min(GEMM_BM, m_valid - m_tile * GEMM_BM); }
   __device__ const void* src(int r, int m_tile, int kb, int c, bool& valid) const {
     return base + (size_t)((m_tile * GEMM_BM + r) * map_mul + map_add) * row_bytes + (size_t)kb * 128 + c * 16;
   }
@@ -226,6 +229,7 @@ struct ARowCfgPairs {
   const uint8_t* base;
   size_t row_bytes;
   int batch;  // B utterances; rows [0,B) cond, [B,2B) uncond
+  __device__ int rows(int m_tile, int m_valid) const { return min(GEMM_BM, m_valid - m_tile * GEMM_BM); }
   __device__ const void* src(int r, int m_tile, int kb, int c, bool& valid) const {
     const int u = m_tile * (GEMM_BM / 2) + (r >> 1);
     const int grow = (r & 1) ? batch + u : u;
@@ -235,8 +239,10 @@ struct ARowCfgPairs {
 
 // ------------------------------------------------------------------------------------------------ launch helper
 template <int NT, int STAGES, int AB_FMT, class ALoader, class Epilogue>
-cudaError_t launch_gemm_tc(const GemmCore& g, const ALoader& al, const Epilogue& epi, int n_tiles, int m_tiles,
+cudaError_t launch_gemm_tc(const GemmCore& g_in, const ALoader& al, const Epilogue& epi, int n_tiles, int m_tiles,
                            cudaStream_t stream) {
+  GemmCore g = g_in;
+  g.n_tiles = n_tiles;
   using SM = GemmSmem<NT, STAGES>;
   auto kern = gemm_tc_kernel<NT, STAGES, AB_FMT, ALoader, Epilogue>;
   static bool configured = false;  // per template instantiation
@@ -245,7 +251,7 @@ cudaError_t launch_gemm_tc(const GemmCore& g, const ALoader& al, const Epilogue&
     if (e != cudaSuccess) return e;
     configured = true;
   }
-  dim3 grid(n_tiles, g.splits, m_tiles);
+  dim3 grid((unsigned)n_tiles * (unsigned)m_tiles, g.splits, 1);
   kern<<<grid, GEMM_THREADS, SM::DYN_BYTES, stream>>>(g, al, epi);
   return cudaGetLastError();
 }
