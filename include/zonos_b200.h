@@ -49,6 +49,19 @@ int64_t zb200_packed_weight_bytes(int n_rows, int k, int tile_n, int row_mode, i
  * may be NULL when splits == 1. */
 int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int splits,
                     float* ws, int* tickets, void* stream);
+/* Same contract for m <= 128 rows through the weight-streaming stream-K kernel of the decode step (csrc/gemm_skinny.cuh)
+ * on `grid` CTAs.  ws: >= grid * 32768 floats, tickets: >= ceil(n/64) zeroed ints. */
+int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int grid,
+                           float* ws, int64_t ws_floats, int* tickets, int n_tickets, void* stream);
+/* The out_proj / fc2 + residual + next LayerNorm group of the decode step (_torch.py:99-102): x <- bf16(x + bf16(a w^T)),
+ * xn <- LayerNorm(x) * ln_w + ln_b, as a split-K weight-streaming GEMM whose partial sums are reduced by the fused
+ * residual + LayerNorm kernel.  m <= 128, n % 256 == 0 (<= 4096); ws: >= splits*m*n floats. */
+int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_packed, int n, int k, int splits, float* ws,
+                        int64_t ws_floats, void* x, const void* ln_w, const void* ln_b, void* xn, float eps, void* stream);
+/* Debug (libraries built with ZB200_TRACE=1 only, ZB200_ERR_STATE otherwise): device_buf uint64 [64][160][12] receives the
+ * in-kernel globaltimer timeline of the following zb200_gemm_skinny_bf16 launches (NULL: off); returns the number of
+ * launches traced since the previous call. */
+int zb200_debug_trace(unsigned long long* device_buf);
 /* nn.LayerNorm(d, eps) with affine weight+bias on bf16 rows, fp32 statistics (_torch.py:62,88,90). */
 int zb200_layernorm(const void* x, const void* w, const void* b, void* out, int rows, int d, float eps, void* stream);
 /* Zonos.embed_codes (model.py:97-98): sum over codebooks in order, each add rounded to bf16.

@@ -45,6 +45,56 @@ def test_gemm_tcgen05(ops, M, N, K, splits):
     assert torch.equal(out, out2)
 
 
+@pytest.mark.parametrize("M,N,K,grid", [(2, 64, 64, 1), (2, 192, 512, 5), (2, 3072, 2048, 148), (128, 3072, 2048, 148),
+                                        (128, 2048, 2048, 148), (7, 1026, 512, 37), (100, 256, 8192, 148), (2, 2048, 8192, 148),
+                                        (2, 16384, 2048, 148), (20, 2048, 8192, 111), (128, 16384, 2048, 74), (64, 9792, 2048, 148),
+                                        (2, 128, 4096, 128), (9, 64, 8192, 128)])
+def test_gemm_skinny_stream_k(ops, M, N, K, grid):
+    """Weight-streaming stream-K kernel of the decode step: all three A-row variants, fragments that start / end inside
+    a tile, tiles shared by many CTAs (grid > tiles), CTAs spanning several tiles, N not a multiple of 64."""
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N + grid)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    wp = ops.pack_weight(w)
+    n_tiles = (N + 63) // 64
+    ws = torch.full((max(grid, 1) * 32768,), float("nan"), device="cuda")  # stale partials must never be read
+    tickets = torch.zeros(n_tiles, dtype=torch.int32, device="cuda")
+    out = ops.gemm_skinny_bf16(a, wp, N, grid=grid, ws=ws, tickets=tickets)
+    ref = (a.float() @ w.float().t())
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2 * max(1.0, ref.abs().max().item()), err
+    assert int(tickets.abs().sum()) == 0  # self-reset
+    for _ in range(3):  # back-to-back launches (programmatic dependent launch): bitwise reproducible
+        out2 = ops.gemm_skinny_bf16(a, wp, N, grid=grid, ws=ws, tickets=tickets)
+    assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("M,N,K,splits", [(2, 2048, 2048, 8), (2, 2048, 8192, 8), (128, 2048, 2048, 8), (128, 2048, 8192, 8),
+                                          (6, 512, 512, 2), (20, 512, 1024, 1), (64, 1024, 2048, 4)])
+def test_gemm_resid_ln(ops, M, N, K, splits):
+    """out_proj / fc2 group of the decode step: deferred split-K GEMM + fused residual + LayerNorm kernel, against the
+    reference's op order (Linear -> bf16, residual add -> bf16, LayerNorm -> bf16: zonos/backbone/_torch.py:99-102)."""
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    x = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    lw = (1 + 0.1 * torch.randn(N, device="cuda", generator=g)).bfloat16()
+    lb = (0.05 * torch.randn(N, device="cuda", generator=g)).bfloat16()
+    x2, xn = ops.gemm_resid_ln(a, ops.pack_weight(w), x, lw, lb, splits=splits)
+    lin = (a.float() @ w.float().t()).bfloat16()
+    x_ref = (x.float() + lin.float()).bfloat16()
+    xn_ref = torch.nn.functional.layer_norm(x_ref.float(), (N,), lw.float(), lb.float(), 1e-5).bfloat16()
+    # the GEMM may differ from the fp32 matmul by one bf16 ulp of the Linear output at rounding ties
+    assert (x2.float() - x_ref.float()).abs().max().item() <= 2 ** -6 * max(1.0, x_ref.float().abs().max().item())
+    assert ((x2 != x_ref).float().mean().item()) < 0.02
+    xn_from_x2 = torch.nn.functional.layer_norm(x2.float(), (N,), lw.float(), lb.float(), 1e-5).bfloat16()
+    d = (xn.float() - xn_from_x2.float()).abs()
+    assert d.max().item() <= 2 ** -6 * max(1.0, xn_from_x2.float().abs().max().item())
+    assert (d > 0).float().mean().item() < 0.02
+    x3, xn3 = ops.gemm_resid_ln(a, ops.pack_weight(w), x, lw, lb, splits=splits)
+    assert torch.equal(x2, x3) and torch.equal(xn, xn3)
+
+
 def test_layernorm(ops):
     g = torch.Generator().manual_seed(0)
     for rows, d in [(2, 2048), (128, 2048), (5, 512), (3, 1024)]:

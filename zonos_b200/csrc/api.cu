@@ -1,6 +1,7 @@
 // Error plumbing and version of the C ABI (include/zonos_b200.h).
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/zonos_b200.h"
 #include "common.cuh"
@@ -17,6 +18,10 @@ void set_error(const char* fmt, ...) {
 int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
   return ZB200_ERR_CUDA;
+}
+bool pdl_enabled() {
+  static const bool on = (getenv("ZB200_NO_PDL") == nullptr);
+  return on;
 }
 }  // namespace zb
 

@@ -57,14 +57,10 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(AttnDecodeArgs
   __shared__ float s_m[ATT_CONSUMER_WARPS][4], s_l[ATT_CONSUMER_WARPS][4];
   __shared__ int s_is_last;
 
+  pdl_launch_dependents();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kvh = blockIdx.x, seq = blockIdx.y, split = blockIdx.z, nsplit = gridDim.z;
   const int group = p.n_heads / p.n_kv_heads;  // 4 query heads share one kv head
-  const int n_keys = (p.pos_ptr ? *p.pos_ptr : 0) + p.pos_add + 1;
-  const int n_pages = (n_keys + PAGE - 1) / PAGE;
-  const int pps = (n_pages + nsplit - 1) / nsplit;
-  const int pg0 = min(n_pages, split * pps), pg1 = min(n_pages, pg0 + pps);
-
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -72,6 +68,12 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(AttnDecodeArgs
     }
     fence_barrier_init();
   }
+  pdl_wait_prior();  // q, this step's K/V rows and the position come from the in_proj kernel
+  const int n_keys = (p.pos_ptr ? *p.pos_ptr : 0) + p.pos_add + 1;
+  const int n_pages = (n_keys + PAGE - 1) / PAGE;
+  const int pps = (n_pages + nsplit - 1) / nsplit;
+  const int pg0 = min(n_pages, split * pps), pg1 = min(n_pages, pg0 + pps);
+
   __syncthreads();
 
   if (warp == ATT_CONSUMER_WARPS) {
@@ -261,8 +263,7 @@ cudaError_t launch_attn_decode(const AttnDecodeArgs& a, int n_seq, int nsplit, c
     configured = true;
   }
   dim3 grid(a.n_kv_heads, n_seq, nsplit);
-  kern<<<grid, ATT_THREADS, AttSmem<STAGES>::DYN, st>>>(a);
-  return cudaGetLastError();
+  return launch_pdl(kern, grid, dim3(ATT_THREADS), (size_t)AttSmem<STAGES>::DYN, st, pdl_enabled(), a);
 }
 
 // ------------------------------------------------------------------------------------------------ prefill

@@ -200,4 +200,19 @@ __host__ __device__ __forceinline__ uint32_t sw128_offset(uint32_t r, uint32_t c
 __device__ __forceinline__ void pdl_wait_prior() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Launch with the programmatic-stream-serialization attribute: the kernel may be scheduled before its predecessor in
+// the stream has finished and orders itself with griddepcontrol.wait (pdl_wait_prior).  Works under stream capture.
+template <class... KArgs, class... Args>
+cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at, cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+bool pdl_enabled();  // api.cu: false when ZB200_NO_PDL is set in the environment
+
 }  // namespace zb

@@ -5,9 +5,13 @@
 #include "attention.cuh"
 #include "common.cuh"
 #include "epilogues.cuh"
+#include "gemm_skinny.cuh"
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 #include "sampler.cuh"
+
+#include <algorithm>
+#include <cstdlib>
 
 using namespace zb;
 
@@ -16,6 +20,7 @@ struct zb200_engine {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   int launches = 0;  // kernels launched by the last step
+  int sk_sms = 0;    // SMs the weight-streaming GEMM plans for (0: tiled kernel only)
 };
 
 namespace {
@@ -58,12 +63,133 @@ KvLayout kv_of(const zb200_engine_desc& d, int layer) {
   return kv;
 }
 
+// ---- decode-step GEMM plans (weight-streaming kernel, gemm_skinny.cuh) -------------------------------------------------
+// Every CTA should be exactly one fragment, so grids are aligned to the group structure:
+//   ticketed epilogues (in_proj, fc1, heads): whole groups per CTA when there are enough groups; otherwise each group is
+//     shared by at most 3 CTAs (the last one to arrive reduces, so the contributor count is the fix-up latency);
+//   deferred epilogues (out_proj, fc2): n_groups * splits CTAs, the split sums are reduced by resid_ln_kernel.
+// `sms` CTAs are resident at M > 32 (192 KB of shared memory each), 2 * sms at M <= 32.
+struct SkPlan {
+  int grid, splits;
+  bool prefer_k1;
+};
+SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
+  const int cap = sms * (rows <= 32 ? 2 : 1);
+  SkPlan p{cap, 1, false};
+  int mode = skinny_mode(rows, n_tiles, k_blocks);
+  int groups = n_tiles / skinny_tg(mode);
+  if (groups * 2 <= cap && mode == MODE_T2) {  // few, shared groups: single-tile units keep the fix-up slots at 32 KB
+    p.prefer_k1 = true;
+    mode = MODE_K1, groups = n_tiles;
+  }
+  if (groups >= cap) {
+    for (int r = 1; r <= 2; ++r)
+      if (groups % r == 0 && groups / r <= cap) {
+        p.grid = groups / r;
+        return p;
+      }
+    p.grid = cap;  // unaligned stream-K: most groups end up with two contributors
+  } else {
+    const int s = std::max(1, std::min(3, cap / groups));
+    p.grid = groups * s;
+  }
+  return p;
+}
+SkPlan plan_deferred(int sms, int rows, int n_tiles, int k_blocks, int64_t ws_floats, int n) {
+  const int cap = sms * (rows <= 32 ? 2 : 1);
+  const int mode = skinny_mode(rows, n_tiles, k_blocks);
+  const int groups = n_tiles / skinny_tg(mode), kbu = k_blocks / skinny_kg(mode);
+  int s = 1;
+  for (int c = 1; c <= kbu; ++c)
+    if (kbu % c == 0 && groups * c <= cap && kbu / c >= 2 && (int64_t)c * rows * n <= ws_floats) s = c;
+  return SkPlan{groups * s, s, false};
+}
+
+SkinnyCore sk_core(const zb200_engine_desc& d, const void* w, int n_tiles, int rows, int k) {
+  SkinnyCore g{};
+  g.Wp = w, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = rows;
+  g.partial_ws = d.gemm_ws, g.tickets = d.gemm_tickets, g.split_units = 0, g.trace = nullptr, g.trace_id = -1;
+  return g;
+}
+
+// Ticketed-epilogue GEMM: the weight-streaming kernel for the decode step (rows <= 128), the tiled kernel otherwise.
+template <class ALoader, class Epilogue>
+cudaError_t gemm_any(const zb200_engine* e, const void* w, int n_tiles, int rows, int k, const ALoader& al,
+                     const Epilogue& epi, cudaStream_t st) {
+  const zb200_engine_desc& d = e->d;
+  if (rows <= GEMM_BM && e->sk_sms > 0) {
+    const SkPlan p = plan_ticketed(e->sk_sms, rows, n_tiles, k / 64);
+    return launch_gemm_skinny(sk_core(d, w, n_tiles, rows, k), al, epi, p.grid, st, p.prefer_k1);
+  }
+  GemmCore g = make_core(d, w, n_tiles, rows, k);
+  return launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, ceil_div(rows, GEMM_BM), st);
+}
+
 #define ZB_TRY(expr)                                         \
   do {                                                       \
     cudaError_t _e = (expr);                                 \
     if (_e != cudaSuccess) return zb::cuda_fail(_e, #expr);  \
     ++e->launches;                                           \
   } while (0)
+
+// Decode step with rows = 2B <= 128: every projection streams its weights through gemm_skinny; out_proj and fc2 leave
+// their split-K partial sums to the fused residual + LayerNorm kernel, which also produces the next GEMM's input.
+int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
+  const zb200_engine_desc& d = e->d;
+  const int dm = d.d_model, hd = d.n_heads * ZB200_HEAD_DIM, kvd = d.n_kv_heads * ZB200_HEAD_DIM;
+  const int rows = 2 * d.batch, n_seq = rows;
+  const int* pos_ptr = d.state + ST_POS;
+  bf16 *x = (bf16*)d.x, *xn = (bf16*)d.xn, *q = (bf16*)d.q, *att = (bf16*)d.att, *h = (bf16*)d.h;
+  const SkPlan p_out = plan_deferred(e->sk_sms, rows, dm / NT, hd / 64, d.gemm_ws_floats, dm);
+  const SkPlan p_fc2 = plan_deferred(e->sk_sms, rows, dm / NT, d.d_ff / 64, d.gemm_ws_floats, dm);
+  ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w, (const bf16*)d.ln1_b, xn, rows, dm, d.ln_eps, 1, 0, st));
+  for (int l = 0; l < d.n_layer; ++l) {
+    {  // in_proj + RoPE + KV page write
+      ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+      EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, 1, d.n_heads};
+      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
+    }
+    {
+      AttnDecodeArgs a;
+      a.q = q, a.out = att, a.kv = kv_of(d, l), a.pos_ptr = pos_ptr, a.pos_add = 0;
+      a.n_heads = d.n_heads, a.n_kv_heads = d.n_kv_heads, a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
+      a.partial_ws = d.attn_ws, a.tickets = d.attn_tickets;
+      ZB_TRY(launch_attn_decode(a, n_seq, d.attn_nsplit, st));
+    }
+    {  // out_proj (split-K partials) -> residual + norm2
+      SkinnyCore g = sk_core(d, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, dm / NT, rows, hd);
+      g.split_units = (hd / 64) / skinny_kg(skinny_mode(rows, dm / NT, hd / 64)) / p_out.splits;
+      ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
+      EpiPartial epi{d.gemm_ws, rows, dm};
+      ZB_TRY(launch_gemm_skinny(g, al, epi, p_out.grid, st));
+      ZB_TRY(launch_resid_ln(x, d.gemm_ws, p_out.splits, rows, (const bf16*)d.ln2_w + (size_t)l * dm,
+                             (const bf16*)d.ln2_b + (size_t)l * dm, xn, dm, d.ln_eps, st));
+    }
+    {  // fc1 + SiLU gate
+      ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+      EpiSwiGLU<NT> epi{h, d.d_ff};
+      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
+    }
+    {  // fc2 (split-K partials) -> residual + the next layer's norm (norm_f after the last layer)
+      SkinnyCore g = sk_core(d, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, dm / NT, rows, d.d_ff);
+      g.split_units = (d.d_ff / 64) / skinny_kg(skinny_mode(rows, dm / NT, d.d_ff / 64)) / p_fc2.splits;
+      ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
+      EpiPartial epi{d.gemm_ws, rows, dm};
+      ZB_TRY(launch_gemm_skinny(g, al, epi, p_fc2.grid, st));
+      const bool last = (l + 1 == d.n_layer);
+      const bf16* nw = last ? (const bf16*)d.lnf_w : (const bf16*)d.ln1_w + (size_t)(l + 1) * dm;
+      const bf16* nb = last ? (const bf16*)d.lnf_b : (const bf16*)d.ln1_b + (size_t)(l + 1) * dm;
+      ZB_TRY(launch_resid_ln(x, d.gemm_ws, p_fc2.splits, rows, nw, nb, xn, dm, d.ln_eps, st));
+    }
+  }
+  {  // heads + CFG on the normalised rows (model.py:110-115)
+    const int tiles_per_head = d.head_rows_padded / NT;
+    ARowCfgPairs al{(const uint8_t*)xn, (size_t)dm * 2, d.batch};
+    EpiHeadsCfg<NT> epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
+    ZB_TRY(gemm_any(e, d.w_heads, d.n_q * tiles_per_head, n_seq, dm, al, epi, st));
+  }
+  return ZB200_OK;
+}
 
 // All transformer layers on `rows` rows of x (seq_len positions per sequence), then norm_f + heads + CFG.
 int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream_t st) {
@@ -81,10 +207,9 @@ int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream
     ZB_TRY(launch_layernorm(x, ln1w, ln1b, xn, rows, dm, d.ln_eps, 1, 0, st));
     {  // in_proj + RoPE + KV page write
       const int n_tiles = (hd + 2 * kvd) / NT;
-      GemmCore g = make_core(d, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, n_tiles, rows, dm);
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
       EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, seq_len, d.n_heads};
-      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, n_tiles, rows, dm, al, epi, st));
     }
     if (decode) {
       AttnDecodeArgs a;
@@ -100,25 +225,22 @@ int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream
     }
     {  // out_proj + residual
       const int n_tiles = dm / NT;
-      GemmCore g = make_core(d, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, n_tiles, rows, hd);
       ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
       EpiResidual<NT> epi{x, dm};
-      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, n_tiles, rows, hd, al, epi, st));
     }
     ZB_TRY(launch_layernorm(x, ln2w, ln2b, xn, rows, dm, d.ln_eps, 1, 0, st));
     {  // fc1 + SiLU gate
       const int n_tiles = d.d_ff / (NT / 2);
-      GemmCore g = make_core(d, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, n_tiles, rows, dm);
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
       EpiSwiGLU<NT> epi{h, d.d_ff};
-      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, n_tiles, rows, dm, al, epi, st));
     }
     {  // fc2 + residual
       const int n_tiles = dm / NT;
-      GemmCore g = make_core(d, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, n_tiles, rows, d.d_ff);
       ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
       EpiResidual<NT> epi{x, dm};
-      ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, m_tiles, st)));
+      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, n_tiles, rows, d.d_ff, al, epi, st));
     }
   }
   // norm_f on the last position of every sequence, heads + CFG (model.py:110-115)
@@ -126,11 +248,9 @@ int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream
   {
     const int tiles_per_head = d.head_rows_padded / NT;
     const int n_tiles = d.n_q * tiles_per_head;
-    GemmCore g = make_core(d, d.w_heads, n_tiles, n_seq, dm);
-    g.m_valid = n_seq;
     ARowCfgPairs al{(const uint8_t*)xn, (size_t)dm * 2, d.batch};
     EpiHeadsCfg<NT> epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
-    ZB_TRY((launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, ceil_div(n_seq, GEMM_BM), st)));
+    ZB_TRY(gemm_any(e, d.w_heads, n_tiles, n_seq, dm, al, epi, st));
   }
   return ZB200_OK;
 }
@@ -161,6 +281,14 @@ extern "C" int zb200_engine_create(const zb200_engine_desc* desc, zb200_engine**
   if (rc != ZB200_OK) return rc;
   zb200_engine* e = new zb200_engine();
   e->d = *desc;
+  {
+    int sms = SM_COUNT, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (const char* v = getenv("ZB200_SK_SMS")) sms = atoi(v);  // 0 switches the decode step back to the tiled kernel
+    // fix-up workspace per SM: two CTAs x two slots x one 32 KB sub-tile (M <= 32) or one CTA x two slots x two sub-tiles
+    const int64_t cap = desc->gemm_ws_floats / (4 * SK_PARTIAL_F4 * 4);
+    e->sk_sms = (int)std::max<int64_t>(0, std::min<int64_t>(sms, cap));
+  }
   *out = e;
   return ZB200_OK;
 }
@@ -189,6 +317,7 @@ static int decode_logits(zb200_engine* e, cudaStream_t st) {
   // embed the previous frame (column offset-1) for the B conditional rows and duplicate for the unconditional ones
   ZB_TRY(launch_embed_sum(d.delayed, d.n_q * d.t_delayed, d.t_delayed, d.state + ST_OFFSET, -1, 1, (const bf16*)d.emb,
                           (bf16*)d.x, d.batch, d.n_q, d.vocab, d.d_model, 1, 0, d.batch, st));
+  if (2 * d.batch <= GEMM_BM && e->sk_sms > 0) return run_decode_skinny(e, st);
   return run_backbone(e, 2 * d.batch, 1, true, st);
 }
 

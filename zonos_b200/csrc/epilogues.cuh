@@ -48,6 +48,21 @@ struct EpiStoreBf16 {
   }
 };
 
+// Deferred split-K (gemm_skinny.cuh): the raw fp32 partial sums of one K split go to ws[split][row][n]; the consumer
+// (resid_ln_kernel, ops.cu) adds the splits in order, rounds, adds the residual and normalises.
+struct EpiPartial {
+  static constexpr bool kDeferred = true;
+  float* ws;  // [splits][rows][ldn]
+  int rows, ldn;
+  __device__ void partial(int row, bool valid, int n_tile, int split, const float* acc) const {
+    if (!valid) return;
+    float4* o = reinterpret_cast<float4*>(ws + ((size_t)split * rows + row) * ldn + n_tile * 64);
+#pragma unroll
+    for (int c = 0; c < 16; ++c) o[c] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+  }
+  __device__ void operator()(int, bool, int, int, float*) const {}
+};
+
 // x[row, n] = bf16( x[row, n] + bf16(acc) )      (out_proj / fc2 followed by the residual add, _torch.py:100-101)
 template <int NT>
 struct EpiResidual {

@@ -1,0 +1,403 @@
+// Weight-streaming GEMM of the decode step:  C[M <= 128, N] = A[M, K] * W[N, K]^T  (bf16 in, fp32 accumulate).
+//
+// At M = 2B <= 128 rows every projection of the decode step is bound by reading W once from HBM (intensity ~ M flop/B,
+// far below the tensor ridge), so the kernel is built around ONE thing: every SM streams an equal, contiguous range of
+// the packed weights with many bytes in flight, and nothing on the per-stage path waits for a round trip.
+//
+//   * Work unit = one 16 KB shared-memory stage of weights:
+//       MODE_K2: two consecutive k-blocks of one 64-row n_tile (one contiguous 16 KB bulk copy)      -- M <= 32
+//       MODE_T2: one k-block of two adjacent n_tiles (UMMA N = 128; the A k-block is reused twice)    -- M  > 32
+//       MODE_K1: one k-block of one n_tile (8 KB; fallback when K/64 is odd or the tile count is odd)
+//     Units are numbered group-major (group = n_tile or n_tile pair) and CTA c of G owns units [c*U/G, (c+1)*U/G):
+//     "stream-K" with a static, balanced partition.
+//   * weight producer warp (one lane): 1-D TMA bulk copies (UBLKCP, evict-first) into a ring.  It does not depend on
+//     the previous kernel, so under programmatic dependent launch it streams while the previous kernels still drain.
+//   * A producer warp(s): cp.async gather of the A k-block(s) (functor, as in gemm_tc.cuh) into a short ring.  The loop
+//     polls: it issues a stage whenever one is free and otherwise retires the oldest landed stage, so the round trip
+//     "MMA done -> stage free -> load -> landed" is off the critical path.  Only A_ROWS (8 / 32 / 128) rows are staged;
+//     the tensor core still reads a 128-row operand, the rows past A_ROWS are whatever follows in shared memory and
+//     only ever reach TMEM lanes that nobody reads.
+//   * MMA warp (one lane): tcgen05.mma M=128, two TMEM accumulator sets (ping-pong per fragment).
+//   * warps 0-3 = epilogue: a CTA's range is cut into fragments (runs of units of one group).  A fragment that covers
+//     the whole K runs the fused epilogue directly; otherwise its fp32 partial goes to the CTA's workspace slot and the
+//     LAST contributor to arrive (ticket) sums all contributors in CTA order (bitwise reproducible) and runs the
+//     epilogue.  Nobody waits for anybody: no co-residency requirement.
+//   * M <= 32: 224 threads, <= 112 KB shared memory -> two CTAs per SM, i.e. the next GEMM of the step (launched early
+//     by PDL) prefetches its weights next to the running one.
+#pragma once
+#include "common.cuh"
+#include "gemm_tc.cuh"
+
+namespace zb {
+
+constexpr int SK_NT = 64;                         // weight rows of one packed tile
+constexpr int SK_TILE_BYTES = SK_NT * 128;        // 8 KB packed (n_tile, k_block) image
+constexpr int SK_PARTIAL_F4 = (SK_NT / 4) * 128;  // float4 per partial sub-tile (32 KB)
+enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2 };
+
+// Optional in-kernel timeline (build with ZB200_TRACE=1): globaltimer stamps per launch / CTA / event.
+#ifdef SK_TRACE
+constexpr int SKT_LAUNCHES = 64, SKT_CTAS = 160, SKT_EVENTS = 12;
+__device__ __forceinline__ void sk_stamp(unsigned long long* trace, int launch, int ev) {
+  if (trace && launch >= 0 && launch < SKT_LAUNCHES && blockIdx.x < SKT_CTAS) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[((size_t)launch * SKT_CTAS + blockIdx.x) * SKT_EVENTS + ev] = t;
+  }
+}
+#define SK_STAMP(ev) sk_stamp(g.trace, g.trace_id, ev)
+#else
+#define SK_STAMP(ev)
+#endif
+
+// Epilogues with `static constexpr bool kDeferred = true` take every fragment raw through
+//   partial(row, row_valid, n_tile, split, acc)        split = first unit of the fragment / split_units
+// and leave the reduction over splits to their consumer kernel (resid_ln_kernel): no workspace slots, no tickets.
+template <class E, class = void>
+struct sk_is_deferred { static constexpr bool value = false; };
+template <class E>
+struct sk_is_deferred<E, decltype((void)E::kDeferred)> { static constexpr bool value = E::kDeferred; };
+
+struct SkinnyCore {
+  const void* Wp;     // packed weights [n_tiles][k_blocks][8 KB]
+  int n_tiles, k_blocks;
+  int m_valid;        // rows of A (<= 128)
+  float* partial_ws;  // [gridDim.x][2][TG][SK_PARTIAL_F4] float4
+  int* tickets;       // [n_groups] zero-initialised, self-resetting
+  int split_units;    // deferred epilogues: units per split (the grid is aligned: every CTA is one fragment)
+  unsigned long long* trace;  // debug timeline [64][160][12] (trace builds), else nullptr
+  int trace_id;               // launch slot of the debug timeline
+};
+
+template <int A_ROWS, int MODE>
+struct SkinnyCfg {
+  static constexpr int TG = (MODE == MODE_T2) ? 2 : 1;  // n_tiles per unit
+  static constexpr int KG = (MODE == MODE_K2) ? 2 : 1;  // k-blocks per unit
+  static constexpr int PROD_WARPS = (A_ROWS >= 128) ? 4 : 1;
+  static constexpr int PROD_THREADS = PROD_WARPS * 32;
+  static constexpr int THREADS = (4 + PROD_WARPS + 2) * 32;
+  static constexpr int MIN_BLOCKS = (A_ROWS >= 128) ? 1 : 2;
+  static constexpr int A_SUB_BYTES = A_ROWS * 128;
+  static constexpr int A_STAGE_BYTES = KG * A_SUB_BYTES;
+  static constexpr int W_STAGE_BYTES = TG * KG * SK_TILE_BYTES;
+  static constexpr int SA = 4;
+  static constexpr int SW = (A_ROWS >= 128) ? (128 * 1024 / W_STAGE_BYTES)
+                                            : ((A_ROWS > 8 ? 64 : 96) * 1024 / W_STAGE_BYTES);
+  static constexpr int A_BYTES = SA * A_STAGE_BYTES;
+  static constexpr int W_BYTES = SW * W_STAGE_BYTES;
+  static constexpr int BAR_OFFSET = A_BYTES + W_BYTES;
+  static constexpr int N_BARS = 2 * SA + 2 * SW + 4;
+  static constexpr int TOTAL = BAR_OFFSET + N_BARS * 8 + 16;
+  static constexpr int DYN_BYTES = TOTAL + 1024;
+  static constexpr uint32_t TMEM_COLS = 2 * TG * SK_NT;  // 128 or 256
+  static_assert(W_BYTES >= GEMM_BM * 128, "the 128-row operand read must stay inside the allocation");
+  static_assert(MIN_BLOCKS == 1 || DYN_BYTES <= 113 * 1024, "two CTAs per SM need <= 113 KB each");
+};
+
+// first unit of CTA c, and the CTA that owns unit u (inverse of the former)
+__host__ __device__ __forceinline__ int sk_first_unit(int c, int units, int grid) { return (int)((long long)c * units / grid); }
+__host__ __device__ __forceinline__ int sk_owner(int u, int units, int grid) {
+  return (int)((((long long)u + 1) * grid + units - 1) / units) - 1;
+}
+
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {  // non-blocking
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
+template <int A_ROWS, int MODE, class ALoader, class Epilogue>
+__global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_ROWS, MODE>::MIN_BLOCKS)
+    gemm_skinny_kernel(SkinnyCore g, ALoader aload, Epilogue epi) {
+  using C = SkinnyCfg<A_ROWS, MODE>;
+  constexpr int TG = C::TG, KG = C::KG, SA = C::SA, SW = C::SW;
+  constexpr int W_WARP = 4 + C::PROD_WARPS, MMA_WARP = W_WARP + 1;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_ring = smem;
+  uint8_t* w_ring = smem + C::A_BYTES;
+  uint64_t* full_a = reinterpret_cast<uint64_t*>(smem + C::BAR_OFFSET);
+  uint64_t* empty_a = full_a + SA;
+  uint64_t* full_w = empty_a + SA;
+  uint64_t* empty_w = full_w + SW;
+  uint64_t* tmem_full = empty_w + SW;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  __shared__ int s_is_last;
+
+  pdl_launch_dependents();  // the next kernel of the step may start its own prologue / weight prefetch
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) SK_STAMP(0);
+  const int KB = g.k_blocks;
+  const int KBU = KB / KG;                 // units per group
+  const int n_groups = g.n_tiles / TG;
+  const int units = n_groups * KBU, G = gridDim.x, cta = blockIdx.x;
+  const int u0 = sk_first_unit(cta, units, G), u1 = sk_first_unit(cta + 1, units, G);
+  const int n_units = u1 - u0;
+
+  if (tid == 0) {
+    for (int s = 0; s < SA; ++s) {
+      mbar_init(&full_a[s], C::PROD_THREADS);
+      mbar_init(&empty_a[s], 1);
+    }
+    for (int s = 0; s < SW; ++s) {
+      mbar_init(&full_w[s], 1);
+      mbar_init(&empty_w[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == MMA_WARP) tmem_alloc(tmem_slot, C::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) SK_STAMP(1);
+
+  if (warp == W_WARP) {
+    // ------------------------------------------------------------------ weight producer (independent of prior kernels)
+    if (lane == 0) {
+      const uint64_t pol = l2_policy_evict_first();
+      const uint8_t* wp = reinterpret_cast<const uint8_t*>(g.Wp);
+      int grp = u0 / KBU, ku = u0 - grp * KBU;
+      for (int i = 0; i < n_units; ++i) {
+        const int s = i % SW;
+        mbar_wait(&empty_w[s], ((i / SW) & 1) ^ 1);
+        mbar_arrive_expect_tx(&full_w[s], C::W_STAGE_BYTES);
+        uint8_t* dst = w_ring + s * C::W_STAGE_BYTES;
+        if (MODE == MODE_T2) {
+          const uint8_t* src = wp + ((size_t)(2 * grp) * KB + ku) * SK_TILE_BYTES;
+          bulk_g2s_hint(dst, src, SK_TILE_BYTES, &full_w[s], pol);
+          bulk_g2s_hint(dst + SK_TILE_BYTES, src + (size_t)KB * SK_TILE_BYTES, SK_TILE_BYTES, &full_w[s], pol);
+        } else {  // units are contiguous in memory
+          bulk_g2s_hint(dst, wp + (size_t)(u0 + i) * C::W_STAGE_BYTES, C::W_STAGE_BYTES, &full_w[s], pol);
+        }
+        if (++ku == KBU) ku = 0, ++grp;
+        if (i == 0) SK_STAMP(2);
+      }
+      SK_STAMP(10);
+    }
+  } else if (warp == MMA_WARP) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc(GEMM_BM, TG * SK_NT, 1);
+      int i = 0, f = 0, u = u0;
+      while (u < u1) {
+        const int grp = u / KBU, ku_begin = u - grp * KBU;
+        const int ku_end = min(KBU, ku_begin + (u1 - u));
+        const int b = f & 1;
+        mbar_wait(&tmem_empty[b], ((f >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(b * TG * SK_NT);
+        for (int ku = ku_begin; ku < ku_end; ++ku, ++i) {
+          const int sa = i % SA, sw = i % SW;
+          mbar_wait(&full_w[sw], (i / SW) & 1);
+          if (i == 0) SK_STAMP(3);
+          mbar_wait(&full_a[sa], (i / SA) & 1);
+          if (i == 0) SK_STAMP(5);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(a_ring + sa * C::A_STAGE_BYTES);
+          const uint32_t w_addr = smem_u32(w_ring + sw * C::W_STAGE_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < KG; ++kk) {
+            const uint64_t adesc = umma_desc_sw128(a_addr + kk * C::A_SUB_BYTES);
+            const uint64_t bdesc = umma_desc_sw128(w_addr + kk * SK_TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < GEMM_BK / 16; ++k)
+              umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                       (ku != ku_begin) || (kk != 0) || (k != 0));
+          }
+          umma_commit(&empty_a[sa]);
+          umma_commit(&empty_w[sw]);
+        }
+        umma_commit(&tmem_full[b]);
+        u += ku_end - ku_begin;
+        ++f;
+      }
+      SK_STAMP(6);
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ A producers (cp.async gather -> SW128 tiles)
+    pdl_wait_prior();  // activations are written by the previous kernel
+    const int ptid = tid - 128;
+    if (ptid == 0) SK_STAMP(4);
+    const int rows = min(g.m_valid, A_ROWS);
+    constexpr int CHUNKS = KG * A_ROWS * 8;  // 16-byte chunks per stage
+    constexpr int PER_THREAD = (CHUNKS + C::PROD_THREADS - 1) / C::PROD_THREADS;
+    constexpr int MAXPEND = 4;
+    static_assert(MAXPEND <= SA, "pending cp.async groups must fit the ring");
+    int issued = 0, arrived = 0;
+    int ku = u0 % KBU;
+    while (arrived < n_units) {
+      // ramp: the first stage is retired as soon as it lands, then up to MAXPEND loads stay in flight
+      bool can_issue = issued < n_units && (issued - arrived) < min(MAXPEND, arrived + 1);
+      if (can_issue) {
+        uint64_t* eb = &empty_a[issued % SA];
+        const uint32_t par = ((issued / SA) & 1) ^ 1;
+        if (issued == arrived) mbar_wait(eb, par);          // nothing in flight: block until a stage is free
+        else can_issue = mbar_test_wait(eb, par);           // otherwise poll, and retire landed stages meanwhile
+      }
+      if (can_issue) {
+        uint8_t* a_tile = a_ring + (issued % SA) * C::A_STAGE_BYTES;
+#pragma unroll
+        for (int j = 0; j < PER_THREAD; ++j) {
+          const int idx = j * C::PROD_THREADS + ptid;
+          const int kk = idx / (A_ROWS * 8), rem = idx - kk * (A_ROWS * 8);
+          const int r = rem >> 3, c = rem & 7;
+          if (idx < CHUNKS && r < rows) {
+            bool valid = true;
+            const void* src = aload.src(r, 0, ku * KG + kk, c, valid);
+            cp_async16(a_tile + kk * C::A_SUB_BYTES + sw128_offset(r, c), src, valid ? 16u : 0u);
+          }
+        }
+        cp_async_commit();
+        ++issued;
+        if (++ku == KBU) ku = 0;
+      } else {
+        switch (issued - arrived) {  // wait for the OLDEST pending group only
+          case 1: cp_async_wait<0>(); break;
+          case 2: cp_async_wait<1>(); break;
+          case 3: cp_async_wait<2>(); break;
+          default: cp_async_wait<3>(); break;
+        }
+        fence_proxy_async();
+        mbar_arrive(&full_a[arrived % SA]);
+        ++arrived;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps (row == TMEM lane)
+    pdl_wait_prior();  // residual input, workspace and tickets belong to the previous kernels until they are done
+    const int row = tid;
+    const bool row_valid = row < g.m_valid;
+    float4* ws = reinterpret_cast<float4*>(g.partial_ws);
+    int f = 0, u = u0;
+    while (u < u1) {
+      const int grp = u / KBU, ku_begin = u - grp * KBU;
+      const int ku_end = min(KBU, ku_begin + (u1 - u));
+      const int b = f & 1;
+      const bool complete = (ku_begin == 0 && ku_end == KBU);
+      const int slot = (u == u0) ? 0 : 1;  // a CTA has at most two partial fragments: its first and its last
+      float4* mine = ws + ((size_t)cta * 2 + slot) * TG * SK_PARTIAL_F4;
+      mbar_wait(&tmem_full[b], (f >> 1) & 1);
+      if (tid == 0 && f == 0) SK_STAMP(7);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * TG * SK_NT);
+      float acc[SK_NT];
+#pragma unroll
+      for (int j = 0; j < TG; ++j) {
+        tmem_ld32(taddr + j * SK_NT, acc);
+        tmem_ld32(taddr + j * SK_NT + 32, acc + 32);
+        tmem_ld_wait();
+        if (j == TG - 1) {
+          tc_fence_before();
+          mbar_arrive(&tmem_empty[b]);  // the issuer may start the next-but-one fragment into this accumulator set
+        }
+        if constexpr (sk_is_deferred<Epilogue>::value) {
+          epi.partial(row, row_valid, grp * TG + j, ku_begin / g.split_units, acc);
+        } else if (complete) {
+          epi(row, row_valid, 0, grp * TG + j, acc);
+        } else if (row_valid) {
+#pragma unroll
+          for (int c = 0; c < SK_NT / 4; ++c)
+            mine[(j * (SK_NT / 4) + c) * 128 + row] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+        }
+      }
+      if (!sk_is_deferred<Epilogue>::value && !complete) {
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int c_first = sk_owner(grp * KBU, units, G), c_last = sk_owner(grp * KBU + KBU - 1, units, G);
+        if (tid == 0) {
+          const int old = atomicAdd(&g.tickets[grp], 1);
+          s_is_last = (old == c_last - c_first);
+          if (s_is_last) g.tickets[grp] = 0;  // self-reset for the next launch / graph replay
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (s_is_last) {
+          __threadfence();
+#pragma unroll
+          for (int j = 0; j < TG; ++j) {
+            if (row_valid) {
+#pragma unroll
+              for (int c = 0; c < SK_NT; ++c) acc[c] = 0.f;
+              for (int cc = c_first; cc <= c_last; ++cc) {  // fixed order -> bitwise reproducible
+                const int sl = (sk_first_unit(cc, units, G) / KBU == grp) ? 0 : 1;
+                const float4* part = ws + (((size_t)cc * 2 + sl) * TG + j) * SK_PARTIAL_F4;
+#pragma unroll
+                for (int c = 0; c < SK_NT / 4; ++c) {
+                  const float4 v = __ldcg(&part[c * 128 + row]);
+                  acc[4 * c] += v.x, acc[4 * c + 1] += v.y, acc[4 * c + 2] += v.z, acc[4 * c + 3] += v.w;
+                }
+              }
+            }
+            if constexpr (!sk_is_deferred<Epilogue>::value) epi(row, row_valid, 0, grp * TG + j, acc);
+          }
+        }
+      }
+      u += ku_end - ku_begin;
+      ++f;
+    }
+    if (tid == 0) SK_STAMP(8);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (tid == 0) SK_STAMP(9);
+  if (warp == MMA_WARP) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ launch helpers
+template <int A_ROWS, int MODE, class ALoader, class Epilogue>
+cudaError_t launch_gemm_skinny_cfg(const SkinnyCore& g, const ALoader& al, const Epilogue& epi, int grid, cudaStream_t st) {
+  using C = SkinnyCfg<A_ROWS, MODE>;
+  auto kern = gemm_skinny_kernel<A_ROWS, MODE, ALoader, Epilogue>;
+  static bool configured = false;  // per template instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::DYN_BYTES);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  const int units = (g.n_tiles / C::TG) * (g.k_blocks / C::KG);
+  grid = grid < 1 ? 1 : (grid > units ? units : grid);
+  return launch_pdl(kern, dim3((unsigned)grid), dim3(C::THREADS), (size_t)C::DYN_BYTES, st, pdl_enabled(), g, al, epi);
+}
+
+// Mode the launcher picks for (rows, n_tiles, k_blocks); prefer_k1 forces 8 KB single-tile units at M > 32 (smaller
+// fix-up slots when a group is shared by several CTAs).
+inline int skinny_mode(int m, int n_tiles, int k_blocks, bool prefer_k1 = false) {
+  if (m <= 32) return (k_blocks % 2 == 0) ? MODE_K2 : MODE_K1;
+  return (n_tiles % 2 == 0 && !prefer_k1) ? MODE_T2 : MODE_K1;
+}
+inline int skinny_tg(int mode) { return mode == MODE_T2 ? 2 : 1; }
+inline int skinny_kg(int mode) { return mode == MODE_K2 ? 2 : 1; }
+
+// grid: number of CTAs wanted (clamped to the unit count).  Ticketed epilogues: ws must hold grid*2*tg 32 KB slots and
+// tickets n_tiles ints.  Deferred epilogues: grid must be n_groups * splits with splits | units-per-group.
+template <class ALoader, class Epilogue>
+cudaError_t launch_gemm_skinny(const SkinnyCore& g, const ALoader& al, const Epilogue& epi, int grid, cudaStream_t st,
+                               bool prefer_k1 = false) {
+  const int mode = skinny_mode(g.m_valid, g.n_tiles, g.k_blocks, prefer_k1);
+  if (g.m_valid <= 8)
+    return mode == MODE_K2 ? launch_gemm_skinny_cfg<8, MODE_K2>(g, al, epi, grid, st)
+                           : launch_gemm_skinny_cfg<8, MODE_K1>(g, al, epi, grid, st);
+  if (g.m_valid <= 32)
+    return mode == MODE_K2 ? launch_gemm_skinny_cfg<32, MODE_K2>(g, al, epi, grid, st)
+                           : launch_gemm_skinny_cfg<32, MODE_K1>(g, al, epi, grid, st);
+  return mode == MODE_T2 ? launch_gemm_skinny_cfg<128, MODE_T2>(g, al, epi, grid, st)
+                         : launch_gemm_skinny_cfg<128, MODE_K1>(g, al, epi, grid, st);
+}
+
+}  // namespace zb

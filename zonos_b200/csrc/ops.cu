@@ -2,6 +2,7 @@
 #include "../../include/zonos_b200.h"
 #include "common.cuh"
 #include "epilogues.cuh"
+#include "gemm_skinny.cuh"
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 
@@ -12,6 +13,8 @@ namespace zb {
 template <int MAX_VEC>
 __global__ void layernorm_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* __restrict__ b,
                                  bf16* __restrict__ out, int rows, int d, float eps, int in_row_mul, int in_row_add) {
+  pdl_launch_dependents();
+  pdl_wait_prior();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows) return;
   const int nvec = d / 256;  // uint4 (8 bf16) per lane
@@ -62,11 +65,98 @@ cudaError_t launch_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* 
                              int in_row_mul, int in_row_add, cudaStream_t st) {
   const int warps_per_block = 4;
   const int blocks = ceil_div(rows, warps_per_block);
+  const dim3 grid(blocks), block(warps_per_block * 32);
   if (d <= 2048)
-    layernorm_kernel<8><<<blocks, warps_per_block * 32, 0, st>>>(x, w, b, out, rows, d, eps, in_row_mul, in_row_add);
-  else
-    layernorm_kernel<16><<<blocks, warps_per_block * 32, 0, st>>>(x, w, b, out, rows, d, eps, in_row_mul, in_row_add);
-  return cudaGetLastError();
+    return launch_pdl(layernorm_kernel<8>, grid, block, 0, st, pdl_enabled(), x, w, b, out, rows, d, eps, in_row_mul, in_row_add);
+  return launch_pdl(layernorm_kernel<16>, grid, block, 0, st, pdl_enabled(), x, w, b, out, rows, d, eps, in_row_mul, in_row_add);
+}
+
+// ------------------------------------------------------------------------------------------------ residual + LayerNorm
+// Consumer of a deferred split-K GEMM (EpiPartial): one CTA per row,
+//   o = bf16(sum_s ws[s][row][:])  (splits added in order, fp32)      -- the nn.Linear output, rounded like the reference
+//   x = bf16(x + o)                                                  -- residual add (_torch.py:100-101)
+//   xn = LayerNorm(x) * w + b                                        -- the NEXT norm (norm2, next layer's norm, or norm_f)
+// which replaces the separate residual epilogue + LayerNorm kernel pair by one pass over the row.
+constexpr int RLN_THREADS = 256;
+__global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict__ x, const float* __restrict__ ws, int splits,
+                                                               int rows, const bf16* __restrict__ w, const bf16* __restrict__ b,
+                                                               bf16* __restrict__ xn, int d, float eps) {
+  pdl_launch_dependents();
+  pdl_wait_prior();
+  __shared__ float red[RLN_THREADS / 32];
+  __shared__ float bcast;
+  const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int MAXV = 2;  // d <= 4096
+  float v[MAXV][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int col = (i * RLN_THREADS + tid) * 8;
+    if (col < d) {
+      float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int s = 0; s < splits; ++s) {
+        const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)s * rows + row) * d + col);
+        const float4 a = __ldcg(p), c = __ldcg(p + 1);
+        o[0] += a.x, o[1] += a.y, o[2] += a.z, o[3] += a.w, o[4] += c.x, o[5] += c.y, o[6] += c.z, o[7] += c.w;
+      }
+      const uint4 xu = *reinterpret_cast<const uint4*>(x + (size_t)row * d + col);
+      const float2 x0 = unpack_bf16x2(xu.x), x1 = unpack_bf16x2(xu.y), x2 = unpack_bf16x2(xu.z), x3 = unpack_bf16x2(xu.w);
+      const float xin[8] = {x0.x, x0.y, x1.x, x1.y, x2.x, x2.y, x3.x, x3.y};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[i][j] = bf16_round(xin[j] + bf16_round(o[j]));
+        sum += v[i][j];
+      }
+      *reinterpret_cast<uint4*>(x + (size_t)row * d + col) =
+          make_uint4(pack_bf16x2(v[i][0], v[i][1]), pack_bf16x2(v[i][2], v[i][3]), pack_bf16x2(v[i][4], v[i][5]),
+                     pack_bf16x2(v[i][6], v[i][7]));
+    }
+  }
+  auto block_sum = [&](float t) {
+    t = warp_sum(t);
+    __syncthreads();
+    if (lane == 0) red[warp] = t;
+    __syncthreads();
+    if (tid == 0) {
+      float a = 0.f;
+#pragma unroll
+      for (int k = 0; k < RLN_THREADS / 32; ++k) a += red[k];
+      bcast = a;
+    }
+    __syncthreads();
+    return bcast;
+  };
+  const float mean = block_sum(sum) / (float)d;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i)
+    if ((i * RLN_THREADS + tid) * 8 < d)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float t = v[i][j] - mean;
+        sq += t * t;
+      }
+  const float rstd = 1.0f / sqrtf(block_sum(sq) / (float)d + eps);
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int col = (i * RLN_THREADS + tid) * 8;
+    if (col < d) {
+      const uint4 wu = __ldg(reinterpret_cast<const uint4*>(w + col)), bu = __ldg(reinterpret_cast<const uint4*>(b + col));
+      const uint32_t wv[4] = {wu.x, wu.y, wu.z, wu.w}, bv[4] = {bu.x, bu.y, bu.z, bu.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 ww = unpack_bf16x2(wv[j]), bb = unpack_bf16x2(bv[j]);
+        o[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * ww.x + bb.x, (v[i][2 * j + 1] - mean) * rstd * ww.y + bb.y);
+      }
+      *reinterpret_cast<uint4*>(xn + (size_t)row * d + col) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+cudaError_t launch_resid_ln(bf16* x, const float* ws, int splits, int rows, const bf16* w, const bf16* b, bf16* xn, int d,
+                            float eps, cudaStream_t st) {
+  return launch_pdl(resid_ln_kernel, dim3(rows), dim3(RLN_THREADS), 0, st, pdl_enabled(), x, ws, splits, rows, w, b, xn, d, eps);
 }
 
 // ------------------------------------------------------------------------------------------------ embedding sum
@@ -75,6 +165,8 @@ cudaError_t launch_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* 
 __global__ void embed_sum_kernel(const int32_t* __restrict__ ids, int ids_stride_b, int ids_stride_q, const int* col_ptr,
                                  int col_add, const bf16* __restrict__ emb, bf16* __restrict__ out, int n_q, int vocab,
                                  int d, int out_stride_b, int out_off, int dup_off) {
+  pdl_launch_dependents();
+  pdl_wait_prior();
   const int s = blockIdx.x, b = blockIdx.y;
   const int col = (col_ptr ? *col_ptr : 0) + col_add + s;
   __shared__ int sid[ZB200_MAX_CODEBOOKS];
@@ -107,9 +199,8 @@ cudaError_t launch_embed_sum(const int32_t* ids, int ids_stride_b, int ids_strid
                              int n_cols, const bf16* emb, bf16* out, int batch, int n_q, int vocab, int d,
                              int out_stride_b, int out_off, int dup_off, cudaStream_t st) {
   dim3 grid(n_cols, batch);
-  embed_sum_kernel<<<grid, 256, 0, st>>>(ids, ids_stride_b, ids_stride_q, col_ptr, col_add, emb, out, n_q, vocab, d,
-                                         out_stride_b, out_off, dup_off);
-  return cudaGetLastError();
+  return launch_pdl(embed_sum_kernel, grid, dim3(256), 0, st, pdl_enabled(), ids, ids_stride_b, ids_stride_q, col_ptr,
+                    col_add, emb, out, n_q, vocab, d, out_stride_b, out_off, dup_off);
 }
 
 }  // namespace zb
@@ -153,5 +244,63 @@ extern "C" int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_pack
   ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
   EpiStoreBf16<NT> epi{(bf16*)out, ldo, n};
   ZB_CHECK_CUDA((launch_gemm_tc<NT, 6, 1>(g, al, epi, ceil_div(n, NT), ceil_div(m, GEMM_BM), (cudaStream_t)stream)));
+  return ZB200_OK;
+}
+
+static unsigned long long* g_trace_buf = nullptr;
+static int g_trace_next = 0;
+/* debug: device buffer [64][160][12] uint64 receiving the in-kernel globaltimer timeline of the next
+ * zb200_gemm_skinny_bf16 launches (libraries built with ZB200_TRACE=1); returns launches traced so far and resets. */
+extern "C" int zb200_debug_trace(unsigned long long* device_buf) {
+  const int n = g_trace_next;
+  g_trace_buf = device_buf;
+  g_trace_next = 0;
+#ifdef SK_TRACE
+  return n;
+#else
+  (void)n;
+  set_error("debug_trace: library built without ZB200_TRACE=1");
+  return ZB200_ERR_STATE;
+#endif
+}
+
+extern "C" int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out,
+                                      int ldo, int grid, float* ws, int64_t ws_floats, int* tickets, int n_tickets,
+                                      void* stream) {
+  ZB_REQUIRE(m > 0 && m <= GEMM_BM && n > 0 && k > 0 && k % 64 == 0 && lda % 8 == 0,
+             "gemm_skinny: bad shape m=%d n=%d k=%d lda=%d (m <= 128)", m, n, k, lda);
+  const int n_tiles = ceil_div(n, SK_NT);
+  ZB_REQUIRE(grid >= 1 && grid <= 1024, "gemm_skinny: grid=%d out of range", grid);
+  ZB_REQUIRE(ws && tickets && ws_floats >= (int64_t)grid * 2 * skinny_tg(skinny_mode(m, n_tiles, k / 64)) * SK_PARTIAL_F4 * 4 && n_tickets >= n_tiles,
+             "gemm_skinny: workspace too small (needs grid*2*tg*32 KB and n_tiles tickets)");
+  SkinnyCore g{};
+  g.Wp = w_packed, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = m, g.partial_ws = ws, g.tickets = tickets;
+  g.split_units = 0;
+  g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
+  ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
+  EpiStoreBf16<SK_NT> epi{(bf16*)out, ldo, n};
+  ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, grid, (cudaStream_t)stream));
+  return ZB200_OK;
+}
+
+/* x <- bf16(x + bf16(a * w^T)); xn <- LayerNorm(x) * ln_w + ln_b: the out_proj / fc2 + residual + next-norm group of the
+ * decode step as the engine runs it (deferred split-K GEMM -> resid_ln_kernel).  ws: >= splits*m*n floats. */
+extern "C" int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_packed, int n, int k, int splits, float* ws,
+                                   int64_t ws_floats, void* x, const void* ln_w, const void* ln_b, void* xn, float eps,
+                                   void* stream) {
+  ZB_REQUIRE(m > 0 && m <= GEMM_BM && n > 0 && n % 256 == 0 && n <= 4096 && k > 0 && k % 64 == 0 && lda % 8 == 0,
+             "gemm_resid_ln: bad shape m=%d n=%d k=%d lda=%d", m, n, k, lda);
+  const int n_tiles = n / SK_NT, mode = skinny_mode(m, n_tiles, k / 64);
+  const int n_groups = n_tiles / skinny_tg(mode), kbu = (k / 64) / skinny_kg(mode);
+  ZB_REQUIRE(splits >= 1 && kbu % splits == 0, "gemm_resid_ln: splits=%d must divide the %d units of a group", splits, kbu);
+  ZB_REQUIRE(ws && ws_floats >= (int64_t)splits * m * n, "gemm_resid_ln: workspace too small");
+  SkinnyCore g{};
+  g.Wp = w_packed, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = m, g.partial_ws = nullptr, g.tickets = nullptr;
+  g.split_units = kbu / splits, g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
+  ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
+  EpiPartial epi{ws, m, n};
+  ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, n_groups * splits, (cudaStream_t)stream));
+  ZB_CHECK_CUDA(launch_resid_ln((bf16*)x, ws, splits, m, (const bf16*)ln_w, (const bf16*)ln_b, (bf16*)xn, n, eps,
+                                (cudaStream_t)stream));
   return ZB200_OK;
 }

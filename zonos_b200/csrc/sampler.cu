@@ -306,6 +306,8 @@ __global__ void __launch_bounds__(SMP_THREADS) sampler_kernel(SamplerArgs a, int
   __shared__ float red[32];
   __shared__ int redi[32];
   __shared__ int s_last;
+  pdl_launch_dependents();
+  pdl_wait_prior();
   const int q = blockIdx.x, b = blockIdx.y;
   if (a.loop_mode && a.state[ST_DONE]) return;  // steps launched past the end of the loop are no-ops
   const int offset = a.loop_mode ? a.state[ST_OFFSET] : a.first_offset;
@@ -338,8 +340,7 @@ __global__ void __launch_bounds__(SMP_THREADS) sampler_kernel(SamplerArgs a, int
 
 cudaError_t launch_sampler(const SamplerArgs& a, int pass, cudaStream_t st) {
   dim3 grid(a.n_q, a.batch);
-  sampler_kernel<<<grid, SMP_THREADS, 0, st>>>(a, pass);
-  return cudaGetLastError();
+  return launch_pdl(sampler_kernel, grid, dim3(SMP_THREADS), 0, st, pdl_enabled(), a, pass);
 }
 
 }  // namespace zb

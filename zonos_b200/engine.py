@@ -92,7 +92,7 @@ class Engine:
         self.att = torch.empty(rows, H * 128, **bf)
         self.h = torch.empty(rows, pw.d_ff, **bf)
         self.logits = torch.empty(batch, self.pw.emb.shape[0], pw.vocab, dtype=torch.float32, device=dev)
-        self.gemm_ws = torch.empty(512 * 64 * 128, dtype=torch.float32, device=dev)
+        self.gemm_ws = torch.empty(160 * 32768, dtype=torch.float32, device=dev)  # 160 CTAs x 2 slots x 2 sub-tiles x 32 KB
         self.gemm_tickets = torch.zeros(1024, dtype=torch.int32, device=dev)
         if attn_nsplit is None:  # enough CTAs for ~2 waves of 2 CTAs/SM
             attn_nsplit = max(1, min(16, math.ceil(2 * 148 * 2 / (B2 * Hkv)), self.kv.pages_per_seq))

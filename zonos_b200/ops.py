@@ -70,6 +70,36 @@ def gemm_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, splits: int = 1) 
     return out
 
 
+def gemm_skinny_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, grid: int = 148, ws=None, tickets=None) -> torch.Tensor:
+    """Test hook: bf16 [M<=128,K] x packed [N,K]^T -> bf16 [M,N] through the weight-streaming stream-K kernel."""
+    a = _cuda(a, torch.bfloat16)
+    M, K = a.shape
+    n_tiles = (n + 63) // 64
+    grid = max(1, min(grid, 1024))
+    out = torch.empty(M, n, dtype=torch.bfloat16, device=a.device)
+    if ws is None:
+        ws = torch.empty(grid * 32768, dtype=torch.float32, device=a.device)
+    if tickets is None:
+        tickets = torch.zeros(n_tiles, dtype=torch.int32, device=a.device)
+    check(lib().zb200_gemm_skinny_bf16(ptr(a), M, K, ptr(w_packed), n, K, ptr(out), n, grid, ptr(ws),
+                                       ctypes.c_int64(ws.numel()), ptr(tickets), tickets.numel(), stream_ptr()),
+          "gemm_skinny_bf16")
+    return out
+
+
+def gemm_resid_ln(a, w_packed, x, ln_w, ln_b, splits: int = 4, eps: float = 1e-5):
+    """Test hook: returns (bf16(x + bf16(a @ w^T)), LayerNorm of that) through the deferred split-K GEMM + resid_ln kernel."""
+    a, x = _cuda(a, torch.bfloat16), _cuda(x, torch.bfloat16).clone()
+    M, K = a.shape
+    n = x.shape[1]
+    ws = torch.full((splits * M * n,), float("nan"), dtype=torch.float32, device=a.device)
+    xn = torch.empty_like(x)
+    check(lib().zb200_gemm_resid_ln(ptr(a), M, K, ptr(w_packed), n, K, splits, ptr(ws), ctypes.c_int64(ws.numel()), ptr(x),
+                                    ptr(_cuda(ln_w, torch.bfloat16)), ptr(_cuda(ln_b, torch.bfloat16)), ptr(xn),
+                                    ctypes.c_float(eps), stream_ptr()), "gemm_resid_ln")
+    return x, xn
+
+
 def layernorm(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
     x = _cuda(x, torch.bfloat16)
     d = x.shape[-1]
