@@ -90,7 +90,8 @@ SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
       }
     p.grid = cap;  // unaligned stream-K: most groups end up with two contributors
   } else {
-    const int s = std::max(1, std::min(3, cap / groups));
+    static const int max_split = getenv("ZB200_SK_MAXSPLIT") ? atoi(getenv("ZB200_SK_MAXSPLIT")) : 3;
+    const int s = std::max(1, std::min(max_split, cap / groups));
     p.grid = groups * s;
   }
   return p;

@@ -80,9 +80,9 @@ struct SkinnyCfg {
   static constexpr int A_SUB_BYTES = A_ROWS * 128;
   static constexpr int A_STAGE_BYTES = KG * A_SUB_BYTES;
   static constexpr int W_STAGE_BYTES = TG * KG * SK_TILE_BYTES;
-  static constexpr int SA = 4;
+  static constexpr int SA = (A_ROWS <= 8) ? 8 : 4;
   static constexpr int SW = (A_ROWS >= 128) ? (128 * 1024 / W_STAGE_BYTES)
-                                            : ((A_ROWS > 8 ? 64 : 96) * 1024 / W_STAGE_BYTES);
+                                            : ((A_ROWS > 8 ? 64 : 80) * 1024 / W_STAGE_BYTES);
   static constexpr int A_BYTES = SA * A_STAGE_BYTES;
   static constexpr int W_BYTES = SW * W_STAGE_BYTES;
   static constexpr int BAR_OFFSET = A_BYTES + W_BYTES;
@@ -235,13 +235,11 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
     const int rows = min(g.m_valid, A_ROWS);
     constexpr int CHUNKS = KG * A_ROWS * 8;  // 16-byte chunks per stage
     constexpr int PER_THREAD = (CHUNKS + C::PROD_THREADS - 1) / C::PROD_THREADS;
-    constexpr int MAXPEND = 4;
-    static_assert(MAXPEND <= SA, "pending cp.async groups must fit the ring");
+    constexpr int MAXPEND = (SA < 8) ? SA : 8;
     int issued = 0, arrived = 0;
     int ku = u0 % KBU;
     while (arrived < n_units) {
-      // ramp: the first stage is retired as soon as it lands, then up to MAXPEND loads stay in flight
-      bool can_issue = issued < n_units && (issued - arrived) < min(MAXPEND, arrived + 1);
+      bool can_issue = issued < n_units && (issued - arrived) < MAXPEND;
       if (can_issue) {
         uint64_t* eb = &empty_a[issued % SA];
         const uint32_t par = ((issued / SA) & 1) ^ 1;
@@ -269,7 +267,11 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           case 1: cp_async_wait<0>(); break;
           case 2: cp_async_wait<1>(); break;
           case 3: cp_async_wait<2>(); break;
-          default: cp_async_wait<3>(); break;
+          case 4: cp_async_wait<3>(); break;
+          case 5: cp_async_wait<4>(); break;
+          case 6: cp_async_wait<5>(); break;
+          case 7: cp_async_wait<6>(); break;
+          default: cp_async_wait<7>(); break;
         }
         fence_proxy_async();
         mbar_arrive(&full_a[arrived % SA]);

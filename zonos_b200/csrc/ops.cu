@@ -6,6 +6,9 @@
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 
+static unsigned long long* g_trace_buf = nullptr;  // debug timeline (zb200_debug_trace)
+static int g_trace_next = 0;
+
 namespace zb {
 
 // ------------------------------------------------------------------------------------------------ LayerNorm
@@ -80,9 +83,16 @@ cudaError_t launch_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* 
 constexpr int RLN_THREADS = 256;
 __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict__ x, const float* __restrict__ ws, int splits,
                                                                int rows, const bf16* __restrict__ w, const bf16* __restrict__ b,
-                                                               bf16* __restrict__ xn, int d, float eps) {
+                                                               bf16* __restrict__ xn, int d, float eps,
+                                                               unsigned long long* trace, int trace_id) {
   pdl_launch_dependents();
+#ifdef SK_TRACE
+  if (threadIdx.x == 0) sk_stamp(trace, trace_id, 0);
+#endif
   pdl_wait_prior();
+#ifdef SK_TRACE
+  if (threadIdx.x == 0) sk_stamp(trace, trace_id, 4);
+#endif
   __shared__ float red[RLN_THREADS / 32];
   __shared__ float bcast;
   const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -94,10 +104,20 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
     const int col = (i * RLN_THREADS + tid) * 8;
     if (col < d) {
       float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int s = 0; s < splits; ++s) {
-        const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)s * rows + row) * d + col);
-        const float4 a = __ldcg(p), c = __ldcg(p + 1);
-        o[0] += a.x, o[1] += a.y, o[2] += a.z, o[3] += a.w, o[4] += c.x, o[5] += c.y, o[6] += c.z, o[7] += c.w;
+      for (int s0 = 0; s0 < splits; s0 += 8) {  // 16 independent loads in flight, added in split order
+        float4 a[8], c[8];
+#pragma unroll
+        for (int s = 0; s < 8; ++s)
+          if (s0 + s < splits) {
+            const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)(s0 + s) * rows + row) * d + col);
+            a[s] = __ldcg(p), c[s] = __ldcg(p + 1);
+          }
+#pragma unroll
+        for (int s = 0; s < 8; ++s)
+          if (s0 + s < splits) {
+            o[0] += a[s].x, o[1] += a[s].y, o[2] += a[s].z, o[3] += a[s].w;
+            o[4] += c[s].x, o[5] += c[s].y, o[6] += c[s].z, o[7] += c[s].w;
+          }
       }
       const uint4 xu = *reinterpret_cast<const uint4*>(x + (size_t)row * d + col);
       const float2 x0 = unpack_bf16x2(xu.x), x1 = unpack_bf16x2(xu.y), x2 = unpack_bf16x2(xu.z), x3 = unpack_bf16x2(xu.w);
@@ -112,6 +132,9 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
                      pack_bf16x2(v[i][6], v[i][7]));
     }
   }
+#ifdef SK_TRACE
+  if (threadIdx.x == 0) sk_stamp(trace, trace_id, 5);
+#endif
   auto block_sum = [&](float t) {
     t = warp_sum(t);
     __syncthreads();
@@ -152,11 +175,16 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
       *reinterpret_cast<uint4*>(xn + (size_t)row * d + col) = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
+#ifdef SK_TRACE
+  __syncthreads();
+  if (threadIdx.x == 0) sk_stamp(trace, trace_id, 9);
+#endif
 }
 
 cudaError_t launch_resid_ln(bf16* x, const float* ws, int splits, int rows, const bf16* w, const bf16* b, bf16* xn, int d,
-                            float eps, cudaStream_t st) {
-  return launch_pdl(resid_ln_kernel, dim3(rows), dim3(RLN_THREADS), 0, st, pdl_enabled(), x, ws, splits, rows, w, b, xn, d, eps);
+                            float eps, cudaStream_t st, unsigned long long* trace, int trace_id) {
+  return launch_pdl(resid_ln_kernel, dim3(rows), dim3(RLN_THREADS), 0, st, pdl_enabled(), x, ws, splits, rows, w, b, xn, d, eps,
+                    trace, trace_id);
 }
 
 // ------------------------------------------------------------------------------------------------ embedding sum
@@ -247,8 +275,6 @@ extern "C" int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_pack
   return ZB200_OK;
 }
 
-static unsigned long long* g_trace_buf = nullptr;
-static int g_trace_next = 0;
 /* debug: device buffer [64][160][12] uint64 receiving the in-kernel globaltimer timeline of the next
  * zb200_gemm_skinny_bf16 launches (libraries built with ZB200_TRACE=1); returns launches traced so far and resets. */
 extern "C" int zb200_debug_trace(unsigned long long* device_buf) {
@@ -300,7 +326,8 @@ extern "C" int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_
   ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
   EpiPartial epi{ws, m, n};
   ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, n_groups * splits, (cudaStream_t)stream));
+  const int rln_id = g_trace_buf ? g_trace_next++ : -1;
   ZB_CHECK_CUDA(launch_resid_ln((bf16*)x, ws, splits, m, (const bf16*)ln_w, (const bf16*)ln_b, (bf16*)xn, n, eps,
-                                (cudaStream_t)stream));
+                                (cudaStream_t)stream, g_trace_buf, rln_id));
   return ZB200_OK;
 }
