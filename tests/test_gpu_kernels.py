@@ -30,7 +30,8 @@ def test_delay_pattern_full_size_roundtrip(ops):
 
 
 @pytest.mark.parametrize("M,N,K,splits", [(2, 64, 64, 1), (2, 192, 512, 1), (128, 3072, 2048, 1), (128, 2048, 2048, 4),
-                                          (7, 1026, 512, 1), (130, 256, 8192, 8), (300, 512, 1024, 3), (2, 2048, 8192, 16)])
+                                          (7, 1026, 512, 1), (130, 256, 8192, 8), (300, 512, 1024, 3), (2, 2048, 8192, 16),
+                                          (300, 512, 1024, 1), (700, 1026, 512, 1), (260, 384, 1024, 1), (1000, 3072, 2048, 1)])
 def test_gemm_tcgen05(ops, M, N, K, splits):
     g = torch.Generator(device="cuda").manual_seed(M * 7 + N)
     a = torch.randn(M, K, device="cuda", generator=g).bfloat16()

@@ -56,6 +56,14 @@ struct EpiDac {
   __device__ void operator()(int row, bool valid, int m_tile, int n_tile, float* acc) const {
     if (!valid) return;
     const int b = m_tile / tiles_per_seq, j = (m_tile - b * tiles_per_seq) * GEMM_BM + row;
+    // residual rows are streamed from HBM: issue all of this row's loads before anything depends on them
+    uint4 rbuf[NT / 8];
+    if (resid && up == 0 && j < T_out) {
+      const f16* rrow = resid + ((size_t)b * T_out + j) * pitch_out + n_tile * NT;
+#pragma unroll
+      for (int c = 0; c < NT; c += 8)
+        if (n_tile * NT + c < n_total) rbuf[c / 8] = __ldcs(reinterpret_cast<const uint4*>(rrow + c));
+    }
 #pragma unroll
     for (int c = 0; c < NT; c += 8) {
       const int n = n_tile * NT + c;
@@ -72,7 +80,7 @@ struct EpiDac {
 #pragma unroll
       for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[c + i] + __ldg(bias + n + i)));
       if (resid) {
-        const uint4 ru = *reinterpret_cast<const uint4*>(resid + off);
+        const uint4 ru = (up == 0) ? rbuf[c / 8] : *reinterpret_cast<const uint4*>(resid + off);
         const __half2* rh = reinterpret_cast<const __half2*>(&ru);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -190,7 +198,7 @@ static cudaError_t launch_dac_layer(const zb200_dac_layer& L, int batch, int T, 
         if (e != cudaSuccess) return e;
       }
   }
-  return launch_gemm_tc<NT, 4, 0>(g, al, epi, ceil_div(n_total, NT), batch * tiles_per_seq, st);
+  return launch_gemm_tc<NT, 4, 0, 2>(g, al, epi, ceil_div(n_total, NT), batch * tiles_per_seq, st);
 }
 
 extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, int batch, int t, void* const* regions,

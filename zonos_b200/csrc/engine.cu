@@ -21,9 +21,26 @@ struct zb200_engine {
   cudaGraphExec_t exec = nullptr;
   int launches = 0;  // kernels launched by the last step
   int sk_sms = 0;    // SMs the weight-streaming GEMM plans for (0: tiled kernel only)
+  // L2 weight prefetch: a side stream (forked / joined inside the captured step) runs ahead of the GEMM chain
+  int l2_prefetch = 0;
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool forked = false;
 };
 
 namespace {
+
+// Asks the L2 to fetch [base, base+bytes) from HBM (TMA-engine bulk prefetch, no shared memory, no registers held):
+// the weights of the NEXT GEMM of the step travel HBM -> L2 while the current kernels run their dependent chains.
+__global__ void l2_prefetch_kernel(const uint8_t* base, long long bytes) {
+  constexpr long long CHUNK = 16384;
+  const long long n = (bytes + CHUNK - 1) / CHUNK;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long off = i * CHUNK;
+    const unsigned sz = (unsigned)((bytes - off < CHUNK ? bytes - off : CHUNK) & ~15LL);
+    if (sz) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + off), "r"(sz) : "memory");
+  }
+}
 
 constexpr int NT = 64;
 constexpr int STAGES = 6;
@@ -133,6 +150,30 @@ cudaError_t gemm_any(const zb200_engine* e, const void* w, int n_tiles, int rows
     ++e->launches;                                           \
   } while (0)
 
+// Forks the side stream off `st` (everything launched on `st` so far is a dependency) and queues an L2 prefetch on it.
+int prefetch_l2(zb200_engine* e, const void* w, int64_t bytes, cudaStream_t st) {
+  if (!e->l2_prefetch || bytes <= 0) return ZB200_OK;
+  ZB_CHECK_CUDA(cudaEventRecord(e->ev_fork, st));
+  ZB_CHECK_CUDA(cudaStreamWaitEvent(e->side, e->ev_fork, 0));
+  l2_prefetch_kernel<<<16, 128, 0, e->side>>>((const uint8_t*)w, (long long)bytes);
+  ZB_CHECK_LAUNCH("l2_prefetch_kernel");
+  ++e->launches;
+  e->forked = true;
+  return ZB200_OK;
+}
+int join_side(zb200_engine* e, cudaStream_t st) {
+  if (!e->forked) return ZB200_OK;
+  ZB_CHECK_CUDA(cudaEventRecord(e->ev_join, e->side));
+  ZB_CHECK_CUDA(cudaStreamWaitEvent(st, e->ev_join, 0));
+  e->forked = false;
+  return ZB200_OK;
+}
+#define ZB_TRY_RC(expr)            \
+  do {                             \
+    const int _rc = (expr);        \
+    if (_rc != ZB200_OK) return _rc; \
+  } while (0)
+
 // Decode step with rows = 2B <= 128: every projection streams its weights through gemm_skinny; out_proj and fc2 leave
 // their split-K partial sums to the fused residual + LayerNorm kernel, which also produces the next GEMM's input.
 int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
@@ -146,6 +187,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
   ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w, (const bf16*)d.ln1_b, xn, rows, dm, d.ln_eps, 1, 0, st));
   for (int l = 0; l < d.n_layer; ++l) {
     {  // in_proj + RoPE + KV page write
+      ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, d.out_stride, st));
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
       EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, 1, d.n_heads};
       ZB_TRY(gemm_any(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
@@ -158,6 +200,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       ZB_TRY(launch_attn_decode(a, n_seq, d.attn_nsplit, st));
     }
     {  // out_proj (split-K partials) -> residual + norm2
+      ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.fc1_stride, st));
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, dm / NT, rows, hd);
       g.split_units = (hd / 64) / skinny_kg(skinny_mode(rows, dm / NT, hd / 64)) / p_out.splits;
       ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
@@ -167,11 +210,16 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
                              (const bf16*)d.ln2_b + (size_t)l * dm, xn, dm, d.ln_eps, st));
     }
     {  // fc1 + SiLU gate
+      ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, d.fc2_stride, st));
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
       EpiSwiGLU<NT> epi{h, d.d_ff};
       ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
     }
     {  // fc2 (split-K partials) -> residual + the next layer's norm (norm_f after the last layer)
+      if (l + 1 < d.n_layer)
+        ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_qkv + (size_t)(l + 1) * d.qkv_stride, d.qkv_stride, st));
+      else
+        ZB_TRY_RC(prefetch_l2(e, d.w_heads, (int64_t)d.n_q * d.head_rows_padded * dm * 2, st));
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, dm / NT, rows, d.d_ff);
       g.split_units = (d.d_ff / 64) / skinny_kg(skinny_mode(rows, dm / NT, d.d_ff / 64)) / p_fc2.splits;
       ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
@@ -184,12 +232,13 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
     }
   }
   {  // heads + CFG on the normalised rows (model.py:110-115)
+    ZB_TRY_RC(prefetch_l2(e, d.w_qkv, d.qkv_stride, st));  // the next frame starts with layer 0's in_proj
     const int tiles_per_head = d.head_rows_padded / NT;
     ARowCfgPairs al{(const uint8_t*)xn, (size_t)dm * 2, d.batch};
     EpiHeadsCfg<NT> epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
     ZB_TRY(gemm_any(e, d.w_heads, d.n_q * tiles_per_head, n_seq, dm, al, epi, st));
   }
-  return ZB200_OK;
+  return join_side(e, st);
 }
 
 // All transformer layers on `rows` rows of x (seq_len positions per sequence), then norm_f + heads + CFG.
@@ -289,6 +338,16 @@ extern "C" int zb200_engine_create(const zb200_engine_desc* desc, zb200_engine**
     // fix-up workspace per SM: two CTAs x two slots x one 32 KB sub-tile (M <= 32) or one CTA x two slots x two sub-tiles
     const int64_t cap = desc->gemm_ws_floats / (4 * SK_PARTIAL_F4 * 4);
     e->sk_sms = (int)std::max<int64_t>(0, std::min<int64_t>(sms, cap));
+    if (const char* v = getenv("ZB200_L2_PREFETCH")) e->l2_prefetch = atoi(v);
+    if (e->l2_prefetch) {
+      cudaError_t ce = cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking);
+      if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
+      if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming);
+      if (ce != cudaSuccess) {
+        zb200_engine_destroy(e);
+        return cuda_fail(ce, "engine_create: side stream");
+      }
+    }
   }
   *out = e;
   return ZB200_OK;
@@ -298,6 +357,9 @@ extern "C" void zb200_engine_destroy(zb200_engine* e) {
   if (!e) return;
   if (e->exec) cudaGraphExecDestroy(e->exec);
   if (e->graph) cudaGraphDestroy(e->graph);
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  if (e->ev_join) cudaEventDestroy(e->ev_join);
+  if (e->side) cudaStreamDestroy(e->side);
   delete e;
 }
 
