@@ -53,6 +53,10 @@ int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_packed, int n, 
  * on `grid` CTAs.  ws: >= grid * 32768 floats, tickets: >= ceil(n/64) zeroed ints. */
 int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int grid,
                            float* ws, int64_t ws_floats, int* tickets, int n_tickets, void* stream);
+/* Same contract for m <= 8 rows through the operand-swapped weight-streaming kernel (csrc/gemm_swap.cuh: weights are the
+ * 128-row UMMA operand).  k % 128 == 0; ws: >= grid * 2048 floats, tickets: >= ceil(n/128) zeroed ints. */
+int zb200_gemm_swap_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int grid,
+                         float* ws, int64_t ws_floats, int* tickets, int n_tickets, void* stream);
 /* The out_proj / fc2 + residual + next LayerNorm group of the decode step (_torch.py:99-102): x <- bf16(x + bf16(a w^T)),
  * xn <- LayerNorm(x) * ln_w + ln_b, as a split-K weight-streaming GEMM whose partial sums are reduced by the fused
  * residual + LayerNorm kernel.  m <= 128, n % 256 == 0 (<= 4096); ws: >= splits*m*n floats. */

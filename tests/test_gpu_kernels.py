@@ -70,6 +70,25 @@ def test_gemm_skinny_stream_k(ops, M, N, K, grid):
     assert torch.equal(out, out2)
 
 
+@pytest.mark.parametrize("M,N,K,grid", [(2, 128, 128, 1), (2, 3072, 2048, 192), (2, 2048, 2048, 128), (2, 16384, 2048, 256),
+                                        (2, 2048, 8192, 128), (8, 9792, 2048, 231), (6, 1026, 512, 20), (1, 192, 1024, 7),
+                                        (4, 2048, 8192, 296), (2, 512, 512, 16), (5, 64, 256, 2)])
+def test_gemm_swap_stream_k(ops, M, N, K, grid):
+    """Operand-swapped weight-streaming kernel (M <= 8): aligned and unaligned partitions, up to 16 contributors per
+    group, odd tile counts (half-empty last group), N not a multiple of 64."""
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N + grid)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    wp = ops.pack_weight(w)
+    out = ops.gemm_swap_bf16(a, wp, N, grid=grid)
+    ref = (a.float() @ w.float().t())
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2 * max(1.0, ref.abs().max().item()), err
+    for _ in range(3):
+        out2 = ops.gemm_swap_bf16(a, wp, N, grid=grid)
+    assert torch.equal(out, out2)
+
+
 @pytest.mark.parametrize("M,N,K,splits", [(2, 2048, 2048, 8), (2, 2048, 8192, 8), (128, 2048, 2048, 8), (128, 2048, 8192, 8),
                                           (6, 512, 512, 2), (20, 512, 1024, 1), (64, 1024, 2048, 4)])
 def test_gemm_resid_ln(ops, M, N, K, splits):

@@ -5,7 +5,9 @@
 #include "attention.cuh"
 #include "common.cuh"
 #include "epilogues.cuh"
+#include "epilogues_t.cuh"
 #include "gemm_skinny.cuh"
+#include "gemm_swap.cuh"
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 #include "sampler.cuh"
@@ -174,6 +176,17 @@ int join_side(zb200_engine* e, cudaStream_t st) {
     if (_rc != ZB200_OK) return _rc; \
   } while (0)
 
+template <class ALoader, class Epilogue>
+cudaError_t gemm_swap(const zb200_engine* e, const void* w, int n_tiles, int rows, int k, const ALoader& al,
+                      const Epilogue& epi, cudaStream_t st) {
+  SwapCore g{};
+  g.Wp = w, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = rows;
+  g.partial_ws = e->d.gemm_ws, g.tickets = e->d.gemm_tickets, g.trace = nullptr, g.trace_id = -1;
+  const int groups = (n_tiles + 1) / 2, kbu = g.k_blocks / 2, cap = 2 * e->sk_sms;
+  const int s = std::max(1, std::min(std::min(SWP_MAXC, kbu), cap / groups));
+  return launch_gemm_swap(g, al, epi, groups * s, st);
+}
+
 // Decode step with rows = 2B <= 128: every projection streams its weights through gemm_skinny; out_proj and fc2 leave
 // their split-K partial sums to the fused residual + LayerNorm kernel, which also produces the next GEMM's input.
 int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
@@ -182,6 +195,9 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
   const int rows = 2 * d.batch, n_seq = rows;
   const int* pos_ptr = d.state + ST_POS;
   bf16 *x = (bf16*)d.x, *xn = (bf16*)d.xn, *q = (bf16*)d.q, *att = (bf16*)d.att, *h = (bf16*)d.h;
+  // at <= 8 rows selected projections run on the operand-swapped kernel (bit 0 in_proj, 2 fc1, 3 heads)
+  static const int swap_env = getenv("ZB200_SWAP_MASK") ? atoi(getenv("ZB200_SWAP_MASK")) : 13;
+  const int swap_mask = (rows <= 8 && dm % 128 == 0) ? swap_env : 0;
   const SkPlan p_out = plan_deferred(e->sk_sms, rows, dm / NT, hd / 64, d.gemm_ws_floats, dm);
   const SkPlan p_fc2 = plan_deferred(e->sk_sms, rows, dm / NT, d.d_ff / 64, d.gemm_ws_floats, dm);
   ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w, (const bf16*)d.ln1_b, xn, rows, dm, d.ln_eps, 1, 0, st));
@@ -189,8 +205,13 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
     {  // in_proj + RoPE + KV page write
       ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, d.out_stride, st));
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
-      EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, 1, d.n_heads};
-      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
+      if (swap_mask & 1) {
+        EpiTQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, d.n_heads};
+        ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
+      } else {
+        EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, 1, d.n_heads};
+        ZB_TRY(gemm_any(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
+      }
     }
     {
       AttnDecodeArgs a;
@@ -212,8 +233,13 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
     {  // fc1 + SiLU gate
       ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, d.fc2_stride, st));
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
-      EpiSwiGLU<NT> epi{h, d.d_ff};
-      ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
+      if (swap_mask & 4) {
+        EpiTSwiGLU epi{h, d.d_ff};
+        ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
+      } else {
+        EpiSwiGLU<NT> epi{h, d.d_ff};
+        ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
+      }
     }
     {  // fc2 (split-K partials) -> residual + the next layer's norm (norm_f after the last layer)
       if (l + 1 < d.n_layer)
@@ -234,11 +260,69 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
   {  // heads + CFG on the normalised rows (model.py:110-115)
     ZB_TRY_RC(prefetch_l2(e, d.w_qkv, d.qkv_stride, st));  // the next frame starts with layer 0's in_proj
     const int tiles_per_head = d.head_rows_padded / NT;
-    ARowCfgPairs al{(const uint8_t*)xn, (size_t)dm * 2, d.batch};
-    EpiHeadsCfg<NT> epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
-    ZB_TRY(gemm_any(e, d.w_heads, d.n_q * tiles_per_head, n_seq, dm, al, epi, st));
+    if (swap_mask & 8) {
+      ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+      EpiTHeadsCfg epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
+      ZB_TRY(gemm_swap(e, d.w_heads, d.n_q * tiles_per_head, n_seq, dm, al, epi, st));
+    } else {
+      ARowCfgPairs al{(const uint8_t*)xn, (size_t)dm * 2, d.batch};
+      EpiHeadsCfg<NT> epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
+      ZB_TRY(gemm_any(e, d.w_heads, d.n_q * tiles_per_head, n_seq, dm, al, epi, st));
+    }
   }
   return join_side(e, st);
+}
+
+// Decode step with rows = 2B <= 8 (gemm_swap.cuh): the weights are the 128-row UMMA operand, thread == output feature.
+// Each group of two n_tiles is shared by at most 8 CTAs whose 4 KB partials the last one to arrive sums in one batch of
+// loads, so RoPE / residual / SwiGLU / CFG epilogues run in the GEMM itself and no partial-sum pass exists.
+int run_decode_small(zb200_engine* e, cudaStream_t st) {
+  const zb200_engine_desc& d = e->d;
+  const int dm = d.d_model, hd = d.n_heads * ZB200_HEAD_DIM, kvd = d.n_kv_heads * ZB200_HEAD_DIM;
+  const int rows = 2 * d.batch;
+  const int* pos_ptr = d.state + ST_POS;
+  bf16 *x = (bf16*)d.x, *xn = (bf16*)d.xn, *q = (bf16*)d.q, *att = (bf16*)d.att, *h = (bf16*)d.h;
+  for (int l = 0; l < d.n_layer; ++l) {
+    ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w + (size_t)l * dm, (const bf16*)d.ln1_b + (size_t)l * dm, xn, rows, dm,
+                            d.ln_eps, 1, 0, st));
+    {  // in_proj + RoPE + KV page write
+      ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+      EpiTQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, d.n_heads};
+      ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
+    }
+    {
+      AttnDecodeArgs a;
+      a.q = q, a.out = att, a.kv = kv_of(d, l), a.pos_ptr = pos_ptr, a.pos_add = 0;
+      a.n_heads = d.n_heads, a.n_kv_heads = d.n_kv_heads, a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
+      a.partial_ws = d.attn_ws, a.tickets = d.attn_tickets;
+      ZB_TRY(launch_attn_decode(a, rows, d.attn_nsplit, st));
+    }
+    {  // out_proj + residual
+      ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
+      EpiTResidual epi{x, dm};
+      ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, dm / NT, rows, hd, al, epi, st));
+    }
+    ZB_TRY(launch_layernorm(x, (const bf16*)d.ln2_w + (size_t)l * dm, (const bf16*)d.ln2_b + (size_t)l * dm, xn, rows, dm,
+                            d.ln_eps, 1, 0, st));
+    {  // fc1 + SiLU gate
+      ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+      EpiTSwiGLU epi{h, d.d_ff};
+      ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
+    }
+    {  // fc2 + residual
+      ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
+      EpiTResidual epi{x, dm};
+      ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, dm / NT, rows, d.d_ff, al, epi, st));
+    }
+  }
+  ZB_TRY(launch_layernorm(x, (const bf16*)d.lnf_w, (const bf16*)d.lnf_b, xn, rows, dm, d.ln_eps, 1, 0, st));
+  {  // heads + CFG on the normalised rows (model.py:110-115)
+    const int tiles_per_head = d.head_rows_padded / NT;
+    ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
+    EpiTHeadsCfg epi{d.logits, d.batch, d.n_q, d.vocab, tiles_per_head, d.cfg_scale};
+    ZB_TRY(gemm_swap(e, d.w_heads, d.n_q * tiles_per_head, rows, dm, al, epi, st));
+  }
+  return ZB200_OK;
 }
 
 // All transformer layers on `rows` rows of x (seq_len positions per sequence), then norm_f + heads + CFG.
@@ -380,6 +464,9 @@ static int decode_logits(zb200_engine* e, cudaStream_t st) {
   // embed the previous frame (column offset-1) for the B conditional rows and duplicate for the unconditional ones
   ZB_TRY(launch_embed_sum(d.delayed, d.n_q * d.t_delayed, d.t_delayed, d.state + ST_OFFSET, -1, 1, (const bf16*)d.emb,
                           (bf16*)d.x, d.batch, d.n_q, d.vocab, d.d_model, 1, 0, d.batch, st));
+  static const bool all_swap = getenv("ZB200_ALL_SWAP") != nullptr;
+  if (2 * d.batch <= 8 && e->sk_sms > 0 && all_swap && d.d_model % 128 == 0 && d.d_ff % 128 == 0)
+    return run_decode_small(e, st);
   if (2 * d.batch <= GEMM_BM && e->sk_sms > 0) return run_decode_skinny(e, st);
   return run_backbone(e, 2 * d.batch, 1, true, st);
 }

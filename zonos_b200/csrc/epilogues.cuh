@@ -112,10 +112,12 @@ struct EpiSwiGLU {
   }
 };
 
-// in_proj epilogue (NT = 64 = half a head): interleaved-pair RoPE in fp32 on q and k (separately rounded products,
-// result cast to bf16: _torch.py:18-30), q -> q_out [rows, H*128], k/v -> paged cache (replaces _update_kv_cache,
-// _torch.py:33-49).  Row m is (sequence m / seq_len, position pos0 + m % seq_len).
-struct EpiQkvRope {
+// in_proj epilogue (NT = 64 or 16 columns of one head): interleaved-pair RoPE in fp32 on q and k (separately rounded
+// products, result cast to bf16: _torch.py:18-30), q -> q_out [rows, H*128], k/v -> paged cache (replaces
+// _update_kv_cache, _torch.py:33-49).  Row m is (sequence m / seq_len, position pos0 + m % seq_len).
+template <int NT>
+struct EpiQkvRopeT {
+  static_assert(128 % NT == 0 && NT % 8 == 0, "a tile must not straddle heads");
   bf16* q_out;
   KvLayout kv;
   const float* rope;   // fp32 [n_pos][64][2] (cos, sin)
@@ -126,13 +128,14 @@ struct EpiQkvRope {
     const int grow = m_tile * GEMM_BM + row;
     const int seq = grow / seq_len;
     const int pos = (pos_ptr ? *pos_ptr : 0) + pos_add + grow % seq_len;
-    const int head_all = n_tile >> 1, half = n_tile & 1;  // 128 dims per head, 64 per tile
+    const int col0 = n_tile * NT;
+    const int head_all = col0 >> 7, within = col0 & 127;  // 128 dims per head
     const int q_heads = n_heads, kv_heads = kv.n_kv_heads;
-    float r[64];
+    float r[NT];
     if (head_all < q_heads + kv_heads) {  // q or k: rotate
-      const float2* cs = reinterpret_cast<const float2*>(rope) + (size_t)pos * 64 + half * 32;
+      const float2* cs = reinterpret_cast<const float2*>(rope) + (size_t)pos * 64 + within / 2;
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
+      for (int i = 0; i < NT / 2; ++i) {
         const float2 t = __ldg(cs + i);
         const float a = bf16_round(acc[2 * i]), b = bf16_round(acc[2 * i + 1]);
         r[2 * i] = __fsub_rn(__fmul_rn(a, t.x), __fmul_rn(b, t.y));
@@ -140,27 +143,28 @@ struct EpiQkvRope {
       }
     } else {
 #pragma unroll
-      for (int i = 0; i < 64; ++i) r[i] = acc[i];
+      for (int i = 0; i < NT; ++i) r[i] = acc[i];
     }
-    uint4 v[8];
+    uint4 v[NT / 8];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
+    for (int c = 0; c < NT / 8; ++c) {
       v[c].x = pack_bf16x2(r[8 * c], r[8 * c + 1]), v[c].y = pack_bf16x2(r[8 * c + 2], r[8 * c + 3]);
       v[c].z = pack_bf16x2(r[8 * c + 4], r[8 * c + 5]), v[c].w = pack_bf16x2(r[8 * c + 6], r[8 * c + 7]);
     }
     if (head_all < q_heads) {
-      uint4* o = reinterpret_cast<uint4*>(q_out + (size_t)grow * q_heads * 128 + head_all * 128 + half * 64);
+      uint4* o = reinterpret_cast<uint4*>(q_out + (size_t)grow * q_heads * 128 + head_all * 128 + within);
 #pragma unroll
-      for (int c = 0; c < 8; ++c) o[c] = v[c];
+      for (int c = 0; c < NT / 8; ++c) o[c] = v[c];
     } else {
       const int is_v = head_all >= q_heads + kv_heads;
       const int head = head_all - q_heads - (is_v ? kv_heads : 0);
       uint4* o = reinterpret_cast<uint4*>(kv.row(seq, pos, is_v, head));
 #pragma unroll
-      for (int c = 0; c < 8; ++c) o[(half * 8 + c) ^ (pos & 7)] = v[c];
+      for (int c = 0; c < NT / 8; ++c) o[(within / 8 + c) ^ (pos & 7)] = v[c];
     }
   }
 };
+typedef EpiQkvRopeT<64> EpiQkvRope;
 
 // 9 output heads + classifier-free guidance + pad mask (model.py:100-116).  A rows are loaded as (cond, uncond)
 // pairs (ARowCfgPairs) so the partner logit sits in the neighbouring lane.

@@ -8,6 +8,9 @@
 //       MODE_K2: two consecutive k-blocks of one 64-row n_tile (one contiguous 16 KB bulk copy)      -- M <= 32
 //       MODE_T2: one k-block of two adjacent n_tiles (UMMA N = 128; the A k-block is reused twice)    -- M  > 32
 //       MODE_K1: one k-block of one n_tile (8 KB; fallback when K/64 is odd or the tile count is odd)
+//       MODE_N16: eight consecutive k-blocks of one 16-row n_tile (weights packed with tile_n = 16)    -- M <= 8:
+//                 N / 16 >= 128 independent column slices, every CTA runs the whole K of its slice, so no split-K
+//                 fix-up, no partial sums and the fused epilogue (RoPE / residual) runs straight from TMEM
 //     Units are numbered group-major (group = n_tile or n_tile pair) and CTA c of G owns units [c*U/G, (c+1)*U/G):
 //     "stream-K" with a static, balanced partition.
 //   * weight producer warp (one lane): 1-D TMA bulk copies (UBLKCP, evict-first) into a ring.  It does not depend on
@@ -33,7 +36,7 @@ namespace zb {
 constexpr int SK_NT = 64;                         // weight rows of one packed tile
 constexpr int SK_TILE_BYTES = SK_NT * 128;        // 8 KB packed (n_tile, k_block) image
 constexpr int SK_PARTIAL_F4 = (SK_NT / 4) * 128;  // float4 per partial sub-tile (32 KB)
-enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2 };
+enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2, MODE_N16 = 3 };
 
 // Optional in-kernel timeline (build with ZB200_TRACE=1): globaltimer stamps per launch / CTA / event.
 #ifdef SK_TRACE
@@ -71,25 +74,29 @@ struct SkinnyCore {
 
 template <int A_ROWS, int MODE>
 struct SkinnyCfg {
+  static constexpr int NTILE = (MODE == MODE_N16) ? 16 : SK_NT;  // weight rows of one packed tile
+  static constexpr int TILE_BYTES = NTILE * 128;
+  static constexpr int PARTIAL_F4 = (NTILE / 4) * 128;
   static constexpr int TG = (MODE == MODE_T2) ? 2 : 1;  // n_tiles per unit
-  static constexpr int KG = (MODE == MODE_K2) ? 2 : 1;  // k-blocks per unit
+  static constexpr int KG = (MODE == MODE_K2) ? 2 : (MODE == MODE_N16) ? 8 : 1;  // k-blocks per unit
+  static_assert(MODE != MODE_N16 || A_ROWS <= 8, "16-column slices are the M <= 8 path");
   static constexpr int PROD_WARPS = (A_ROWS >= 128) ? 4 : 1;
   static constexpr int PROD_THREADS = PROD_WARPS * 32;
   static constexpr int THREADS = (4 + PROD_WARPS + 2) * 32;
   static constexpr int MIN_BLOCKS = (A_ROWS >= 128) ? 1 : 2;
   static constexpr int A_SUB_BYTES = A_ROWS * 128;
   static constexpr int A_STAGE_BYTES = KG * A_SUB_BYTES;
-  static constexpr int W_STAGE_BYTES = TG * KG * SK_TILE_BYTES;
-  static constexpr int SA = (A_ROWS <= 8) ? 8 : 4;
+  static constexpr int W_STAGE_BYTES = TG * KG * TILE_BYTES;
+  static constexpr int SA = (A_ROWS <= 8 && MODE != MODE_N16) ? 8 : 4;
   static constexpr int SW = (A_ROWS >= 128) ? (128 * 1024 / W_STAGE_BYTES)
-                                            : ((A_ROWS > 8 ? 64 : 80) * 1024 / W_STAGE_BYTES);
+                                            : ((A_ROWS > 8 || MODE == MODE_N16 ? 64 : 80) * 1024 / W_STAGE_BYTES);
   static constexpr int A_BYTES = SA * A_STAGE_BYTES;
   static constexpr int W_BYTES = SW * W_STAGE_BYTES;
   static constexpr int BAR_OFFSET = A_BYTES + W_BYTES;
   static constexpr int N_BARS = 2 * SA + 2 * SW + 4;
   static constexpr int TOTAL = BAR_OFFSET + N_BARS * 8 + 16;
   static constexpr int DYN_BYTES = TOTAL + 1024;
-  static constexpr uint32_t TMEM_COLS = 2 * TG * SK_NT;  // 128 or 256
+  static constexpr uint32_t TMEM_COLS = 2 * TG * NTILE;  // 32, 128 or 256
   static_assert(W_BYTES >= GEMM_BM * 128, "the 128-row operand read must stay inside the allocation");
   static_assert(MIN_BLOCKS == 1 || DYN_BYTES <= 113 * 1024, "two CTAs per SM need <= 113 KB each");
 };
@@ -177,9 +184,9 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
         mbar_arrive_expect_tx(&full_w[s], C::W_STAGE_BYTES);
         uint8_t* dst = w_ring + s * C::W_STAGE_BYTES;
         if (MODE == MODE_T2) {
-          const uint8_t* src = wp + ((size_t)(2 * grp) * KB + ku) * SK_TILE_BYTES;
-          bulk_g2s_hint(dst, src, SK_TILE_BYTES, &full_w[s], pol);
-          bulk_g2s_hint(dst + SK_TILE_BYTES, src + (size_t)KB * SK_TILE_BYTES, SK_TILE_BYTES, &full_w[s], pol);
+          const uint8_t* src = wp + ((size_t)(2 * grp) * KB + ku) * C::TILE_BYTES;
+          bulk_g2s_hint(dst, src, C::TILE_BYTES, &full_w[s], pol);
+          bulk_g2s_hint(dst + C::TILE_BYTES, src + (size_t)KB * C::TILE_BYTES, C::TILE_BYTES, &full_w[s], pol);
         } else {  // units are contiguous in memory
           bulk_g2s_hint(dst, wp + (size_t)(u0 + i) * C::W_STAGE_BYTES, C::W_STAGE_BYTES, &full_w[s], pol);
         }
@@ -191,7 +198,7 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
   } else if (warp == MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(GEMM_BM, TG * SK_NT, 1);
+      constexpr uint32_t idesc = umma_idesc(GEMM_BM, TG * C::NTILE, 1);
       int i = 0, f = 0, u = u0;
       while (u < u1) {
         const int grp = u / KBU, ku_begin = u - grp * KBU;
@@ -199,7 +206,7 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
         const int b = f & 1;
         mbar_wait(&tmem_empty[b], ((f >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)(b * TG * SK_NT);
+        const uint32_t tmem_d = tmem_base + (uint32_t)(b * TG * C::NTILE);
         for (int ku = ku_begin; ku < ku_end; ++ku, ++i) {
           const int sa = i % SA, sw = i % SW;
           mbar_wait(&full_w[sw], (i / SW) & 1);
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
 #pragma unroll
           for (int kk = 0; kk < KG; ++kk) {
             const uint64_t adesc = umma_desc_sw128(a_addr + kk * C::A_SUB_BYTES);
-            const uint64_t bdesc = umma_desc_sw128(w_addr + kk * SK_TILE_BYTES);
+            const uint64_t bdesc = umma_desc_sw128(w_addr + kk * C::TILE_BYTES);
 #pragma unroll
             for (int k = 0; k < GEMM_BK / 16; ++k)
               umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
@@ -291,16 +298,20 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
       const int b = f & 1;
       const bool complete = (ku_begin == 0 && ku_end == KBU);
       const int slot = (u == u0) ? 0 : 1;  // a CTA has at most two partial fragments: its first and its last
-      float4* mine = ws + ((size_t)cta * 2 + slot) * TG * SK_PARTIAL_F4;
+      float4* mine = ws + ((size_t)cta * 2 + slot) * TG * C::PARTIAL_F4;
       mbar_wait(&tmem_full[b], (f >> 1) & 1);
       if (tid == 0 && f == 0) SK_STAMP(7);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * TG * SK_NT);
-      float acc[SK_NT];
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * TG * C::NTILE);
+      float acc[C::NTILE];
 #pragma unroll
       for (int j = 0; j < TG; ++j) {
-        tmem_ld32(taddr + j * SK_NT, acc);
-        tmem_ld32(taddr + j * SK_NT + 32, acc + 32);
+        if constexpr (C::NTILE == 16) {
+          tmem_ld16(taddr, acc);
+        } else {
+          tmem_ld32(taddr + j * C::NTILE, acc);
+          tmem_ld32(taddr + j * C::NTILE + 32, acc + 32);
+        }
         tmem_ld_wait();
         if (j == TG - 1) {
           tc_fence_before();
@@ -312,8 +323,8 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           epi(row, row_valid, 0, grp * TG + j, acc);
         } else if (row_valid) {
 #pragma unroll
-          for (int c = 0; c < SK_NT / 4; ++c)
-            mine[(j * (SK_NT / 4) + c) * 128 + row] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+          for (int c = 0; c < C::NTILE / 4; ++c)
+            mine[(j * (C::NTILE / 4) + c) * 128 + row] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
         }
       }
       if (!sk_is_deferred<Epilogue>::value && !complete) {
@@ -332,12 +343,12 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           for (int j = 0; j < TG; ++j) {
             if (row_valid) {
 #pragma unroll
-              for (int c = 0; c < SK_NT; ++c) acc[c] = 0.f;
+              for (int c = 0; c < C::NTILE; ++c) acc[c] = 0.f;
               for (int cc = c_first; cc <= c_last; ++cc) {  // fixed order -> bitwise reproducible
                 const int sl = (sk_first_unit(cc, units, G) / KBU == grp) ? 0 : 1;
-                const float4* part = ws + (((size_t)cc * 2 + sl) * TG + j) * SK_PARTIAL_F4;
+                const float4* part = ws + (((size_t)cc * 2 + sl) * TG + j) * C::PARTIAL_F4;
 #pragma unroll
-                for (int c = 0; c < SK_NT / 4; ++c) {
+                for (int c = 0; c < C::NTILE / 4; ++c) {
                   const float4 v = __ldcg(&part[c * 128 + row]);
                   acc[4 * c] += v.x, acc[4 * c + 1] += v.y, acc[4 * c + 2] += v.z, acc[4 * c + 3] += v.w;
                 }
@@ -375,6 +386,12 @@ cudaError_t launch_gemm_skinny_cfg(const SkinnyCore& g, const ALoader& al, const
   const int units = (g.n_tiles / C::TG) * (g.k_blocks / C::KG);
   grid = grid < 1 ? 1 : (grid > units ? units : grid);
   return launch_pdl(kern, dim3((unsigned)grid), dim3(C::THREADS), (size_t)C::DYN_BYTES, st, pdl_enabled(), g, al, epi);
+}
+
+// M <= 8 with weights packed in 16-row tiles (g.n_tiles = N / 16, k_blocks % 8 == 0): one CTA per column slice.
+template <class ALoader, class Epilogue>
+cudaError_t launch_gemm_skinny_n16(const SkinnyCore& g, const ALoader& al, const Epilogue& epi, cudaStream_t st) {
+  return launch_gemm_skinny_cfg<8, MODE_N16>(g, al, epi, g.n_tiles, st);
 }
 
 // Mode the launcher picks for (rows, n_tiles, k_blocks); prefer_k1 forces 8 KB single-tile units at M > 32 (smaller

@@ -2,7 +2,9 @@
 #include "../../include/zonos_b200.h"
 #include "common.cuh"
 #include "epilogues.cuh"
+#include "epilogues_t.cuh"
 #include "gemm_skinny.cuh"
+#include "gemm_swap.cuh"
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 
@@ -329,5 +331,22 @@ extern "C" int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_
   const int rln_id = g_trace_buf ? g_trace_next++ : -1;
   ZB_CHECK_CUDA(launch_resid_ln((bf16*)x, ws, splits, m, (const bf16*)ln_w, (const bf16*)ln_b, (bf16*)xn, n, eps,
                                 (cudaStream_t)stream, g_trace_buf, rln_id));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_gemm_swap_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo,
+                                    int grid, float* ws, int64_t ws_floats, int* tickets, int n_tickets, void* stream) {
+  ZB_REQUIRE(m > 0 && m <= 8 && n > 0 && k > 0 && k % 128 == 0 && lda % 8 == 0,
+             "gemm_swap: bad shape m=%d n=%d k=%d lda=%d (m <= 8, k %% 128 == 0)", m, n, k, lda);
+  const int n_tiles = ceil_div(n, SK_NT);
+  ZB_REQUIRE(grid >= 1 && grid <= 1024, "gemm_swap: grid=%d out of range", grid);
+  ZB_REQUIRE(ws && tickets && ws_floats >= (int64_t)grid * 2048 && n_tickets >= (n_tiles + 1) / 2,
+             "gemm_swap: workspace too small (needs grid*8 KB and ceil(n/128) tickets)");
+  SwapCore g{};
+  g.Wp = w_packed, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = m, g.partial_ws = ws, g.tickets = tickets;
+  g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
+  ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
+  EpiTStoreBf16 epi{(bf16*)out, ldo, n};
+  ZB_CHECK_CUDA(launch_gemm_swap(g, al, epi, grid, (cudaStream_t)stream));
   return ZB200_OK;
 }

@@ -87,6 +87,20 @@ def gemm_skinny_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, grid: int 
     return out
 
 
+def gemm_swap_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, grid: int = 148) -> torch.Tensor:
+    """Test hook: bf16 [M<=8,K] x packed [N,K]^T -> bf16 [M,N] through the operand-swapped weight-streaming kernel."""
+    a = _cuda(a, torch.bfloat16)
+    M, K = a.shape
+    grid = max(1, min(grid, 1024))
+    out = torch.empty(M, n, dtype=torch.bfloat16, device=a.device)
+    ws = torch.full((grid * 2048,), float("nan"), dtype=torch.float32, device=a.device)
+    tickets = torch.zeros((n + 127) // 128, dtype=torch.int32, device=a.device)
+    check(lib().zb200_gemm_swap_bf16(ptr(a), M, K, ptr(w_packed), n, K, ptr(out), n, grid, ptr(ws),
+                                     ctypes.c_int64(ws.numel()), ptr(tickets), tickets.numel(), stream_ptr()), "gemm_swap_bf16")
+    assert int(tickets.abs().sum()) == 0
+    return out
+
+
 def gemm_resid_ln(a, w_packed, x, ln_w, ln_b, splits: int = 4, eps: float = 1e-5):
     """Test hook: returns (bf16(x + bf16(a @ w^T)), LayerNorm of that) through the deferred split-K GEMM + resid_ln kernel."""
     a, x = _cuda(a, torch.bfloat16), _cuda(x, torch.bfloat16).clone()
