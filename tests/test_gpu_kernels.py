@@ -90,7 +90,8 @@ def test_gemm_swap_stream_k(ops, M, N, K, grid):
 
 
 @pytest.mark.parametrize("M,N,K,splits", [(2, 2048, 2048, 8), (2, 2048, 8192, 8), (128, 2048, 2048, 8), (128, 2048, 8192, 8),
-                                          (6, 512, 512, 2), (20, 512, 1024, 1), (64, 1024, 2048, 4)])
+                                          (6, 512, 512, 2), (20, 512, 1024, 1), (64, 1024, 2048, 4), (128, 2048, 2048, 9),
+                                          (128, 2048, 8192, 9), (2, 2048, 2048, 5)])
 def test_gemm_resid_ln(ops, M, N, K, splits):
     """out_proj / fc2 group of the decode step: deferred split-K GEMM + fused residual + LayerNorm kernel, against the
     reference's op order (Linear -> bf16, residual add -> bf16, LayerNorm -> bf16: zonos/backbone/_torch.py:99-102)."""

@@ -138,3 +138,34 @@ def test_generate_teacher_forced_vs_oracle(tiny_model, golden, name):
                 flips += int(bad.sum())
             delayed[..., col] = got
         print(f"{name}: {flips} near-tie flips over {frames.shape[-1]} frames")
+
+
+@pytest.mark.parametrize("B", [6, 20, 64])
+def test_decode_batch_paths_vs_oracle(tiny_model, B):
+    """The decode step picks its kernels by 2B (<= 8: operand-swapped GEMM; <= 32 / <= 128: weight-streaming GEMM with
+    ticketed or deferred split-K, fused residual+LayerNorm, in_proj finish kernel).  Every path must give the oracle's
+    CFG logits, teacher-forced on the GPU's own greedy tokens."""
+    from oracle import delay as odelay
+    from oracle import generate as ogen
+
+    Lc, N = 5, 5
+    W = shapes.synth_transformer_weights("tiny", seed=0)
+    cond = shapes.synth_conditioning(B, Lc, shapes.SHAPES["tiny"]["d_model"], seed=11)
+    taps = []
+    out = tiny_model.generate(cond.cuda(), None, max_new_tokens=N, batch_size=B, progress_bar=False,
+                              sampling_params=dict(temperature=0.0, repetition_penalty=1.0),
+                              _tap=lambda s, l, f: taps.append((l.cpu(), f.cpu())))
+    assert len(out) == B
+    delayed = odelay.apply_delay_pattern(torch.full((B, 9, N), -1, dtype=torch.int64), 1025)
+    src = ogen.ModelLogits(W, "tiny", cond, Lc + N + 9, 2.0)
+    ref = [src.prefill(delayed[..., :1])]
+    ids = taps[0][1]
+    for s in range(1, len(taps)):
+        ref.append(src.step(ids))
+        ids = taps[s][1]
+    for (got, _), want in zip(taps, ref):
+        fin = torch.isfinite(want)
+        assert torch.equal(fin, torch.isfinite(got))
+        d = got[fin] - want[fin]
+        assert float(d.abs().max()) <= logit_max_abs(2.0, want) + 1e-6
+        assert float(d.pow(2).mean().sqrt() / want[fin].pow(2).mean().sqrt()) <= LOGIT_REL_RMS

@@ -121,14 +121,14 @@ SkPlan plan_deferred(int sms, int rows, int n_tiles, int k_blocks, int64_t ws_fl
   const int groups = n_tiles / skinny_tg(mode), kbu = k_blocks / skinny_kg(mode);
   int s = 1;
   for (int c = 1; c <= kbu; ++c)
-    if (kbu % c == 0 && groups * c <= cap && kbu / c >= 2 && (int64_t)c * rows * n <= ws_floats) s = c;
+    if (groups * c <= cap && kbu / c >= 2 && (int64_t)c * rows * n <= ws_floats) s = c;
   return SkPlan{groups * s, s, false};
 }
 
 SkinnyCore sk_core(const zb200_engine_desc& d, const void* w, int n_tiles, int rows, int k) {
   SkinnyCore g{};
   g.Wp = w, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = rows;
-  g.partial_ws = d.gemm_ws, g.tickets = d.gemm_tickets, g.split_units = 0, g.trace = nullptr, g.trace_id = -1;
+  g.partial_ws = d.gemm_ws, g.tickets = d.gemm_tickets, g.n_splits = 1, g.trace = nullptr, g.trace_id = -1;
   return g;
 }
 
@@ -198,6 +198,9 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
   // at <= 8 rows selected projections run on the operand-swapped kernel (bit 0 in_proj, 2 fc1, 3 heads)
   static const int swap_env = getenv("ZB200_SWAP_MASK") ? atoi(getenv("ZB200_SWAP_MASK")) : 13;
   const int swap_mask = (rows <= 8 && dm % 128 == 0) ? swap_env : 0;
+  static const bool no_qkv_def = getenv("ZB200_NO_QKV_DEFERRED") != nullptr;
+  const bool qkv_deferred = rows > 32 && !no_qkv_def && (hd + 2 * kvd) <= 8192;
+  const SkPlan p_qkv = plan_deferred(e->sk_sms, rows, (hd + 2 * kvd) / NT, dm / 64, d.gemm_ws_floats, hd + 2 * kvd);
   const SkPlan p_out = plan_deferred(e->sk_sms, rows, dm / NT, hd / 64, d.gemm_ws_floats, dm);
   const SkPlan p_fc2 = plan_deferred(e->sk_sms, rows, dm / NT, d.d_ff / 64, d.gemm_ws_floats, dm);
   ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w, (const bf16*)d.ln1_b, xn, rows, dm, d.ln_eps, 1, 0, st));
@@ -208,6 +211,12 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       if (swap_mask & 1) {
         EpiTQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, d.n_heads};
         ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
+      } else if (qkv_deferred) {  // split-K partials, finished (sum + RoPE + q / KV write) by a row x column kernel
+        SkinnyCore g = sk_core(d, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm);
+        g.n_splits = p_qkv.splits;
+        EpiPartial epi{d.gemm_ws, rows, hd + 2 * kvd};
+        ZB_TRY(launch_gemm_skinny(g, al, epi, p_qkv.grid, st));
+        ZB_TRY(launch_qkv_finish(d.gemm_ws, p_qkv.splits, rows, hd + 2 * kvd, q, kv_of(d, l), d.rope, pos_ptr, d.n_heads, st));
       } else {
         EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, 1, d.n_heads};
         ZB_TRY(gemm_any(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm, al, epi, st));
@@ -223,7 +232,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
     {  // out_proj (split-K partials) -> residual + norm2
       ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.fc1_stride, st));
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, dm / NT, rows, hd);
-      g.split_units = (hd / 64) / skinny_kg(skinny_mode(rows, dm / NT, hd / 64)) / p_out.splits;
+      g.n_splits = p_out.splits;
       ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
       EpiPartial epi{d.gemm_ws, rows, dm};
       ZB_TRY(launch_gemm_skinny(g, al, epi, p_out.grid, st));
@@ -247,7 +256,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       else
         ZB_TRY_RC(prefetch_l2(e, d.w_heads, (int64_t)d.n_q * d.head_rows_padded * dm * 2, st));
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, dm / NT, rows, d.d_ff);
-      g.split_units = (d.d_ff / 64) / skinny_kg(skinny_mode(rows, dm / NT, d.d_ff / 64)) / p_fc2.splits;
+      g.n_splits = p_fc2.splits;
       ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
       EpiPartial epi{d.gemm_ws, rows, dm};
       ZB_TRY(launch_gemm_skinny(g, al, epi, p_fc2.grid, st));

@@ -54,7 +54,7 @@ __device__ __forceinline__ void sk_stamp(unsigned long long* trace, int launch, 
 #endif
 
 // Epilogues with `static constexpr bool kDeferred = true` take every fragment raw through
-//   partial(row, row_valid, n_tile, split, acc)        split = first unit of the fragment / split_units
+//   partial(row, row_valid, n_tile, split, acc)        split = CTA index % n_splits (grid = n_groups * n_splits)
 // and leave the reduction over splits to their consumer kernel (resid_ln_kernel): no workspace slots, no tickets.
 template <class E, class = void>
 struct sk_is_deferred { static constexpr bool value = false; };
@@ -67,7 +67,7 @@ struct SkinnyCore {
   int m_valid;        // rows of A (<= 128)
   float* partial_ws;  // [gridDim.x][2][TG][SK_PARTIAL_F4] float4
   int* tickets;       // [n_groups] zero-initialised, self-resetting
-  int split_units;    // deferred epilogues: units per split (the grid is aligned: every CTA is one fragment)
+  int n_splits;       // deferred epilogues: CTAs per group (grid = n_groups * n_splits: every CTA is one fragment)
   unsigned long long* trace;  // debug timeline [64][160][12] (trace builds), else nullptr
   int trace_id;               // launch slot of the debug timeline
 };
@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           mbar_arrive(&tmem_empty[b]);  // the issuer may start the next-but-one fragment into this accumulator set
         }
         if constexpr (sk_is_deferred<Epilogue>::value) {
-          epi.partial(row, row_valid, grp * TG + j, ku_begin / g.split_units, acc);
+          epi.partial(row, row_valid, grp * TG + j, cta % g.n_splits, acc);
         } else if (complete) {
           epi(row, row_valid, 0, grp * TG + j, acc);
         } else if (row_valid) {

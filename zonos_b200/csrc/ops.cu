@@ -189,6 +189,66 @@ cudaError_t launch_resid_ln(bf16* x, const float* ws, int splits, int rows, cons
                     trace, trace_id);
 }
 
+// ------------------------------------------------------------------------------------------------ in_proj finish
+// Consumer of the deferred split-K in_proj GEMM at M > 32 (EpiPartial): sums the splits in order, rounds to bf16 (the
+// nn.Linear output), applies the interleaved-pair RoPE to q and k (_torch.py:18-30) and writes q and the K/V cache row
+// (_torch.py:33-49) -- the work of EpiQkvRope, spread over rows x columns/8 threads instead of the last CTA of a tile.
+__global__ void qkv_finish_kernel(const float* __restrict__ ws, int splits, int rows, int n_cols, bf16* __restrict__ q_out,
+                                  KvLayout kv, const float* __restrict__ rope, const int* pos_ptr, int n_heads) {
+  pdl_launch_dependents();
+  pdl_wait_prior();
+  const int row = blockIdx.x, col0 = threadIdx.x * 8;
+  if (col0 >= n_cols) return;
+  float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int s0 = 0; s0 < splits; s0 += 8) {
+    float4 a[8], c[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s)
+      if (s0 + s < splits) {
+        const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)(s0 + s) * rows + row) * n_cols + col0);
+        a[s] = __ldcg(p), c[s] = __ldcg(p + 1);
+      }
+#pragma unroll
+    for (int s = 0; s < 8; ++s)
+      if (s0 + s < splits) {
+        o[0] += a[s].x, o[1] += a[s].y, o[2] += a[s].z, o[3] += a[s].w;
+        o[4] += c[s].x, o[5] += c[s].y, o[6] += c[s].z, o[7] += c[s].w;
+      }
+  }
+  const int pos = *pos_ptr;
+  const int head_all = col0 >> 7, within = col0 & 127;
+  const int kv_heads = kv.n_kv_heads;
+  float r[8];
+  if (head_all < n_heads + kv_heads) {
+    const float4* cs = reinterpret_cast<const float4*>(rope + ((size_t)pos * 64 + (within >> 1)) * 2);
+    const float4 t01 = __ldg(cs), t23 = __ldg(cs + 1);
+    const float co[4] = {t01.x, t01.z, t23.x, t23.z}, si[4] = {t01.y, t01.w, t23.y, t23.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float a = bf16_round(o[2 * i]), b = bf16_round(o[2 * i + 1]);
+      r[2 * i] = __fsub_rn(__fmul_rn(a, co[i]), __fmul_rn(b, si[i]));
+      r[2 * i + 1] = __fadd_rn(__fmul_rn(b, co[i]), __fmul_rn(a, si[i]));
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = o[i];
+  }
+  const uint4 v = make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
+  if (head_all < n_heads) {
+    *reinterpret_cast<uint4*>(q_out + (size_t)row * n_heads * 128 + head_all * 128 + within) = v;
+  } else {
+    const int is_v = head_all >= n_heads + kv_heads;
+    const int head = head_all - n_heads - (is_v ? kv_heads : 0);
+    reinterpret_cast<uint4*>(kv.row(row, pos, is_v, head))[(within >> 3) ^ (pos & 7)] = v;
+  }
+}
+
+cudaError_t launch_qkv_finish(const float* ws, int splits, int rows, int n_cols, bf16* q_out, const KvLayout& kv,
+                              const float* rope, const int* pos_ptr, int n_heads, cudaStream_t st) {
+  return launch_pdl(qkv_finish_kernel, dim3(rows), dim3((n_cols / 8 + 31) / 32 * 32), 0, st, pdl_enabled(), ws, splits, rows,
+                    n_cols, q_out, kv, rope, pos_ptr, n_heads);
+}
+
 // ------------------------------------------------------------------------------------------------ embedding sum
 // grid (S, B): hidden[b*out_stride_b + out_off + s] = sum_q emb[q][ids[b,q,col0+s]], adds rounded to bf16 in q order;
 // the row is written twice when dup_off > 0 (cond and uncond copies, model.py:141 / :196-199).
@@ -303,7 +363,7 @@ extern "C" int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void*
              "gemm_skinny: workspace too small (needs grid*2*tg*32 KB and n_tiles tickets)");
   SkinnyCore g{};
   g.Wp = w_packed, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = m, g.partial_ws = ws, g.tickets = tickets;
-  g.split_units = 0;
+  g.n_splits = 1;
   g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
   ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
   EpiStoreBf16<SK_NT> epi{(bf16*)out, ldo, n};
@@ -320,11 +380,11 @@ extern "C" int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_
              "gemm_resid_ln: bad shape m=%d n=%d k=%d lda=%d", m, n, k, lda);
   const int n_tiles = n / SK_NT, mode = skinny_mode(m, n_tiles, k / 64);
   const int n_groups = n_tiles / skinny_tg(mode), kbu = (k / 64) / skinny_kg(mode);
-  ZB_REQUIRE(splits >= 1 && kbu % splits == 0, "gemm_resid_ln: splits=%d must divide the %d units of a group", splits, kbu);
+  ZB_REQUIRE(splits >= 1 && splits <= kbu, "gemm_resid_ln: splits=%d exceeds the %d units of a group", splits, kbu);
   ZB_REQUIRE(ws && ws_floats >= (int64_t)splits * m * n, "gemm_resid_ln: workspace too small");
   SkinnyCore g{};
   g.Wp = w_packed, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = m, g.partial_ws = nullptr, g.tickets = nullptr;
-  g.split_units = kbu / splits, g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
+  g.n_splits = splits, g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
   ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
   EpiPartial epi{ws, m, n};
   ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, n_groups * splits, (cudaStream_t)stream));

@@ -7,6 +7,9 @@ cudaError_t launch_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* 
                              int in_row_mul, int in_row_add, cudaStream_t st);
 cudaError_t launch_resid_ln(bf16* x, const float* ws, int splits, int rows, const bf16* w, const bf16* b, bf16* xn, int d,
                             float eps, cudaStream_t st, unsigned long long* trace = nullptr, int trace_id = -1);
+struct KvLayout;
+cudaError_t launch_qkv_finish(const float* ws, int splits, int rows, int n_cols, bf16* q_out, const KvLayout& kv,
+                              const float* rope, const int* pos_ptr, int n_heads, cudaStream_t st);
 cudaError_t launch_embed_sum(const int32_t* ids, int ids_stride_b, int ids_stride_q, const int* col_ptr, int col_add,
                              int n_cols, const bf16* emb, bf16* out, int batch, int n_q, int vocab, int d,
                              int out_stride_b, int out_off, int dup_off, cudaStream_t st);
