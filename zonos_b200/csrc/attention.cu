@@ -68,7 +68,9 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(AttnDecodeArgs
     }
     fence_barrier_init();
   }
-  pdl_wait_prior();  // q, this step's K/V rows and the position come from the in_proj kernel
+  // The position was written by the previous frame (complete before this graph launch started), and every KV page but
+  // the one holding the current position is older than this frame: the producer streams those before the dependency on
+  // the in_proj kernel is resolved; q, the current K/V row and all outputs wait for it.
   const int n_keys = (p.pos_ptr ? *p.pos_ptr : 0) + p.pos_add + 1;
   const int n_pages = (n_keys + PAGE - 1) / PAGE;
   const int pps = (n_pages + nsplit - 1) / nsplit;
@@ -81,8 +83,14 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(AttnDecodeArgs
     if (lane == 0) {
       const uint64_t pol = l2_policy_evict_first();
       const int* bt = p.kv.block_table + seq * p.kv.pages_per_seq;
+      const int cur_page = (n_keys - 1) / PAGE;
+      bool waited = false;
       for (int i = 0; i < pg1 - pg0; ++i) {
         const int s = i % STAGES;
+        if (!waited && pg0 + i >= cur_page) {
+          pdl_wait_prior();
+          waited = true;
+        }
         mbar_wait(&empty_bar[s], ((i / STAGES) & 1) ^ 1);
         const int page = bt[pg0 + i];
         const size_t kbase = ((((size_t)p.kv.layer * p.kv.num_pages + page) * 2 + 0) * p.kv.n_kv_heads + kvh) * (size_t)(PAGE * HD);
@@ -94,6 +102,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(AttnDecodeArgs
     }
   } else {
     // ---------------------------------------------------------------------------------- consumers
+    pdl_wait_prior();
     // Q fragments (A operand, rows 0..group-1 are heads, the rest zero), kept in registers for the whole kernel
     const int qrow = lane >> 2;
     uint32_t qa0[8], qa2[8];
