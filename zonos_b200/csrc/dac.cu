@@ -11,11 +11,12 @@
 // (:94-99) never makes its own pass over memory.  fp16 storage / fp32 accumulate mirrors the reference's CUDA autocast.
 #include "../../include/zonos_b200.h"
 #include "common.cuh"
+#include <cstdlib>
+
+#include "dac_conv.cuh"
 #include "gemm_tc.cuh"
 
 namespace zb {
-
-typedef __half f16;
 
 // ------------------------------------------------------------------------------------------------ A loader
 struct AConvTaps {
@@ -167,13 +168,118 @@ __global__ void __launch_bounds__(FIN_TILE) dac_final_conv_kernel(const f16* __r
 
 using namespace zb;
 
+// ------------------------------------------------------------------------------------------------ layer launch
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+static int sm_count() {
+  static int n = [] {
+    int dev = 0, v = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    return v > 0 ? v : 148;
+  }();
+  return n;
+}
+static bool dac_use_gemm_tc() {
+  static const bool v = getenv("ZB200_DAC_GEMM_TC") != nullptr;  // the round-1 per-tap gather path, kept for A/B runs
+  return v;
+}
+
 template <int NT>
-static cudaError_t launch_dac_layer(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
+static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
+  const int T_in = L.t_mul_in * T;
+  DacConvArgs a{};
+  a.m_rows = L.up > 0 ? T_in + 1 : T_in;
+  a.T_out = L.up > 0 ? T_in * L.up : T_in;
+  a.n_total = L.c_out * (L.up > 0 ? L.up : 1);
+  a.tiles_per_seq = ceil_div(a.m_rows, 128);
+  a.Wp = (const uint8_t*)L.w;
+  a.n_tiles = ceil_div(a.n_total, NT);
+  const int max_tpc = 256 / NT;
+  a.n_groups = ceil_div(a.n_tiles, max_tpc);
+  a.tpc = ceil_div(a.n_tiles, a.n_groups);
+  a.cblocks = L.pitch_in / 64, a.taps = L.taps, a.shift0 = L.shift0, a.shift_step = L.shift_step;
+  const int s_last = L.shift0 + (L.taps - 1) * L.shift_step;
+  a.smin = s_last < L.shift0 ? s_last : L.shift0;
+  a.halo_rows = 128 + (s_last < L.shift0 ? L.shift0 - s_last : s_last - L.shift0);
+  ZB_REQUIRE(a.halo_rows <= 256, "dac_decode: filter span %d too wide for one TMA box", a.halo_rows - 128);
+  a.a_stage_bytes = (a.halo_rows * 128 + 1023) & ~1023;
+  a.w_stage_bytes = a.tpc * NT * 128;
+  const int budget = DC_SMEM_BYTES - DC_BAR_BYTES - 1024;
+  const int kb = a.taps * a.cblocks;
+  a.w_resident = a.n_groups == 1 && kb <= DC_MAX_SW && kb * a.w_stage_bytes + 2 * a.a_stage_bytes <= budget;
+  if (a.w_resident) {
+    a.sw = kb;
+    a.sa = (budget - a.sw * a.w_stage_bytes) / a.a_stage_bytes;
+  } else {
+    a.sa = 3;
+    a.sw = (budget - a.sa * a.a_stage_bytes) / a.w_stage_bytes;
+  }
+  a.sa = a.sa > DC_MAX_SA ? DC_MAX_SA : a.sa;
+  a.sw = a.sw > DC_MAX_SW ? DC_MAX_SW : a.sw;
+  ZB_REQUIRE(a.sa >= 2 && a.sw >= (a.w_resident ? 1 : 2), "dac_decode: layer does not fit the shared-memory rings");
+  a.total_tiles = batch * a.tiles_per_seq * a.n_groups;
+  a.bias = L.bias;
+  a.resid = L.resid_region >= 0 ? (const f16*)regions[L.resid_region] : nullptr;
+  a.out_raw = L.raw_region >= 0 ? (f16*)regions[L.raw_region] : nullptr;
+  a.out_act = L.act_region >= 0 ? (f16*)regions[L.act_region] : nullptr;
+  a.alpha = L.alpha, a.inv_alpha = L.inv_alpha;
+  a.pitch_out = L.pitch_out, a.C_out = L.c_out, a.up = L.up, a.pad = L.up / 2;
+  ZB_REQUIRE(!(a.resid && a.up > 0), "dac_decode: residual input on a transposed conv");
+
+  EncodeTiledFn enc = encode_tiled_fn();
+  ZB_REQUIRE(enc != nullptr, "dac_decode: cuTensorMapEncodeTiled is not available from this driver");
+  CUtensorMap xmap;
+  const cuuint64_t gdim[3] = {(cuuint64_t)L.pitch_in, (cuuint64_t)T_in, (cuuint64_t)batch};
+  const cuuint64_t gstr[2] = {(cuuint64_t)L.pitch_in * 2, (cuuint64_t)T_in * L.pitch_in * 2};
+  const cuuint32_t box[3] = {64, (cuuint32_t)a.halo_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult cr = enc(&xmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, regions[L.in_region], gdim, gstr, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  ZB_REQUIRE(cr == CUDA_SUCCESS, "dac_decode: cuTensorMapEncodeTiled failed (%d)", (int)cr);
+
+  auto kern = dac_conv_kernel<NT>;
+  static bool configured = false;  // per template instantiation
+  if (!configured) {
+    ZB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DC_SMEM_BYTES));
+    configured = true;
+  }
+  const int smem = a.sa * a.a_stage_bytes + a.sw * a.w_stage_bytes + DC_BAR_BYTES + 1024;
+  const int grid = a.total_tiles < sm_count() ? a.total_tiles : sm_count();
+  kern<<<grid, DC_THREADS, smem, st>>>(xmap, a);
+  ZB_CHECK_LAUNCH("dac_conv_kernel");
+  return ZB200_OK;
+}
+
+template <int NT>
+static int launch_dac_layer(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
   const int T_in = L.t_mul_in * T;
   const int m_rows = L.up > 0 ? T_in + 1 : T_in;
   const int T_out = L.up > 0 ? T_in * L.up : T_in;
   const int n_total = L.c_out * (L.up > 0 ? L.up : 1);
   const int tiles_per_seq = ceil_div(m_rows, GEMM_BM);
+  // the pad columns of an A-operand region must be finite zeros (the matching weights are zero, but 0 * NaN = NaN)
+  if (L.pitch_out > L.c_out) {
+    const size_t rows = (size_t)batch * T_out;
+    for (int r : {L.raw_region, L.act_region})
+      if (r >= 0)
+        ZB_CHECK_CUDA(cudaMemset2DAsync((f16*)regions[r] + L.c_out, (size_t)L.pitch_out * 2, 0,
+                                        (size_t)(L.pitch_out - L.c_out) * 2, rows, st));
+  }
+  if (!dac_use_gemm_tc()) return launch_dac_conv<NT>(L, batch, T, regions, st);
   AConvTaps al;
   al.base = (const uint8_t*)regions[L.in_region], al.T = T_in, al.m_rows = m_rows, al.tiles_per_seq = tiles_per_seq;
   al.cblocks = L.pitch_in / 64, al.row_bytes = L.pitch_in * 2, al.shift0 = L.shift0, al.shift_step = L.shift_step;
@@ -188,17 +294,9 @@ static cudaError_t launch_dac_layer(const zb200_dac_layer& L, int batch, int T, 
   GemmCore g{};
   g.Wp = L.w, g.k_blocks = L.taps * (L.pitch_in / 64), g.kb_per_split = g.k_blocks, g.splits = 1;
   g.m_valid = batch * tiles_per_seq * GEMM_BM, g.partial_ws = nullptr, g.tickets = nullptr, g.stream_weights = 0;
-  // the pad columns of an A-operand region must be finite zeros (the matching weights are zero, but 0 * NaN = NaN)
-  if (L.pitch_out > L.c_out) {
-    const size_t rows = (size_t)batch * T_out;
-    for (int r : {L.raw_region, L.act_region})
-      if (r >= 0) {
-        cudaError_t e = cudaMemset2DAsync((f16*)regions[r] + L.c_out, (size_t)L.pitch_out * 2, 0,
-                                          (size_t)(L.pitch_out - L.c_out) * 2, rows, st);
-        if (e != cudaSuccess) return e;
-      }
-  }
-  return launch_gemm_tc<NT, 4, 0, 2>(g, al, epi, ceil_div(n_total, NT), batch * tiles_per_seq, st);
+  cudaError_t e = launch_gemm_tc<NT, 4, 0, 2>(g, al, epi, ceil_div(n_total, NT), batch * tiles_per_seq, st);
+  if (e != cudaSuccess) return cuda_fail(e, "dac layer launch");
+  return ZB200_OK;
 }
 
 extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, int batch, int t, void* const* regions,
@@ -224,8 +322,8 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
   }
   for (int i = 0; i < p->n_layers; ++i) {
     const zb200_dac_layer& L = p->layers[i];
-    cudaError_t e = L.tile_n == 96 ? launch_dac_layer<96>(L, batch, t, regions, st) : launch_dac_layer<64>(L, batch, t, regions, st);
-    if (e != cudaSuccess) return cuda_fail(e, "dac layer launch");
+    const int rc = L.tile_n == 96 ? launch_dac_layer<96>(L, batch, t, regions, st) : launch_dac_layer<64>(L, batch, t, regions, st);
+    if (rc != ZB200_OK) return rc;
   }
   {
     const int T_out = p->final_t_mul * t;
