@@ -166,11 +166,11 @@ typedef struct {
   int32_t taps;          /* 7, 1, or 2 (transposed conv) */
   int32_t shift0, shift_step; /* time shift of tap i = shift0 + i*shift_step */
   int32_t up;            /* 0 = Conv1d; s > 0 = ConvTranspose1d with stride s, kernel 2s, padding s/2 */
-  int32_t pitch_in;      /* channel pitch of the input region (multiple of 64) */
+  int32_t pitch_in;      /* channels == channel pitch of the input region (multiple of 8; k-blocks of 64 are zero-filled) */
   int32_t c_out, pitch_out, tile_n; /* output channels, output pitch, N tile (64 or 96) */
   int32_t t_mul_in;      /* input rows per code frame (T_in = t_mul_in * T) */
   int32_t in_region, resid_region, raw_region, act_region; /* region index or -1 */
-  const void* w;         /* packed fp16 [n_total][taps*pitch_in], n_total = c_out * max(up,1) */
+  const void* w;         /* packed fp16 [n_total][taps*round_up(pitch_in,64)], n_total = c_out * max(up,1) */
   const float* bias;     /* [n_total] */
   const float* alpha;    /* [c_out] Snake alpha of the consumer (NULL when act_region < 0) */
   const float* inv_alpha;/* [c_out] 1/(alpha + 1e-9) */

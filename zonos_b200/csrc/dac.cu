@@ -1,114 +1,20 @@
 // DAC 44.1 kHz decoder (zonos/autoencoder.py:44-47 -> transformers DacModel.decode, modeling_dac.py:608-638).
 //
-// Every convolution is an implicit GEMM on the tcgen05 core (gemm_tc.cuh) over channels-last fp16 activations
-// [batch][time][channels]:  out[t, co] = sum_tap sum_ci x[t + shift(tap), ci] * W[co][tap][ci]
+// Every convolution is an implicit GEMM on tcgen05 (dac_conv.cuh) over channels-last fp16 activations
+// [batch][time][channels] (pitch == channels: no pad columns in memory, the TMA unit zero-fills up to the 64-channel
+// k-block):  out[t, co] = sum_tap sum_ci x[t + shift(tap), ci] * W[co][tap][ci]
 //   * Conv1d k=7, dilation d : 7 taps, shift = (tap-3)*d, zero padding outside [0,T)     (modeling_dac.py:181-186,417,426)
 //   * Conv1d k=1             : 1 tap
 //   * ConvTranspose1d k=2s, stride s, padding s/2 (:243-249): each output phase r has exactly two taps, so it is a
 //     2-tap conv with N = s*C_out columns (n = r*C_out + co) over rows j = 0..T_in, scattered to t = s*j + r - s/2.
-// The A operand of tap `tap` is the same activation tile shifted in time, gathered by cp.async with zero fill.
+// The A operand of tap `tap` is the same activation halo tile, read through a row-shifted UMMA descriptor.
 // Fused epilogue: + bias, (+ residual), store raw fp16 and/or Snake(alpha of the CONSUMER layer) fp16, so Snake1d
 // (:94-99) never makes its own pass over memory.  fp16 storage / fp32 accumulate mirrors the reference's CUDA autocast.
 #include "../../include/zonos_b200.h"
 #include "common.cuh"
-#include <cstdlib>
-
 #include "dac_conv.cuh"
-#include "gemm_tc.cuh"
 
 namespace zb {
-
-// ------------------------------------------------------------------------------------------------ A loader
-struct AConvTaps {
-  const uint8_t* base;  // fp16 [B][T][pitch]
-  int T;                // input rows per batch element
-  int m_rows;           // GEMM rows per batch element (T, or T+1 for the transposed conv)
-  int tiles_per_seq;    // ceil(m_rows / 128)
-  int cblocks;          // pitch / 64 : k-blocks per tap
-  int row_bytes;        // pitch * 2
-  int shift0, shift_step;  // time shift of tap i = shift0 + i*shift_step
-  __device__ int rows(int m_tile, int) const { return min(GEMM_BM, m_rows - (m_tile % tiles_per_seq) * GEMM_BM); }
-  __device__ const void* src(int r, int m_tile, int kb, int c, bool& valid) const {
-    const int b = m_tile / tiles_per_seq, tl = m_tile - b * tiles_per_seq;
-    const int tap = kb / cblocks, cb = kb - tap * cblocks;
-    const int t = tl * GEMM_BM + r + shift0 + tap * shift_step;
-    valid = (t >= 0) && (t < T);
-    const int tc = valid ? t : 0;
-    return base + ((size_t)b * T + tc) * row_bytes + cb * 128 + c * 16;
-  }
-};
-
-// ------------------------------------------------------------------------------------------------ epilogue
-__device__ __forceinline__ float snake_f(float x, float alpha, float inv_alpha) {
-  const float s = sinf(alpha * x);
-  return x + inv_alpha * (s * s);
-}
-
-template <int NT>
-struct EpiDac {
-  const float* bias;       // [n_total] (per output column; for the transposed conv: bias[co] repeated per phase)
-  const f16* resid;        // optional [B][T_out][pitch_out]
-  f16* out_raw;            // optional
-  f16* out_act;            // optional: Snake with the consumer's alpha
-  const float* alpha;      // [C_out]
-  const float* inv_alpha;  // [C_out] = 1/(alpha + 1e-9)
-  int T_out, tiles_per_seq, pitch_out, C_out, n_total;
-  int up, pad;             // transposed conv: stride and padding (up == 0: plain conv)
-  __device__ void operator()(int row, bool valid, int m_tile, int n_tile, float* acc) const {
-    if (!valid) return;
-    const int b = m_tile / tiles_per_seq, j = (m_tile - b * tiles_per_seq) * GEMM_BM + row;
-    // residual rows are streamed from HBM: issue all of this row's loads before anything depends on them
-    uint4 rbuf[NT / 8];
-    if (resid && up == 0 && j < T_out) {
-      const f16* rrow = resid + ((size_t)b * T_out + j) * pitch_out + n_tile * NT;
-#pragma unroll
-      for (int c = 0; c < NT; c += 8)
-        if (n_tile * NT + c < n_total) rbuf[c / 8] = __ldcs(reinterpret_cast<const uint4*>(rrow + c));
-    }
-#pragma unroll
-    for (int c = 0; c < NT; c += 8) {
-      const int n = n_tile * NT + c;
-      if (n >= n_total) break;
-      int t = j, co = n;
-      if (up > 0) {
-        const int r = n / C_out;
-        co = n - r * C_out;
-        t = up * j + r - pad;
-      }
-      if (t < 0 || t >= T_out) continue;
-      const size_t off = ((size_t)b * T_out + t) * pitch_out + co;
-      float v[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[c + i] + __ldg(bias + n + i)));
-      if (resid) {
-        const uint4 ru = (up == 0) ? rbuf[c / 8] : *reinterpret_cast<const uint4*>(resid + off);
-        const __half2* rh = reinterpret_cast<const __half2*>(&ru);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 rf = __half22float2(rh[i]);
-          v[2 * i] = __half2float(__float2half_rn(v[2 * i] + rf.x));
-          v[2 * i + 1] = __half2float(__float2half_rn(v[2 * i + 1] + rf.y));
-        }
-      }
-      if (out_raw) {
-        uint4 o;
-        __half2* oh = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-        *reinterpret_cast<uint4*>(out_raw + off) = o;
-      }
-      if (out_act) {
-        uint4 o;
-        __half2* oh = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          oh[i] = __floats2half2_rn(snake_f(v[2 * i], __ldg(alpha + co + 2 * i), __ldg(inv_alpha + co + 2 * i)),
-                                    snake_f(v[2 * i + 1], __ldg(alpha + co + 2 * i + 1), __ldg(inv_alpha + co + 2 * i + 1)));
-        *reinterpret_cast<uint4*>(out_act + off) = o;
-      }
-    }
-  }
-};
 
 // ------------------------------------------------------------------------------------------------ from_codes
 // z[b,t,:] = sum_k table[k][codes[b,k,t]][:]  with table[k][c] = out_proj_k(codebook_k[c]) + bias_k precomputed in fp32
@@ -192,11 +98,6 @@ static int sm_count() {
   }();
   return n;
 }
-static bool dac_use_gemm_tc() {
-  static const bool v = getenv("ZB200_DAC_GEMM_TC") != nullptr;  // the round-1 per-tap gather path, kept for A/B runs
-  return v;
-}
-
 template <int NT>
 static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
   const int T_in = L.t_mul_in * T;
@@ -210,7 +111,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   const int max_tpc = 256 / NT;
   a.n_groups = ceil_div(a.n_tiles, max_tpc);
   a.tpc = ceil_div(a.n_tiles, a.n_groups);
-  a.cblocks = L.pitch_in / 64, a.taps = L.taps, a.shift0 = L.shift0, a.shift_step = L.shift_step;
+  a.cblocks = ceil_div(L.pitch_in, 64), a.taps = L.taps, a.shift0 = L.shift0, a.shift_step = L.shift_step;
   const int s_last = L.shift0 + (L.taps - 1) * L.shift_step;
   a.smin = s_last < L.shift0 ? s_last : L.shift0;
   a.halo_rows = 128 + (s_last < L.shift0 ? L.shift0 - s_last : s_last - L.shift0);
@@ -264,41 +165,6 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   return ZB200_OK;
 }
 
-template <int NT>
-static int launch_dac_layer(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
-  const int T_in = L.t_mul_in * T;
-  const int m_rows = L.up > 0 ? T_in + 1 : T_in;
-  const int T_out = L.up > 0 ? T_in * L.up : T_in;
-  const int n_total = L.c_out * (L.up > 0 ? L.up : 1);
-  const int tiles_per_seq = ceil_div(m_rows, GEMM_BM);
-  // the pad columns of an A-operand region must be finite zeros (the matching weights are zero, but 0 * NaN = NaN)
-  if (L.pitch_out > L.c_out) {
-    const size_t rows = (size_t)batch * T_out;
-    for (int r : {L.raw_region, L.act_region})
-      if (r >= 0)
-        ZB_CHECK_CUDA(cudaMemset2DAsync((f16*)regions[r] + L.c_out, (size_t)L.pitch_out * 2, 0,
-                                        (size_t)(L.pitch_out - L.c_out) * 2, rows, st));
-  }
-  if (!dac_use_gemm_tc()) return launch_dac_conv<NT>(L, batch, T, regions, st);
-  AConvTaps al;
-  al.base = (const uint8_t*)regions[L.in_region], al.T = T_in, al.m_rows = m_rows, al.tiles_per_seq = tiles_per_seq;
-  al.cblocks = L.pitch_in / 64, al.row_bytes = L.pitch_in * 2, al.shift0 = L.shift0, al.shift_step = L.shift_step;
-  EpiDac<NT> epi;
-  epi.bias = L.bias;
-  epi.resid = L.resid_region >= 0 ? (const f16*)regions[L.resid_region] : nullptr;
-  epi.out_raw = L.raw_region >= 0 ? (f16*)regions[L.raw_region] : nullptr;
-  epi.out_act = L.act_region >= 0 ? (f16*)regions[L.act_region] : nullptr;
-  epi.alpha = L.alpha, epi.inv_alpha = L.inv_alpha;
-  epi.T_out = T_out, epi.tiles_per_seq = tiles_per_seq, epi.pitch_out = L.pitch_out, epi.C_out = L.c_out;
-  epi.n_total = n_total, epi.up = L.up, epi.pad = L.up / 2;
-  GemmCore g{};
-  g.Wp = L.w, g.k_blocks = L.taps * (L.pitch_in / 64), g.kb_per_split = g.k_blocks, g.splits = 1;
-  g.m_valid = batch * tiles_per_seq * GEMM_BM, g.partial_ws = nullptr, g.tickets = nullptr, g.stream_weights = 0;
-  cudaError_t e = launch_gemm_tc<NT, 4, 0, 2>(g, al, epi, ceil_div(n_total, NT), batch * tiles_per_seq, st);
-  if (e != cudaSuccess) return cuda_fail(e, "dac layer launch");
-  return ZB200_OK;
-}
-
 extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, int batch, int t, void* const* regions,
                                 int64_t region_halves, float* wav, void* stream) {
   ZB_REQUIRE(p && codes && regions && wav && batch > 0 && t > 0, "dac_decode: bad arguments");
@@ -307,12 +173,12 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
   // capacity check of every region use
   for (int i = 0; i < p->n_layers; ++i) {
     const zb200_dac_layer& L = p->layers[i];
-    ZB_REQUIRE(L.pitch_in % 64 == 0 && L.pitch_out % 8 == 0 && L.c_out % 8 == 0 && (L.tile_n == 64 || L.tile_n == 96),
+    ZB_REQUIRE(L.pitch_in % 8 == 0 && L.pitch_out % 8 == 0 && L.c_out % 8 == 0 && (L.tile_n == 64 || L.tile_n == 96),
                "dac_decode: layer %d has an unsupported shape", i);
     const int64_t T_in = (int64_t)L.t_mul_in * t, T_out = L.up > 0 ? T_in * L.up : T_in;
     ZB_REQUIRE(batch * T_in * L.pitch_in <= region_halves && batch * T_out * L.pitch_out <= region_halves,
                "dac_decode: layer %d does not fit the work regions (%lld halves)", i, (long long)region_halves);
-    ZB_REQUIRE((int64_t)batch * ceil_div((int)(L.up > 0 ? T_in + 1 : T_in), GEMM_BM) * ceil_div(L.c_out * (L.up > 0 ? L.up : 1), L.tile_n) < (1ll << 31),
+    ZB_REQUIRE((int64_t)batch * ceil_div((int)(L.up > 0 ? T_in + 1 : T_in), 128) * ceil_div(L.c_out * (L.up > 0 ? L.up : 1), L.tile_n) < (1ll << 31),
                "dac_decode: layer %d grid too large", i);
   }
   {
@@ -322,7 +188,7 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
   }
   for (int i = 0; i < p->n_layers; ++i) {
     const zb200_dac_layer& L = p->layers[i];
-    const int rc = L.tile_n == 96 ? launch_dac_layer<96>(L, batch, t, regions, st) : launch_dac_layer<64>(L, batch, t, regions, st);
+    const int rc = L.tile_n == 96 ? launch_dac_conv<96>(L, batch, t, regions, st) : launch_dac_conv<64>(L, batch, t, regions, st);
     if (rc != ZB200_OK) return rc;
   }
   {

@@ -34,7 +34,9 @@ class DacPlan(ctypes.Structure):
     ]
 
 
-def _pitch(c: int) -> int:
+def _kpad(c: int) -> int:
+    """Input channels of a tap are padded to whole 64-channel k-blocks in the PACKED WEIGHTS only; activations are stored
+    with pitch == channels and the TMA unit zero-fills the rest of the last k-block."""
     return ((c + 63) // 64) * 64
 
 
@@ -78,15 +80,16 @@ class DacDecoderB200:
             k, dil = taps_dil
             w = f32(prefix + ".weight")
             c_out, c_in, _ = w.shape
-            m = torch.zeros(c_out, k, pitch_in, device=self.device)
+            assert c_in == pitch_in and c_in % 8 == 0 and c_out % 8 == 0
+            m = torch.zeros(c_out, k, _kpad(c_in), device=self.device)
             m[:, :, :c_in] = w.permute(0, 2, 1)
             tile = 96 if c_out % 64 else 64
-            wp = ops.pack_weight(m.reshape(c_out, k * pitch_in).half(), tile_n=tile)
+            wp = ops.pack_weight(m.reshape(c_out, k * _kpad(c_in)).half(), tile_n=tile)
             b = f32(prefix + ".bias")
             self._keep += [wp, b]
             L = DacLayer()
             L.taps, L.shift0, L.shift_step, L.up = k, -(k // 2) * dil, dil if k > 1 else 0, 0
-            L.pitch_in, L.c_out, L.pitch_out, L.tile_n, L.t_mul_in = pitch_in, c_out, _pitch(c_out), tile, t_mul
+            L.pitch_in, L.c_out, L.pitch_out, L.tile_n, L.t_mul_in = pitch_in, c_out, c_out, tile, t_mul
             L.in_region, L.resid_region, L.raw_region, L.act_region = regions
             L.w, L.bias = wp.data_ptr(), b.data_ptr()
             if act_key is not None:
@@ -102,15 +105,16 @@ class DacDecoderB200:
             w = f32(prefix + ".weight")
             c_in, c_out, k = w.shape
             assert k == 2 * s and s % 2 == 0
-            m = torch.zeros(s, c_out, 2, pitch_in, device=self.device)
+            assert c_in == pitch_in and c_in % 8 == 0 and c_out % 8 == 0
+            m = torch.zeros(s, c_out, 2, _kpad(c_in), device=self.device)
             m[:, :, 0, :c_in] = w[:, :, :s].permute(2, 1, 0)
             m[:, :, 1, :c_in] = w[:, :, s:].permute(2, 1, 0)
-            wp = ops.pack_weight(m.reshape(s * c_out, 2 * pitch_in).half(), tile_n=64)
+            wp = ops.pack_weight(m.reshape(s * c_out, 2 * _kpad(c_in)).half(), tile_n=64)
             b = f32(prefix + ".bias").repeat(s).contiguous()
             self._keep += [wp, b]
             L = DacLayer()
             L.taps, L.shift0, L.shift_step, L.up = 2, 0, -1, s
-            L.pitch_in, L.c_out, L.pitch_out, L.tile_n, L.t_mul_in = pitch_in, c_out, _pitch(c_out), 64, t_mul
+            L.pitch_in, L.c_out, L.pitch_out, L.tile_n, L.t_mul_in = pitch_in, c_out, c_out, 64, t_mul
             L.in_region, L.resid_region, L.raw_region, L.act_region = regions
             L.w, L.bias = wp.data_ptr(), b.data_ptr()
             a, inv = snake(act_key)
@@ -119,13 +123,13 @@ class DacDecoderB200:
             return c_out
 
         # decoder.conv1 (k7): z (R_Z) -> Snake(block0.snake1) in R_IN
-        c = conv("decoder.conv1", (7, 1), _pitch(self.latent), 1, (R_Z, -1, -1, R_IN), "decoder.block.0.snake1.alpha")
+        c = conv("decoder.conv1", (7, 1), self.latent, 1, (R_Z, -1, -1, R_IN), "decoder.block.0.snake1.alpha")
         t_mul = 1
         for j, s in enumerate(strides):
             p = f"decoder.block.{j}."
-            c = conv_t(p + "conv_t1", s, _pitch(c), t_mul, (R_IN, -1, R_RAW_A, R_ACT), p + "res_unit1.snake1.alpha")
+            c = conv_t(p + "conv_t1", s, c, t_mul, (R_IN, -1, R_RAW_A, R_ACT), p + "res_unit1.snake1.alpha")
             t_mul *= s
-            pc = _pitch(c)
+            pc = c
             nxt = f"decoder.block.{j + 1}.snake1.alpha" if j + 1 < len(strides) else "decoder.snake1.alpha"
             plan = [(1, 1, R_RAW_A, R_RAW_B, R_ACT, p + "res_unit2.snake1.alpha"),
                     (2, 3, R_RAW_B, R_RAW_A, R_ACT, p + "res_unit3.snake1.alpha"),
@@ -143,15 +147,15 @@ class DacDecoderB200:
         plan.n_q, plan.n_codes, plan.latent, plan.n_layers = n_q, self.n_codes, self.latent, len(layers)
         plan.code_table, plan.layers = self.code_table.data_ptr(), self._layers
         plan.z_region, plan.final_region, plan.final_c = R_Z, R_IN, c
-        plan.final_pitch, plan.final_t_mul = _pitch(c), t_mul
+        plan.final_pitch, plan.final_t_mul = c, t_mul
         plan.final_w, plan.final_bias = self.final_w.data_ptr(), self.final_bias
         self.plan = plan
         # halves per code frame of the largest tensor a region ever holds
-        per_frame = [self.latent, _pitch(sd["decoder.conv1.weight"].shape[0])]
+        per_frame = [self.latent, sd["decoder.conv1.weight"].shape[0]]
         tm, cc = 1, sd["decoder.conv1.weight"].shape[0]
         for s in strides:
             tm, cc = tm * s, cc // 2
-            per_frame.append(tm * _pitch(cc))
+            per_frame.append(tm * cc)
         self.halves_per_frame = max(per_frame)
         torch.cuda.synchronize(self.device)
 
