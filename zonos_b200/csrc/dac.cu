@@ -11,6 +11,8 @@
 // Fused epilogue: + bias, (+ residual), store raw fp16 and/or Snake(alpha of the CONSUMER layer) fp16, so Snake1d
 // (:94-99) never makes its own pass over memory.  fp16 storage / fp32 accumulate mirrors the reference's CUDA autocast.
 #include "../../include/zonos_b200.h"
+#include <cstdio>
+
 #include "common.cuh"
 #include "dac_conv.cuh"
 
@@ -160,8 +162,29 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   }
   const int smem = a.sa * a.a_stage_bytes + a.sw * a.w_stage_bytes + DC_BAR_BYTES + 1024;
   const int grid = a.total_tiles < sm_count() ? a.total_tiles : sm_count();
+#ifdef SK_TRACE
+  static long long* trace_buf = nullptr;
+  if (!trace_buf) cudaMalloc(&trace_buf, 256 * 8 * sizeof(long long));
+  cudaMemsetAsync(trace_buf, 0, 256 * 8 * sizeof(long long), st);
+  a.trace = trace_buf;
+#endif
   kern<<<grid, DC_THREADS, smem, st>>>(xmap, a);
   ZB_CHECK_LAUNCH("dac_conv_kernel");
+#ifdef SK_TRACE
+  {
+    static long long host[256 * 8];
+    cudaStreamSynchronize(st);
+    cudaMemcpy(host, trace_buf, sizeof(host), cudaMemcpyDeviceToHost);
+    double m[8] = {0};
+    for (int c = 0; c < grid; ++c)
+      for (int k = 0; k < 8; ++k) m[k] += (double)host[c * 8 + k] / grid;
+    const double tiles = (double)a.total_tiles / grid;
+    fprintf(stderr, "[dac trace] N=%d taps=%d cb=%d res=%d sa=%d sw=%d tiles/cta=%.1f | per tile (clk): mma wait t_empty %.0f a_full %.0f w_full %.0f total %.0f"
+            " | epi wait t_full %.0f total %.0f | prodA wait a_empty %.0f total %.0f\n",
+            a.n_total, a.taps, a.cblocks, a.w_resident, a.sa, a.sw, tiles, m[0] / tiles, m[1] / tiles, m[2] / tiles, m[3] / tiles,
+            m[4] / tiles, m[5] / tiles, m[6] / tiles, m[7] / tiles);
+  }
+#endif
   return ZB200_OK;
 }
 

@@ -29,8 +29,9 @@ typedef __half f16;
 constexpr int DC_THREADS = 352;
 constexpr int DC_EPI_THREADS = 256;
 constexpr int DC_MAX_SA = 4;    // activation ring depth
+constexpr int DC_PF_TILES = 3;  // L2 prefetch distance of the activation boxes, in tiles of this CTA
 constexpr int DC_MAX_SW = 16;   // weight ring depth / resident k-blocks
-constexpr int DC_SMEM_BYTES = 220 * 1024;
+constexpr int DC_SMEM_BYTES = 216 * 1024;  // dynamic; + 6.6 KB static epilogue constants < 227 KB
 constexpr int DC_BAR_BYTES = (2 * DC_MAX_SA + 2 * DC_MAX_SW + 4) * 8 + 16;
 
 struct DacConvArgs {
@@ -55,6 +56,7 @@ struct DacConvArgs {
   const float* inv_alpha;  // [C_out] = 1/(alpha + 1e-9)
   int T_out, pitch_out, C_out, n_total;
   int up, pad;             // transposed conv: stride and padding (up == 0: plain conv)
+  long long* trace;        // SK_TRACE builds: [grid][8] cycle counters
 };
 
 // 3-D tiled TMA load (SASS: UTMALDG), completion counted in bytes on an mbarrier.  Coordinates are signed: elements
@@ -79,6 +81,24 @@ __device__ __forceinline__ float snake_fast(float x, float alpha, float inv_alph
   return fmaf(inv_alpha, s * s, x);
 }
 
+// Same box, L2 only (SASS: UTMAPF): pulls a later tile's activations out of HBM while the ring is still occupied.
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* map, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(reinterpret_cast<uint64_t>(map)),
+               "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+
+#ifdef SK_TRACE
+#define DC_TIMED_WAIT(counter, bar, parity) \
+  do {                                      \
+    const long long _t0 = clock64();        \
+    mbar_wait(bar, parity);                 \
+    counter += clock64() - _t0;             \
+  } while (0)
+#else
+#define DC_TIMED_WAIT(counter, bar, parity) mbar_wait(bar, parity)
+#endif
+
 __device__ __forceinline__ void dc_tile_coords(const DacConvArgs& a, int tile, int& m_tile, int& group) {
   m_tile = tile / a.n_groups;
   group = tile - m_tile * a.n_groups;
@@ -99,6 +119,10 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
   uint64_t* t_empty = t_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
+  // per-column epilogue constants of the current column group (two copies: tiles alternate when n_groups > 1)
+  __shared__ __align__(16) float s_bias[2][256], s_alpha[2][256], s_inv[2][256];
+  __shared__ int2 s_grp[2][32];  // per 8 columns: (time offset r - pad of the transposed conv's phase, output channel)
+
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kb_per_tile = a.cblocks * a.taps;
 
@@ -118,84 +142,115 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
     // ---------------------------------------------------------------- activation halo tiles: one TMA per channel block
     if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&xmap)) : "memory");
-      int g = 0;  // running stage counter
+      int s = 0;
+      uint32_t empty_parity = 1;  // ring slot and the parity of its "empty" barrier (flips each time the ring wraps)
+      [[maybe_unused]] long long tr_wait0 = 0, tr_start = clock64();
+      // The ring holds at most one or two tiles' worth of halo boxes when the weights are resident, far less than the
+      // HBM latency-bandwidth product: boxes of the tiles DC_PF_TILES ahead are prefetched into L2.
+      auto prefetch_tile = [&](int tile) {
+        if (tile >= a.total_tiles) return;
+        int m_tile, group;
+        dc_tile_coords(a, tile, m_tile, group);
+        if (a.n_groups > 1 && group != 0) return;  // the other column groups of an m-tile find it in L2 anyway
+        const int b = m_tile / a.tiles_per_seq, t0 = (m_tile - b * a.tiles_per_seq) * 128;
+        for (int cb = 0; cb < a.cblocks; ++cb) tma_prefetch_3d(&xmap, cb * 64, t0 + a.smin, b);
+      };
+      for (int k = 1; k < DC_PF_TILES; ++k) prefetch_tile(blockIdx.x + k * gridDim.x);
       for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+        prefetch_tile(tile + DC_PF_TILES * gridDim.x);
         int m_tile, group;
         dc_tile_coords(a, tile, m_tile, group);
         const int b = m_tile / a.tiles_per_seq, t0 = (m_tile - b * a.tiles_per_seq) * 128;
-        for (int cb = 0; cb < a.cblocks; ++cb, ++g) {
-          const int s = g % a.sa;
-          mbar_wait(&a_empty[s], ((g / a.sa) & 1) ^ 1);
+        for (int cb = 0; cb < a.cblocks; ++cb) {
+          DC_TIMED_WAIT(tr_wait0, &a_empty[s], empty_parity);
           mbar_arrive_expect_tx(&a_full[s], a.halo_rows * 128);
           tma_load_3d(a_ring + s * a.a_stage_bytes, &xmap, cb * 64, t0 + a.smin, b, &a_full[s]);
+          if (++s == a.sa) s = 0, empty_parity ^= 1;
         }
       }
+#ifdef SK_TRACE
+      if (a.trace) a.trace[blockIdx.x * 8 + 6] = tr_wait0, a.trace[blockIdx.x * 8 + 7] = clock64() - tr_start;
+#endif
     }
   } else if (warp == 10) {
     // ---------------------------------------------------------------- weight k-blocks, in the order the MMAs use them
     if (lane == 0) {
-      int g = 0;
-      bool first = true;
+      int s = 0;
+      uint32_t empty_parity = 1;  // ring slot and the parity of its "empty" barrier (flips each time the ring wraps)
+      const size_t tile_stride = (size_t)kb_per_tile * (NT * 128);  // bytes between consecutive NT tiles of one k-block
       for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
-        if (a.w_resident && !first) break;
-        first = false;
-        int m_tile, group;
-        dc_tile_coords(a, tile, m_tile, group);
+        const int group = a.n_groups == 1 ? 0 : tile % a.n_groups;
         const int n_tile0 = group * a.tpc;
         const int tiles_here = min(a.tpc, a.n_tiles - n_tile0);
-        for (int cb = 0; cb < a.cblocks; ++cb)
-          for (int tap = 0; tap < a.taps; ++tap, ++g) {
-            const int s = g % a.sw;
-            if (!a.w_resident) mbar_wait(&w_empty[s], ((g / a.sw) & 1) ^ 1);
-            mbar_arrive_expect_tx(&w_full[s], tiles_here * NT * 128);
-            const int kb = tap * a.cblocks + cb;
+        const uint32_t stage_tx = tiles_here * NT * 128;
+        const uint8_t* wg = a.Wp + (size_t)n_tile0 * tile_stride;
+        for (int cb = 0; cb < a.cblocks; ++cb) {
+          const uint8_t* src = wg + (size_t)cb * (NT * 128);  // k-block index = tap*cblocks + cb
+          for (int tap = 0; tap < a.taps; ++tap, src += (size_t)a.cblocks * (NT * 128)) {
+            if (!a.w_resident) mbar_wait(&w_empty[s], empty_parity);
+            mbar_arrive_expect_tx(&w_full[s], stage_tx);
+            uint8_t* dst = w_ring + s * a.w_stage_bytes;
             for (int jt = 0; jt < tiles_here; ++jt)
-              bulk_g2s(w_ring + s * a.w_stage_bytes + jt * NT * 128,
-                       a.Wp + ((size_t)(n_tile0 + jt) * kb_per_tile + kb) * (NT * 128), NT * 128, &w_full[s]);
+              bulk_g2s(dst + jt * NT * 128, src + jt * tile_stride, NT * 128, &w_full[s]);
+            if (++s == a.sw) s = 0, empty_parity ^= 1;
           }
+        }
+        if (a.w_resident) break;  // the whole filter is in shared memory now and stays
       }
     }
   } else if (warp == 9) {
     // ---------------------------------------------------------------- MMA issuer
     if (lane == 0) {
-      int ga = 0, gw = 0, it = 0;
+      int sa = 0, sw = 0, it = 0;
+      uint32_t a_parity = 0, w_parity = 0;
+      const uint32_t a_ring_addr = smem_u32(a_ring), w_ring_addr = smem_u32(w_ring);
+      const uint32_t tap0_off = (a.shift0 - a.smin) * 128;
+      const int tap_step = a.shift_step * 128;
+      [[maybe_unused]] long long tr_te = 0, tr_af = 0, tr_wf = 0, tr_start = clock64();
       for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
-        int m_tile, group;
-        dc_tile_coords(a, tile, m_tile, group);
+        const int group = a.n_groups == 1 ? 0 : tile % a.n_groups;
         const int tiles_here = min(a.tpc, a.n_tiles - group * a.tpc);
         const uint32_t idesc = umma_idesc(128, tiles_here * NT, 0);
         const int buf = it & 1;
-        mbar_wait(&t_empty[buf], ((it >> 1) & 1) ^ 1);
+        DC_TIMED_WAIT(tr_te, &t_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         uint32_t accumulate = 0;
-        for (int cb = 0; cb < a.cblocks; ++cb, ++ga) {
-          const int sa = ga % a.sa;
-          mbar_wait(&a_full[sa], (ga / a.sa) & 1);
-          const uint32_t a_addr = smem_u32(a_ring + sa * a.a_stage_bytes);
-          for (int tap = 0; tap < a.taps; ++tap, ++gw) {
-            const int sw = gw % a.sw;
-            if (!a.w_resident || it == 0) mbar_wait(&w_full[sw], (gw / a.sw) & 1);
+        for (int cb = 0; cb < a.cblocks; ++cb) {
+          DC_TIMED_WAIT(tr_af, &a_full[sa], a_parity);
+          uint32_t a_addr = a_ring_addr + sa * a.a_stage_bytes + tap0_off;
+          for (int tap = 0; tap < a.taps; ++tap, a_addr += tap_step) {
+            if (!a.w_resident || it == 0) DC_TIMED_WAIT(tr_wf, &w_full[sw], w_parity);
             tc_fence_after();
-            const uint64_t adesc = umma_desc_sw128(a_addr + (a.shift0 + tap * a.shift_step - a.smin) * 128);
-            const uint64_t bdesc = umma_desc_sw128(smem_u32(w_ring + sw * a.w_stage_bytes));
+            const uint64_t adesc = umma_desc_sw128(a_addr);
+            const uint64_t bdesc = umma_desc_sw128(w_ring_addr + sw * a.w_stage_bytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accumulate);
               accumulate = 1;
             }
             if (!a.w_resident) umma_commit(&w_empty[sw]);
+            if (++sw == a.sw) sw = 0, w_parity ^= 1;
           }
           umma_commit(&a_empty[sa]);
+          if (++sa == a.sa) sa = 0, a_parity ^= 1;
         }
         umma_commit(&t_full[buf]);
       }
+#ifdef SK_TRACE
+      if (a.trace) {
+        long long* o = a.trace + blockIdx.x * 8;
+        o[0] = tr_te, o[1] = tr_af, o[2] = tr_wf, o[3] = clock64() - tr_start;
+      }
+#endif
     }
   } else {
     // ---------------------------------------------------------------- epilogue: TMEM -> bias/residual/Snake -> fp16 rows
     const int q = warp & 3, par = warp >> 2;
     const int row = q * 32 + lane;
+    const bool has_resid = a.resid != nullptr && a.up == 0;
     int it = 0;
+    [[maybe_unused]] long long tr_tf = 0, tr_start = clock64();
     for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
       int m_tile, group;
       dc_tile_coords(a, tile, m_tile, group);
@@ -205,9 +260,9 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
       const bool row_valid = j < a.m_rows;
       const int buf = it & 1;
       const int n_chunks = n_cols >> 4;
+      const int n_mine = (n_chunks - par + 1) >> 1;  // 16-column chunks par, par+2, ...
       // the residual row is streamed from HBM: issue this thread's loads before waiting for the accumulator
       uint4 rbuf[16];
-      const bool has_resid = a.resid != nullptr && a.up == 0;
       if (has_resid && row_valid) {
         const f16* rrow = a.resid + ((size_t)b * a.T_out + j) * a.pitch_out + n0;
 #pragma unroll
@@ -219,17 +274,35 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
           }
         }
       }
-      mbar_wait(&t_full[buf], (it >> 1) & 1);
+      // per-column constants of this tile's column group -> shared memory (the L1 is a few KB next to 200+ KB of
+      // rings and is flushed by the streaming stores, so per-use global loads would each go to L2)
+      const int cbuf = a.n_groups == 1 ? 0 : buf;
+      if (a.n_groups > 1 || it == 0) {
+        const int col = tid, n = n0 + col;
+        if (col < n_cols) {
+          const bool ok = n < a.n_total;
+          int co = n, r = 0;
+          if (a.up > 0 && ok) r = n / a.C_out, co = n - r * a.C_out;
+          s_bias[cbuf][col] = ok ? __ldg(a.bias + n) : 0.f;
+          s_alpha[cbuf][col] = ok && a.out_act ? __ldg(a.alpha + co) : 0.f;
+          s_inv[cbuf][col] = ok && a.out_act ? __ldg(a.inv_alpha + co) : 0.f;
+          if ((col & 7) == 0) s_grp[cbuf][col >> 3] = make_int2(ok ? (a.up > 0 ? r - a.pad : 0) : (1 << 30), co);
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+      }
+      DC_TIMED_WAIT(tr_tf, &t_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
+      float acc[2][16];
+      tmem_ld16(taddr + par * 16, acc[0]);
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
+        if (c >= n_mine) break;
         const int ch = 2 * c + par;
-        if (ch >= n_chunks) break;
-        float acc[16];
-        tmem_ld16(taddr + ch * 16, acc);
         tmem_ld_wait();
-        if (c == 7 || ch + 2 >= n_chunks) {  // last TMEM read of this warp: hand the accumulator back to the MMA warp
+        if (c + 1 < n_mine) {
+          tmem_ld16(taddr + (ch + 2) * 16, acc[(c + 1) & 1]);  // in flight while this chunk is processed
+        } else {  // last TMEM read of this warp: hand the accumulator back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&t_empty[buf]);
@@ -237,22 +310,17 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
         if (!row_valid) continue;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int n = n0 + ch * 16 + h * 8;
-          if (n >= a.n_total) break;
-          int t = j, co = n;
-          if (a.up > 0) {
-            const int r = n / a.C_out;
-            co = n - r * a.C_out;
-            t = a.up * j + r - a.pad;
-          }
+          const int col = ch * 16 + h * 8;
+          const int2 grp = s_grp[cbuf][col >> 3];
+          const int t = a.up > 0 ? a.up * j + grp.x : j + grp.x;
           if (t < 0 || t >= a.T_out) continue;
-          const size_t off = ((size_t)b * a.T_out + t) * a.pitch_out + co;
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.bias + n));
-          const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.bias + n + 4));
+          const size_t off = ((size_t)b * a.T_out + t) * a.pitch_out + grp.y;
+          const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col]);
+          const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col + 4]);
           const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
           float v[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[h * 8 + i] + bb[i]));
+          for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[c & 1][h * 8 + i] + bb[i]));
           if (has_resid) {
             const uint4 ru = rbuf[2 * c + h];
             const __half2* rh = reinterpret_cast<const __half2*>(&ru);
@@ -271,10 +339,10 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
             *reinterpret_cast<uint4*>(a.out_raw + off) = o;
           }
           if (a.out_act) {
-            const float4 a0 = __ldg(reinterpret_cast<const float4*>(a.alpha + co));
-            const float4 a1 = __ldg(reinterpret_cast<const float4*>(a.alpha + co + 4));
-            const float4 i0 = __ldg(reinterpret_cast<const float4*>(a.inv_alpha + co));
-            const float4 i1 = __ldg(reinterpret_cast<const float4*>(a.inv_alpha + co + 4));
+            const float4 a0 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col + 4]);
+            const float4 i0 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col]);
+            const float4 i1 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col + 4]);
             const float al[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
             const float ia[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
             uint4 o;
@@ -287,11 +355,10 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
           }
         }
       }
-      if (n_chunks <= par) {  // (cannot happen: n_cols >= 32) keep the barrier protocol whole anyway
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&t_empty[buf]);
-      }
     }
+#ifdef SK_TRACE
+    if (a.trace && tid == 0) a.trace[blockIdx.x * 8 + 4] = tr_tf, a.trace[blockIdx.x * 8 + 5] = clock64() - tr_start;
+#endif
     tc_fence_before();
   }
   __syncthreads();
