@@ -98,6 +98,16 @@ __device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* map, int c0, 
 #else
 #define DC_TIMED_WAIT(counter, bar, parity) mbar_wait(bar, parity)
 #endif
+#ifdef SK_TRACE
+#define DC_TIMED_WAIT_RELAXED(counter, bar, parity) \
+  do {                                              \
+    const long long _t0 = clock64();                \
+    mbar_wait_relaxed(bar, parity);                 \
+    counter += clock64() - _t0;                     \
+  } while (0)
+#else
+#define DC_TIMED_WAIT_RELAXED(counter, bar, parity) mbar_wait_relaxed(bar, parity)
+#endif
 
 __device__ __forceinline__ void dc_tile_coords(const DacConvArgs& a, int tile, int& m_tile, int& group) {
   m_tile = tile / a.n_groups;
@@ -200,12 +210,16 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
     }
   } else if (warp == 9) {
     // ---------------------------------------------------------------- MMA issuer
-    if (lane == 0) {
+    // The whole warp runs the loops (warp-uniform control flow keeps the descriptors in uniform registers and the
+    // issue path short: the single issuing thread is the pacing resource of the small-N layers); one elected lane
+    // issues the MMAs and commits.
+    {
       int sa = 0, sw = 0, it = 0;
       uint32_t a_parity = 0, w_parity = 0;
       const uint32_t a_ring_addr = smem_u32(a_ring), w_ring_addr = smem_u32(w_ring);
       const uint32_t tap0_off = (a.shift0 - a.smin) * 128;
       const int tap_step = a.shift_step * 128;
+      const bool leader = elect_one();
       [[maybe_unused]] long long tr_te = 0, tr_af = 0, tr_wf = 0, tr_start = clock64();
       for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
         const int group = a.n_groups == 1 ? 0 : tile % a.n_groups;
@@ -222,23 +236,28 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
           for (int tap = 0; tap < a.taps; ++tap, a_addr += tap_step) {
             if (!a.w_resident || it == 0) DC_TIMED_WAIT(tr_wf, &w_full[sw], w_parity);
             tc_fence_after();
-            const uint64_t adesc = umma_desc_sw128(a_addr);
-            const uint64_t bdesc = umma_desc_sw128(w_ring_addr + sw * a.w_stage_bytes);
+            if (leader) {
+              const uint64_t adesc = umma_desc_sw128(a_addr);
+              const uint64_t bdesc = umma_desc_sw128(w_ring_addr + sw * a.w_stage_bytes);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accumulate);
-              accumulate = 1;
+              for (int k = 0; k < 4; ++k) {
+                umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accumulate);
+                accumulate = 1;
+              }
+              if (!a.w_resident) umma_commit(&w_empty[sw]);
             }
-            if (!a.w_resident) umma_commit(&w_empty[sw]);
+            __syncwarp();
             if (++sw == a.sw) sw = 0, w_parity ^= 1;
           }
-          umma_commit(&a_empty[sa]);
+          if (leader) umma_commit(&a_empty[sa]);
+          __syncwarp();
           if (++sa == a.sa) sa = 0, a_parity ^= 1;
         }
-        umma_commit(&t_full[buf]);
+        if (leader) umma_commit(&t_full[buf]);
+        __syncwarp();
       }
 #ifdef SK_TRACE
-      if (a.trace) {
+      if (a.trace && leader) {
         long long* o = a.trace + blockIdx.x * 8;
         o[0] = tr_te, o[1] = tr_af, o[2] = tr_wf, o[3] = clock64() - tr_start;
       }
