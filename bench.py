@@ -22,6 +22,8 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 FRAME_RATE = 44100 / 512  # 86.1328 frames per audio second
+# attn_decode_kernel DRAM traffic per launch measured by ncu: key (sequences incl. CFG, kv heads, context)
+NCU_ATTN_TRAFFIC = {(128, 4, 1432): 390_500_000}
 C3_SAMPLING = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0,
                    repetition_penalty_window=2, temperature=1.0)
 
@@ -39,6 +41,7 @@ def parse():
     ap.add_argument("--shape", default="real", choices=["real", "tiny"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-dac", action="store_true")
     ap.add_argument("--cpu-frames", type=int, default=32, help="decode frames in the CPU baseline sample")
     return ap.parse_args()
 
@@ -189,9 +192,56 @@ def attn_roofline(shape, batch, ctx, device, hbm_peak):
     ms = e0.elapsed_time(e1) / (reps * layers)
     algo = n_seq * Hkv * ctx * 128 * 2 * 2 + 2 * n_seq * H * 128 * 2  # K+V rows read once, q in, out
     achieved = algo / (ms * 1e-3) / 1e9
+    # DRAM bytes of one launch from the committed `ncu --set full` capture (dram__bytes_read.sum + dram__bytes_write.sum);
+    # only valid for the configuration that was captured, otherwise null.
+    traffic = None
+    if (n_seq, Hkv, ctx) in NCU_ATTN_TRAFFIC:
+        traffic = NCU_ATTN_TRAFFIC[(n_seq, Hkv, ctx)]
     return {"kernel": "attn_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
-            "frac": round(achieved / hbm_peak, 4), "traffic": None, "bytes_per_launch": algo, "ms_per_launch": round(ms, 5),
-            "ctx": ctx, "nsplit": nsplit}
+            "frac": round(achieved / hbm_peak, 4), "traffic": traffic,
+            "traffic_source": "profiles/r01b_ncu_full_decode_b64.txt" if traffic else None,
+            "bytes_per_launch": algo, "ms_per_launch": round(ms, 5), "ctx": ctx, "nsplit": nsplit}
+
+
+def dac_section(device, batch, frames):
+    """BASELINE configs[3] (C4): DACAutoencoder.decode of `batch` x `frames` synthetic codes -> fp32 waveforms, device
+    resident and end to end (codes from pinned host memory, waveform back to the host)."""
+    from oracle import shapes as oshapes  # synthetic weights only (the decoder under test is the CUDA one)
+    from zonos_b200.autoencoder import DACAutoencoder
+
+    try:
+        tf_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+    except Exception:
+        tf_peak = None
+    ae = DACAutoencoder().to(device)
+    ae.load_dac_state_dict(oshapes.synth_dac_weights(seed=7))
+    g = torch.Generator(device=device).manual_seed(5)
+    codes = torch.randint(0, 1024, (batch, 9, frames), generator=g, device=device)
+    codes_host = codes.cpu().pin_memory()
+    for _ in range(2):
+        wav = ae.decode(codes)
+    wav_host = torch.empty(wav.shape, dtype=wav.dtype).pin_memory()
+    torch.cuda.synchronize()
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    reps = 3
+    e0.record()
+    for _ in range(reps):
+        wav = ae.decode(codes)
+    e1.record()
+    for _ in range(reps):
+        wav = ae.decode(codes_host.to(device, non_blocking=True))
+        wav_host.copy_(wav, non_blocking=True)
+    e2.record()
+    torch.cuda.synchronize()
+    ms, ms_e2e = e0.elapsed_time(e1) / reps, e1.elapsed_time(e2) / reps
+    flops = 1608302592 * batch * frames  # conv MACs x 2 per code frame (DESIGN.md, DAC layer table)
+    audio_s = batch * frames / FRAME_RATE
+    del ae
+    return {"workload": f"DAC 44.1 kHz decode, batch {batch} x {frames} frames", "ms": round(ms, 1),
+            "audio_s_per_s": round(audio_s / (ms * 1e-3), 1), "e2e_audio_s_per_s": round(audio_s / (ms_e2e * 1e-3), 1),
+            "tflops": round(flops / ms / 1e9, 1), "bound": "tensor",
+            "frac_of_sustained_bf16_peak": None if tf_peak is None else round(flops / ms / 1e9 / tf_peak, 4),
+            "launches": 31 * reps * 2, "finite": bool(torch.isfinite(wav_host).all())}
 
 
 def latency_batch1(model, shape, args, device, hbm_peak):
@@ -363,9 +413,12 @@ def main_b200(args, world, rank, local):
     }
     if not args.no_latency:
         line["latency_batch1"] = latency_batch1(model, shape, args, device, hbm_peak)
-    if world == 1 and not args.no_cpu_baseline:
-        del model
+    del model
+    torch.cuda.empty_cache()
+    if world == 1 and not args.no_dac:
+        line["dac_decode"] = dac_section(device, B, args.max_new_tokens)
         torch.cuda.empty_cache()
+    if world == 1 and not args.no_cpu_baseline:
         frames = args.cpu_frames
         v, dt, cores = cpu_reference_sample(frames, args.shape)
         line["cpu_baseline"] = {"value": round(v, 5), "unit": "audio-s/s", "cores": cores, "kind": "port",
