@@ -6,7 +6,7 @@ timeout 900 python -m pytest tests -x -q -m gpu --deselect tests/test_gpu_kernel
 i=0
 for setting in "" "$@"; do
   i=$((i+1))
-  env $setting timeout 400 python bench.py --max-new-tokens 400 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/b_$i.log 2>&1
+  env $setting timeout 400 python bench.py --max-new-tokens 400 --steps 1 --warmup 1 --no-cpu-baseline --no-dac > gpurun_out/b_$i.log 2>&1
   echo "bench[$setting] rc=$?"
   tail -1 gpurun_out/b_$i.log | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['decode_step']['ms_per_frame'], d['latency_batch1']['p50_ms'])"
 done

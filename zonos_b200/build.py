@@ -18,6 +18,10 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "--use_fast_math=false",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--expt-relaxed-constexpr",
 ]
+if os.environ.get("ZB200_DBG_NOA"):  # what-if experiment: the decode GEMMs skip their activation loads (wrong results)
+    NVCC_FLAGS.append("-DSK_DBG_NOA")
+if os.environ.get("ZB200_DBG_NOMMA"):  # what-if experiment: the decode GEMMs issue no MMAs (wrong results)
+    NVCC_FLAGS.append("-DSK_DBG_NOMMA")
 if os.environ.get("ZB200_TRACE"):
     NVCC_FLAGS.append("-DSK_TRACE")
 NVCC_FLAGS.remove("--use_fast_math=false")  # precise math on purpose: the sampler/Snake must match the reference

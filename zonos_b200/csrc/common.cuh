@@ -126,6 +126,11 @@ __device__ __forceinline__ uint64_t l2_policy_evict_last() {
   return p;
 }
 
+// Pull `bytes` (multiple of 16) of global memory into L2 without a destination (SASS: UBLKPF).
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gmem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+}
+
 // 16-byte cp.async (LDGSTS), L2-only caching; src_bytes == 0 zero-fills the destination.
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, uint32_t src_bytes = 16) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(src_bytes)

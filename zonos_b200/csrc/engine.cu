@@ -16,6 +16,10 @@
 #include <cstdlib>
 
 using namespace zb;
+#ifdef SK_TRACE
+extern unsigned long long* g_trace_buf;  // ops.cu: debug timeline of the weight-streaming GEMMs
+extern int g_trace_next;
+#endif
 
 struct zb200_engine {
   zb200_engine_desc d;
@@ -92,8 +96,12 @@ struct SkPlan {
   int grid, splits;
   bool prefer_k1;
 };
+static int big_m_ctas_per_sm() {  // experiment knob: CTAs per SM the planners assume at rows > 32
+  static const int v = getenv("ZB200_SK_CAP2") ? 2 : 1;
+  return v;
+}
 SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
-  const int cap = sms * (rows <= 32 ? 2 : 1);
+  const int cap = sms * (rows <= 32 ? 2 : big_m_ctas_per_sm());
   SkPlan p{cap, 1, false};
   int mode = skinny_mode(rows, n_tiles, k_blocks);
   int groups = n_tiles / skinny_tg(mode);
@@ -116,7 +124,7 @@ SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
   return p;
 }
 SkPlan plan_deferred(int sms, int rows, int n_tiles, int k_blocks, int64_t ws_floats, int n) {
-  const int cap = sms * (rows <= 32 ? 2 : 1);
+  const int cap = sms * (rows <= 32 ? 2 : big_m_ctas_per_sm());
   const int mode = skinny_mode(rows, n_tiles, k_blocks);
   const int groups = n_tiles / skinny_tg(mode), kbu = k_blocks / skinny_kg(mode);
   int s = 1;
@@ -129,17 +137,46 @@ SkinnyCore sk_core(const zb200_engine_desc& d, const void* w, int n_tiles, int r
   SkinnyCore g{};
   g.Wp = w, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = rows;
   g.partial_ws = d.gemm_ws, g.tickets = d.gemm_tickets, g.n_splits = 1, g.trace = nullptr, g.trace_id = -1;
+  g.next = NextW{};
+#ifdef SK_TRACE
+  g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
+#endif
   return g;
+}
+
+// Descriptors of "the GEMM after this one" for the in-kernel L2 prefetch of its first weight bytes (gemm_skinny.cuh).
+static int nextw_bytes(int rows) {
+  static const int kb = getenv("ZB200_NEXTW_KB") ? atoi(getenv("ZB200_NEXTW_KB")) : -1;
+  (void)rows;
+  return kb > 0 ? kb * 1024 : 0;  // off by default: measured neutral at batch 64 and batch 1 (experiments)
+}
+NextW next_skinny(const void* w, int rows, int n_tiles, int k, int grid, bool prefer_k1) {
+  const int mode = skinny_mode(rows, n_tiles, k / 64, prefer_k1);
+  const int units = (n_tiles / skinny_tg(mode)) * ((k / 64) / skinny_kg(mode));
+  NextW nx{(const uint8_t*)w, n_tiles, k / 64, std::min(grid, units), skinny_tg(mode), skinny_kg(mode), nextw_bytes(rows)};
+  if (nx.bytes <= 0) nx.wp = nullptr;
+  return nx;
+}
+int swap_grid(const zb200_engine* e, int n_tiles, int k) {
+  const int groups = (n_tiles + 1) / 2, kbu = (k / 64) / 2, cap = 2 * e->sk_sms;
+  return groups * std::max(1, std::min(std::min(SWP_MAXC, kbu), cap / groups));
+}
+NextW next_swap(const zb200_engine* e, const void* w, int rows, int n_tiles, int k) {
+  NextW nx{(const uint8_t*)w, n_tiles, k / 64, swap_grid(e, n_tiles, k), 2, 2, nextw_bytes(rows)};
+  if (nx.bytes <= 0) nx.wp = nullptr;
+  return nx;
 }
 
 // Ticketed-epilogue GEMM: the weight-streaming kernel for the decode step (rows <= 128), the tiled kernel otherwise.
 template <class ALoader, class Epilogue>
 cudaError_t gemm_any(const zb200_engine* e, const void* w, int n_tiles, int rows, int k, const ALoader& al,
-                     const Epilogue& epi, cudaStream_t st) {
+                     const Epilogue& epi, cudaStream_t st, const NextW& nx = NextW{}) {
   const zb200_engine_desc& d = e->d;
   if (rows <= GEMM_BM && e->sk_sms > 0) {
     const SkPlan p = plan_ticketed(e->sk_sms, rows, n_tiles, k / 64);
-    return launch_gemm_skinny(sk_core(d, w, n_tiles, rows, k), al, epi, p.grid, st, p.prefer_k1);
+    SkinnyCore g = sk_core(d, w, n_tiles, rows, k);
+    g.next = nx;
+    return launch_gemm_skinny(g, al, epi, p.grid, st, p.prefer_k1);
   }
   GemmCore g = make_core(d, w, n_tiles, rows, k);
   return launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, ceil_div(rows, GEMM_BM), st);
@@ -178,13 +215,12 @@ int join_side(zb200_engine* e, cudaStream_t st) {
 
 template <class ALoader, class Epilogue>
 cudaError_t gemm_swap(const zb200_engine* e, const void* w, int n_tiles, int rows, int k, const ALoader& al,
-                      const Epilogue& epi, cudaStream_t st) {
+                      const Epilogue& epi, cudaStream_t st, const NextW& nx = NextW{}) {
   SwapCore g{};
   g.Wp = w, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = rows;
   g.partial_ws = e->d.gemm_ws, g.tickets = e->d.gemm_tickets, g.trace = nullptr, g.trace_id = -1;
-  const int groups = (n_tiles + 1) / 2, kbu = g.k_blocks / 2, cap = 2 * e->sk_sms;
-  const int s = std::max(1, std::min(std::min(SWP_MAXC, kbu), cap / groups));
-  return launch_gemm_swap(g, al, epi, groups * s, st);
+  g.next = nx;
+  return launch_gemm_swap(g, al, epi, swap_grid(e, n_tiles, k), st);
 }
 
 // Decode step with rows = 2B <= 128: every projection streams its weights through gemm_skinny; out_proj and fc2 leave
@@ -203,6 +239,29 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
   const SkPlan p_qkv = plan_deferred(e->sk_sms, rows, (hd + 2 * kvd) / NT, dm / 64, d.gemm_ws_floats, hd + 2 * kvd);
   const SkPlan p_out = plan_deferred(e->sk_sms, rows, dm / NT, hd / 64, d.gemm_ws_floats, dm);
   const SkPlan p_fc2 = plan_deferred(e->sk_sms, rows, dm / NT, d.d_ff / 64, d.gemm_ws_floats, dm);
+  // what follows each GEMM in the step (for the L2 prefetch of its first weight bytes): out_proj -> fc1 -> fc2 -> next
+  // layer's in_proj (heads after the last layer).  in_proj -> out_proj is left out: the attention kernel in between
+  // streams the KV pages through L2.
+  const int qkv_tiles = (hd + 2 * kvd) / NT, fc1_tiles = d.d_ff / (NT / 2), head_tiles = d.n_q * (d.head_rows_padded / NT);
+  auto nx_fc1 = [&](int l) {
+    const void* w = (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride;
+    if (swap_mask & 4) return next_swap(e, w, rows, fc1_tiles, dm);
+    const SkPlan p = plan_ticketed(e->sk_sms, rows, fc1_tiles, dm / 64);
+    return next_skinny(w, rows, fc1_tiles, dm, p.grid, p.prefer_k1);
+  };
+  auto nx_fc2 = [&](int l) { return next_skinny((const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, rows, dm / NT, d.d_ff, p_fc2.grid, false); };
+  auto nx_qkv = [&](int l) {
+    if (l >= d.n_layer) {  // heads
+      if (swap_mask & 8) return next_swap(e, d.w_heads, rows, head_tiles, dm);
+      const SkPlan p = plan_ticketed(e->sk_sms, rows, head_tiles, dm / 64);
+      return next_skinny(d.w_heads, rows, head_tiles, dm, p.grid, p.prefer_k1);
+    }
+    const void* w = (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride;
+    if (swap_mask & 1) return next_swap(e, w, rows, qkv_tiles, dm);
+    if (qkv_deferred) return next_skinny(w, rows, qkv_tiles, dm, p_qkv.grid, false);
+    const SkPlan p = plan_ticketed(e->sk_sms, rows, qkv_tiles, dm / 64);
+    return next_skinny(w, rows, qkv_tiles, dm, p.grid, p.prefer_k1);
+  };
   ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w, (const bf16*)d.ln1_b, xn, rows, dm, d.ln_eps, 1, 0, st));
   for (int l = 0; l < d.n_layer; ++l) {
     {  // in_proj + RoPE + KV page write
@@ -233,6 +292,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       ZB_TRY_RC(prefetch_l2(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.fc1_stride, st));
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, dm / NT, rows, hd);
       g.n_splits = p_out.splits;
+      g.next = nx_fc1(l);
       ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
       EpiPartial epi{d.gemm_ws, rows, dm};
       ZB_TRY(launch_gemm_skinny(g, al, epi, p_out.grid, st));
@@ -244,10 +304,10 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
       if (swap_mask & 4) {
         EpiTSwiGLU epi{h, d.d_ff};
-        ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
+        ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st, nx_fc2(l)));
       } else {
         EpiSwiGLU<NT> epi{h, d.d_ff};
-        ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st));
+        ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st, nx_fc2(l)));
       }
     }
     {  // fc2 (split-K partials) -> residual + the next layer's norm (norm_f after the last layer)
@@ -257,6 +317,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
         ZB_TRY_RC(prefetch_l2(e, d.w_heads, (int64_t)d.n_q * d.head_rows_padded * dm * 2, st));
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, dm / NT, rows, d.d_ff);
       g.n_splits = p_fc2.splits;
+      g.next = nx_qkv(l + 1);
       ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
       EpiPartial epi{d.gemm_ws, rows, dm};
       ZB_TRY(launch_gemm_skinny(g, al, epi, p_fc2.grid, st));

@@ -61,6 +61,25 @@ struct EpiPartial {
     for (int c = 0; c < 16; ++c) o[c] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
   }
   __device__ void operator()(int, bool, int, int, float*) const {}
+  // Warp-collective variant at 128 rows: lane == row would store 16 bytes to 32 different 128-byte lines per
+  // instruction (32 LSU wavefronts, ~2 us per 64 KB tile pair with the 4 epilogue warps sharing one LSU).  The warp
+  // transposes its 32 x 64 tile through `stage` (8 KB of idle ring space, 16-byte chunks XOR-swizzled by the row) and
+  // stores two whole 256-byte row segments per instruction.
+  __device__ void partial_warp(float* stage, int lane, int row0, int n_tile, int split, const float* acc) const {
+    float4* st = reinterpret_cast<float4*>(stage);
+#pragma unroll
+    for (int c = 0; c < 16; ++c) st[lane * 16 + (c ^ (lane & 15))] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+    __syncwarp();
+    const int half = lane >> 4, c = lane & 15;
+#pragma unroll
+    for (int r = 0; r < 32; r += 2) {
+      const int rr = r + half;  // row of the tile this lane moves a chunk of
+      const float4 v = st[rr * 16 + (c ^ (rr & 15))];
+      if (row0 + rr < rows)
+        reinterpret_cast<float4*>(ws + ((size_t)split * rows + row0 + rr) * ldn + n_tile * 64)[c] = v;
+    }
+    __syncwarp();
+  }
 };
 
 // x[row, n] = bf16( x[row, n] + bf16(acc) )      (out_proj / fc2 followed by the residual add, _torch.py:100-101)

@@ -61,6 +61,32 @@ struct sk_is_deferred { static constexpr bool value = false; };
 template <class E>
 struct sk_is_deferred<E, decltype((void)E::kDeferred)> { static constexpr bool value = E::kDeferred; };
 
+// The GEMM that follows this one in the step (weights do not depend on anything): when a CTA has issued its last
+// weight copy, its queue to HBM runs dry while the MMAs / epilogue / exit / next prologue go by.  It fills that bubble by
+// pulling the first bytes that CTA `blockIdx.x` of the NEXT kernel will ask for into L2.  Both weight-streaming
+// kernels number their work the same way: groups of `tg` tiles, units of `kg` k-blocks, CTA c owns units
+// [c*U/G, (c+1)*U/G), and each tile of a group is contiguous along k in the packed layout.
+struct NextW {
+  const uint8_t* wp;  // nullptr: nothing to prefetch
+  int n_tiles, k_blocks, grid, tg, kg;
+  int bytes;          // per CTA
+};
+__host__ __device__ __forceinline__ int sk_first_unit(int c, int units, int grid);
+__device__ __forceinline__ void prefetch_next_weights(const NextW& nx, int cta) {
+  if (nx.wp == nullptr || cta >= nx.grid) return;
+  const int KB = nx.k_blocks, KBU = KB / nx.kg, groups = (nx.n_tiles + nx.tg - 1) / nx.tg, units = groups * KBU;
+  const int u0 = sk_first_unit(cta, units, nx.grid), u1 = sk_first_unit(cta + 1, units, nx.grid);
+  const int grp = u0 / KBU, ku = u0 - grp * KBU;
+  const int nu = min(u1 - u0, KBU - ku);  // units of the CTA's first fragment
+  int per_tile = min(nu * nx.kg * 8192, nx.bytes / nx.tg);
+  for (int j = 0; j < nx.tg; ++j) {
+    const int tile = grp * nx.tg + j;
+    if (tile >= nx.n_tiles) break;
+    const uint8_t* p = nx.wp + ((size_t)tile * KB + (size_t)ku * nx.kg) * 8192;
+    for (int off = 0; off < per_tile; off += 32768) bulk_prefetch_l2(p + off, (uint32_t)min(32768, per_tile - off));
+  }
+}
+
 struct SkinnyCore {
   const void* Wp;     // packed weights [n_tiles][k_blocks][8 KB]
   int n_tiles, k_blocks;
@@ -70,6 +96,7 @@ struct SkinnyCore {
   int n_splits;       // deferred epilogues: CTAs per group (grid = n_groups * n_splits: every CTA is one fragment)
   unsigned long long* trace;  // debug timeline [64][160][12] (trace builds), else nullptr
   int trace_id;               // launch slot of the debug timeline
+  NextW next;                 // weights of the GEMM that follows in the step
 };
 
 template <int A_ROWS, int MODE>
@@ -194,6 +221,7 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
         if (i == 0) SK_STAMP(2);
       }
       SK_STAMP(10);
+      prefetch_next_weights(g.next, cta);
     }
   } else if (warp == MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer
@@ -220,10 +248,14 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           for (int kk = 0; kk < KG; ++kk) {
             const uint64_t adesc = umma_desc_sw128(a_addr + kk * C::A_SUB_BYTES);
             const uint64_t bdesc = umma_desc_sw128(w_addr + kk * C::TILE_BYTES);
+#ifndef SK_DBG_NOMMA
 #pragma unroll
             for (int k = 0; k < GEMM_BK / 16; ++k)
               umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
                        (ku != ku_begin) || (kk != 0) || (k != 0));
+#else
+            (void)adesc, (void)bdesc;
+#endif
           }
           umma_commit(&empty_a[sa]);
           umma_commit(&empty_w[sw]);
@@ -260,7 +292,11 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           const int idx = j * C::PROD_THREADS + ptid;
           const int kk = idx / (A_ROWS * 8), rem = idx - kk * (A_ROWS * 8);
           const int r = rem >> 3, c = rem & 7;
+#ifdef SK_DBG_NOA
+          if (idx < CHUNKS && r < rows && issued == 0) {  // what-if: only the first stage is really loaded
+#else
           if (idx < CHUNKS && r < rows) {
+#endif
             bool valid = true;
             const void* src = aload.src(r, 0, ku * KG + kk, c, valid);
             cp_async16(a_tile + kk * C::A_SUB_BYTES + sw128_offset(r, c), src, valid ? 16u : 0u);
@@ -285,6 +321,28 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
         ++arrived;
       }
     }
+    // ---- at 128 rows the four producer warps are done now: they take the second n_tile of the CTA's LAST fragment off
+    // the epilogue warps (one warp per scheduler is latency-bound on the SwiGLU / store sequences)
+    if constexpr (C::PROD_WARPS == 4 && TG == 2) {
+      const int grp = (u1 - 1) / KBU, u_frag = max(u0, grp * KBU);
+      const int ku_begin = u_frag - grp * KBU, ku_end = u1 - grp * KBU;
+      const bool complete = (ku_begin == 0 && ku_end == KBU);
+      if (sk_is_deferred<Epilogue>::value || complete) {
+        const int f = grp - u0 / KBU, b = f & 1;
+        const int hw = warp - 4, row = hw * 32 + lane;
+        mbar_wait(&tmem_full[b], (f >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(hw * 32) << 16) + (uint32_t)(b * TG * C::NTILE) + C::NTILE;
+        float acc[C::NTILE];
+        tmem_ld32(taddr, acc);
+        tmem_ld32(taddr + 32, acc + 32);
+        tmem_ld_wait();
+        if constexpr (sk_is_deferred<Epilogue>::value)
+          epi.partial_warp(reinterpret_cast<float*>(w_ring) + warp * 2048, lane, hw * 32, grp * TG + 1, cta % g.n_splits, acc);
+        else
+          epi(row, row < g.m_valid, 0, grp * TG + 1, acc);
+      }
+    }
   } else {
     // ------------------------------------------------------------------ epilogue warps (row == TMEM lane)
     pdl_wait_prior();  // residual input, workspace and tickets belong to the previous kernels until they are done
@@ -304,8 +362,12 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * TG * C::NTILE);
       float acc[C::NTILE];
+      // the producer warps take tile 1 of the last fragment (see above)
+      const bool helped = (C::PROD_WARPS == 4 && TG == 2) && (u + (ku_end - ku_begin) == u1) &&
+                          (sk_is_deferred<Epilogue>::value || complete);
 #pragma unroll
       for (int j = 0; j < TG; ++j) {
+        if (helped && j == 1) break;
         if constexpr (C::NTILE == 16) {
           tmem_ld16(taddr, acc);
         } else {
@@ -313,12 +375,19 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           tmem_ld32(taddr + j * C::NTILE + 32, acc + 32);
         }
         tmem_ld_wait();
-        if (j == TG - 1) {
+        if (j == TG - 1 || (helped && j == 0)) {
           tc_fence_before();
           mbar_arrive(&tmem_empty[b]);  // the issuer may start the next-but-one fragment into this accumulator set
         }
         if constexpr (sk_is_deferred<Epilogue>::value) {
-          epi.partial(row, row_valid, grp * TG + j, cta % g.n_splits, acc);
+          if constexpr (C::PROD_WARPS == 4) {
+            if (helped)  // (the ring is idle: all MMAs of the CTA's last fragment have completed)
+              epi.partial_warp(reinterpret_cast<float*>(w_ring) + warp * 2048, lane, warp * 32, grp * TG + j, cta % g.n_splits, acc);
+            else
+              epi.partial(row, row_valid, grp * TG + j, cta % g.n_splits, acc);
+          } else {
+            epi.partial(row, row_valid, grp * TG + j, cta % g.n_splits, acc);
+          }
         } else if (complete) {
           epi(row, row_valid, 0, grp * TG + j, acc);
         } else if (row_valid) {

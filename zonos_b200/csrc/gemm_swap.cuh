@@ -40,6 +40,7 @@ struct SwapCore {
   int* tickets;       // [ceil(n_tiles/2)] zero-initialised, self-resetting
   unsigned long long* trace;  // debug timeline (trace builds), else nullptr
   int trace_id;
+  NextW next;         // weights of the GEMM that follows in the step (gemm_skinny.cuh)
 };
 
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {  // 32 lanes x 8 columns
@@ -114,6 +115,7 @@ __global__ void __launch_bounds__(SWP_THREADS, 2) gemm_swap_kernel(SwapCore g, A
         }
         if (++ku == KBU) ku = 0, ++grp;
       }
+      prefetch_next_weights(g.next, cta);
     }
   } else if (warp == 6) {
     // ------------------------------------------------------------------ MMA issuer: D[128 features, 16] += W * A^T

@@ -8,8 +8,8 @@
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 
-static unsigned long long* g_trace_buf = nullptr;  // debug timeline (zb200_debug_trace)
-static int g_trace_next = 0;
+unsigned long long* g_trace_buf = nullptr;  // debug timeline (zb200_debug_trace); also stamped by the engine's GEMMs
+int g_trace_next = 0;
 
 namespace zb {
 
