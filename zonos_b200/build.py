@@ -22,6 +22,9 @@ if os.environ.get("ZB200_DBG_NOA"):  # what-if experiment: the decode GEMMs skip
     NVCC_FLAGS.append("-DSK_DBG_NOA")
 if os.environ.get("ZB200_DBG_NOMMA"):  # what-if experiment: the decode GEMMs issue no MMAs (wrong results)
     NVCC_FLAGS.append("-DSK_DBG_NOMMA")
+for _k in ("SK_SA128", "SK_SW128_KB"):  # ring-depth experiments
+    if os.environ.get(_k):
+        NVCC_FLAGS.append(f"-D{_k}={os.environ[_k]}")
 if os.environ.get("ZB200_TRACE"):
     NVCC_FLAGS.append("-DSK_TRACE")
 NVCC_FLAGS.remove("--use_fast_math=false")  # precise math on purpose: the sampler/Snake must match the reference

@@ -184,7 +184,9 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
     }
   } else if (warp == 10) {
     // ---------------------------------------------------------------- weight k-blocks, in the order the MMAs use them
-    if (lane == 0) {
+    // Lane jt copies NT tile jt of every stage: one thread only gets a few bulk copies per microsecond through the
+    // TMA unit (scripts/exp_stream.cu), a 256-column stage is four of them.
+    if (lane < 4) {
       int s = 0;
       uint32_t empty_parity = 1;  // ring slot and the parity of its "empty" barrier (flips each time the ring wraps)
       const size_t tile_stride = (size_t)kb_per_tile * (NT * 128);  // bytes between consecutive NT tiles of one k-block
@@ -198,10 +200,9 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
           const uint8_t* src = wg + (size_t)cb * (NT * 128);  // k-block index = tap*cblocks + cb
           for (int tap = 0; tap < a.taps; ++tap, src += (size_t)a.cblocks * (NT * 128)) {
             if (!a.w_resident) mbar_wait(&w_empty[s], empty_parity);
-            mbar_arrive_expect_tx(&w_full[s], stage_tx);
-            uint8_t* dst = w_ring + s * a.w_stage_bytes;
-            for (int jt = 0; jt < tiles_here; ++jt)
-              bulk_g2s(dst + jt * NT * 128, src + jt * tile_stride, NT * 128, &w_full[s]);
+            if (lane == 0) mbar_arrive_expect_tx(&w_full[s], stage_tx);
+            if (lane < tiles_here)
+              bulk_g2s(w_ring + s * a.w_stage_bytes + lane * NT * 128, src + lane * tile_stride, NT * 128, &w_full[s]);
             if (++s == a.sw) s = 0, empty_parity ^= 1;
           }
         }

@@ -37,6 +37,15 @@ constexpr int SK_NT = 64;                         // weight rows of one packed t
 constexpr int SK_TILE_BYTES = SK_NT * 128;        // 8 KB packed (n_tile, k_block) image
 constexpr int SK_PARTIAL_F4 = (SK_NT / 4) * 128;  // float4 per partial sub-tile (32 KB)
 enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2, MODE_N16 = 3 };
+#ifndef SK_WLANES
+#define SK_WLANES 4     // lanes of the weight-producer warp that issue bulk copies
+#endif
+#ifndef SK_SA128
+#define SK_SA128 4      // activation ring depth at 128 rows (16 KB stages)
+#endif
+#ifndef SK_SW128_KB
+#define SK_SW128_KB 128  // weight ring at 128 rows
+#endif
 
 // Optional in-kernel timeline (build with ZB200_TRACE=1): globaltimer stamps per launch / CTA / event.
 #ifdef SK_TRACE
@@ -114,8 +123,8 @@ struct SkinnyCfg {
   static constexpr int A_SUB_BYTES = A_ROWS * 128;
   static constexpr int A_STAGE_BYTES = KG * A_SUB_BYTES;
   static constexpr int W_STAGE_BYTES = TG * KG * TILE_BYTES;
-  static constexpr int SA = (A_ROWS <= 8 && MODE != MODE_N16) ? 8 : 4;
-  static constexpr int SW = (A_ROWS >= 128) ? (128 * 1024 / W_STAGE_BYTES)
+  static constexpr int SA = (A_ROWS >= 128) ? SK_SA128 : (A_ROWS <= 8 && MODE != MODE_N16) ? 8 : 4;
+  static constexpr int SW = (A_ROWS >= 128) ? (SK_SW128_KB * 1024 / W_STAGE_BYTES)
                                             : ((A_ROWS > 8 || MODE == MODE_N16 ? 64 : 80) * 1024 / W_STAGE_BYTES);
   static constexpr int A_BYTES = SA * A_STAGE_BYTES;
   static constexpr int W_BYTES = SW * W_STAGE_BYTES;
@@ -201,12 +210,17 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
 
   if (warp == W_WARP) {
     // ------------------------------------------------------------------ weight producer (independent of prior kernels)
-    if (lane == 0) {
+    // One thread gets only ~2.7 bulk copies per microsecond through the TMA unit whatever their size
+    // (scripts/exp_stream.cu: 22 GB/s with 8 KB copies, 44 GB/s with 16 KB), less than an SM's share of HBM.  SK_WLANES
+    // lanes therefore issue in parallel, lane l owning units l, l + SK_WLANES, ...  A lane must never run two ring
+    // revolutions ahead of the consumer (the parity wait cannot tell 0 from 2 completions): lanes <= slots guarantees it.
+    static_assert(SK_WLANES <= SW, "weight-producer lanes must not outnumber the ring slots");
+    if (lane < SK_WLANES) {
       const uint64_t pol = l2_policy_evict_first();
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(g.Wp);
-      int grp = u0 / KBU, ku = u0 - grp * KBU;
-      for (int i = 0; i < n_units; ++i) {
+      for (int i = lane; i < n_units; i += SK_WLANES) {
         const int s = i % SW;
+        const int u = u0 + i, grp = u / KBU, ku = u - grp * KBU;
         mbar_wait(&empty_w[s], ((i / SW) & 1) ^ 1);
         mbar_arrive_expect_tx(&full_w[s], C::W_STAGE_BYTES);
         uint8_t* dst = w_ring + s * C::W_STAGE_BYTES;
@@ -215,13 +229,14 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
           bulk_g2s_hint(dst, src, C::TILE_BYTES, &full_w[s], pol);
           bulk_g2s_hint(dst + C::TILE_BYTES, src + (size_t)KB * C::TILE_BYTES, C::TILE_BYTES, &full_w[s], pol);
         } else {  // units are contiguous in memory
-          bulk_g2s_hint(dst, wp + (size_t)(u0 + i) * C::W_STAGE_BYTES, C::W_STAGE_BYTES, &full_w[s], pol);
+          bulk_g2s_hint(dst, wp + (size_t)u * C::W_STAGE_BYTES, C::W_STAGE_BYTES, &full_w[s], pol);
         }
-        if (++ku == KBU) ku = 0, ++grp;
         if (i == 0) SK_STAMP(2);
       }
-      SK_STAMP(10);
-      prefetch_next_weights(g.next, cta);
+      if (lane == 0) {
+        SK_STAMP(10);
+        prefetch_next_weights(g.next, cta);
+      }
     }
   } else if (warp == MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer

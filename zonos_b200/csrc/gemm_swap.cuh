@@ -95,12 +95,16 @@ __global__ void __launch_bounds__(SWP_THREADS, 2) gemm_swap_kernel(SwapCore g, A
 
   if (warp == 5) {
     // ------------------------------------------------------------------ weight producer (independent of prior kernels)
-    if (lane == 0) {
+    // SWP_WLANES lanes issue in parallel (one thread gets ~2.7 bulk copies / us through the TMA unit: gemm_skinny.cuh).
+    // A lane must never run two ring revolutions ahead of the consumer (the parity wait cannot tell 0 from 2
+    // completions): lanes <= ring slots guarantees it, here every lane simply owns one slot.
+    constexpr int SWP_WLANES = SWP_SW;
+    if (lane < SWP_WLANES) {
       const uint64_t pol = l2_policy_evict_first();
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(g.Wp);
-      int grp = u0 / KBU, ku = u0 - grp * KBU;
-      for (int i = 0; i < n_units; ++i) {
+      for (int i = lane; i < n_units; i += SWP_WLANES) {
         const int s = i % SWP_SW;
+        const int u = u0 + i, grp = u / KBU, ku = u - grp * KBU;
         mbar_wait(&empty_w[s], ((i / SWP_SW) & 1) ^ 1);
         const bool two = (2 * grp + 1) < g.n_tiles;  // the last group of an odd tile count has one tile
         mbar_arrive_expect_tx(&full_w[s], two ? SWP_W_STAGE : SWP_W_STAGE / 2);
@@ -113,9 +117,8 @@ __global__ void __launch_bounds__(SWP_THREADS, 2) gemm_swap_kernel(SwapCore g, A
             bulk_g2s_hint(dst + kk * 2 * SK_TILE_BYTES + SK_TILE_BYTES, src + ((size_t)KB + kk) * SK_TILE_BYTES, SK_TILE_BYTES,
                           &full_w[s], pol);
         }
-        if (++ku == KBU) ku = 0, ++grp;
       }
-      prefetch_next_weights(g.next, cta);
+      if (lane == 0) prefetch_next_weights(g.next, cta);
     }
   } else if (warp == 6) {
     // ------------------------------------------------------------------ MMA issuer: D[128 features, 16] += W * A^T

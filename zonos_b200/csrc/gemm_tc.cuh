@@ -177,16 +177,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, MINB) gemm_tc_kernel(GemmCore g,
     tc_fence_before();
   } else if (warp == 4) {
     // ------------------------------------------------------------------ weight producer: one bulk copy per tile and stage
-    if (lane == 0) {
+    // (lane jt copies tile jt: a single thread only gets a few bulk copies per microsecond through the TMA unit)
+    if (lane < 4) {
       const uint64_t pol = l2_policy_evict_first();
       const uint8_t* wbase = reinterpret_cast<const uint8_t*>(g.Wp);
       for (int i = 0; i < nkb; ++i) {
         const int s = i % stages;
         mbar_wait(&empty_bar[s], ((i / stages) & 1) ^ 1);
-        mbar_arrive_expect_tx(&full_bar[s], tiles_here * SM::B_TILE_BYTES);
-        for (int jt = 0; jt < tiles_here; ++jt) {
-          uint8_t* dst = smem + s * stage_bytes + GEMM_A_STAGE_BYTES + jt * SM::B_TILE_BYTES;
-          const uint8_t* src = wbase + ((size_t)(n_tile0 + jt) * g.k_blocks + kb0 + i) * SM::B_TILE_BYTES;
+        if (lane == 0) mbar_arrive_expect_tx(&full_bar[s], tiles_here * SM::B_TILE_BYTES);
+        if (lane < tiles_here) {
+          uint8_t* dst = smem + s * stage_bytes + GEMM_A_STAGE_BYTES + lane * SM::B_TILE_BYTES;
+          const uint8_t* src = wbase + ((size_t)(n_tile0 + lane) * g.k_blocks + kb0 + i) * SM::B_TILE_BYTES;
           if (g.stream_weights)
             bulk_g2s_hint(dst, src, SM::B_TILE_BYTES, &full_bar[s], pol);
           else
@@ -196,21 +197,28 @@ __global__ void __launch_bounds__(GEMM_THREADS, MINB) gemm_tc_kernel(GemmCore g,
     }
   } else {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // The warp stays converged (uniform control flow keeps descriptors in uniform registers and the issue sequence
+    // short); one elected lane issues the MMAs and the commits.
+    {
       const uint32_t idesc = umma_idesc(GEMM_BM, n_cols, AB_FMT);
+      const bool leader = elect_one();
       for (int i = 0; i < nkb; ++i) {
         const int s = i % stages;
         mbar_wait(&full_bar[s], (i / stages) & 1);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
-        const uint64_t adesc = umma_desc_sw128(a_addr);
-        const uint64_t bdesc = umma_desc_sw128(a_addr + GEMM_A_STAGE_BYTES);
+        if (leader) {
+          const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
+          const uint64_t adesc = umma_desc_sw128(a_addr);
+          const uint64_t bdesc = umma_desc_sw128(a_addr + GEMM_A_STAGE_BYTES);
 #pragma unroll
-        for (int k = 0; k < GEMM_BK / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle row
-          umma_f16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (i | k) != 0);
-        umma_commit(&empty_bar[s]);
+          for (int k = 0; k < GEMM_BK / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle row
+            umma_f16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (i | k) != 0);
+          umma_commit(&empty_bar[s]);
+        }
+        __syncwarp();
       }
-      umma_commit(accum_bar);
+      if (leader) umma_commit(accum_bar);
+      __syncwarp();
     }
   }
   __syncthreads();
