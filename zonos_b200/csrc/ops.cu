@@ -83,6 +83,7 @@ cudaError_t launch_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* 
 //   xn = LayerNorm(x) * w + b                                        -- the NEXT norm (norm2, next layer's norm, or norm_f)
 // which replaces the separate residual epilogue + LayerNorm kernel pair by one pass over the row.
 constexpr int RLN_THREADS = 256;
+constexpr int RLN_BATCH = 12;  // splits summed per round of loads (the planners use <= 12 splits: one round trip)
 __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict__ x, const float* __restrict__ ws, int splits,
                                                                int rows, const bf16* __restrict__ w, const bf16* __restrict__ b,
                                                                bf16* __restrict__ xn, int d, float eps,
@@ -91,14 +92,21 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
 #ifdef SK_TRACE
   if (threadIdx.x == 0) sk_stamp(trace, trace_id, 0);
 #endif
-  pdl_wait_prior();
-#ifdef SK_TRACE
-  if (threadIdx.x == 0) sk_stamp(trace, trace_id, 4);
-#endif
   __shared__ float red[RLN_THREADS / 32];
   __shared__ float bcast;
   const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int MAXV = 2;  // d <= 4096
+  // the LayerNorm parameters do not depend on the previous kernel: fetch them before the dependency resolves
+  uint4 wu[MAXV], bu[MAXV];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int col = (i * RLN_THREADS + tid) * 8;
+    if (col < d) wu[i] = __ldg(reinterpret_cast<const uint4*>(w + col)), bu[i] = __ldg(reinterpret_cast<const uint4*>(b + col));
+  }
+  pdl_wait_prior();
+#ifdef SK_TRACE
+  if (threadIdx.x == 0) sk_stamp(trace, trace_id, 4);
+#endif
   float v[MAXV][8];
   float sum = 0.f;
 #pragma unroll
@@ -106,16 +114,16 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
     const int col = (i * RLN_THREADS + tid) * 8;
     if (col < d) {
       float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int s0 = 0; s0 < splits; s0 += 8) {  // 16 independent loads in flight, added in split order
-        float4 a[8], c[8];
+      for (int s0 = 0; s0 < splits; s0 += RLN_BATCH) {  // up to 24 independent loads in flight, added in split order
+        float4 a[RLN_BATCH], c[RLN_BATCH];
 #pragma unroll
-        for (int s = 0; s < 8; ++s)
+        for (int s = 0; s < RLN_BATCH; ++s)
           if (s0 + s < splits) {
             const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)(s0 + s) * rows + row) * d + col);
             a[s] = __ldcg(p), c[s] = __ldcg(p + 1);
           }
 #pragma unroll
-        for (int s = 0; s < 8; ++s)
+        for (int s = 0; s < RLN_BATCH; ++s)
           if (s0 + s < splits) {
             o[0] += a[s].x, o[1] += a[s].y, o[2] += a[s].z, o[3] += a[s].w;
             o[4] += c[s].x, o[5] += c[s].y, o[6] += c[s].z, o[7] += c[s].w;
@@ -166,8 +174,7 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
   for (int i = 0; i < MAXV; ++i) {
     const int col = (i * RLN_THREADS + tid) * 8;
     if (col < d) {
-      const uint4 wu = __ldg(reinterpret_cast<const uint4*>(w + col)), bu = __ldg(reinterpret_cast<const uint4*>(b + col));
-      const uint32_t wv[4] = {wu.x, wu.y, wu.z, wu.w}, bv[4] = {bu.x, bu.y, bu.z, bu.w};
+      const uint32_t wv[4] = {wu[i].x, wu[i].y, wu[i].z, wu[i].w}, bv[4] = {bu[i].x, bu[i].y, bu[i].z, bu[i].w};
       uint32_t o[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
