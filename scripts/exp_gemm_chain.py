@@ -10,7 +10,7 @@ from zonos_b200 import ops
 dev = "cuda"
 g = torch.Generator(device=dev).manual_seed(0)
 SHAPES = {"qkv": (3072, 2048), "out": (2048, 2048), "fc1": (16384, 2048), "fc2": (2048, 8192)}
-NW = 10
+NW = int(__import__("os").environ.get("NW", "10"))
 cases = [a.split(":") for a in sys.argv[1:]] or [["fc1", "128", "128"], ["fc1", "128", "148"], ["fc1", "32", "256"], ["fc1", "2", "256"]]
 packed = {}
 side = torch.cuda.Stream()
@@ -24,8 +24,9 @@ for name, M, grid in cases:
     tickets = torch.zeros(1024, dtype=torch.int32, device=dev)
 
     def chain():
-        for w in packed[name]:
-            ops.gemm_skinny_bf16(a, w, N, grid=grid, ws=ws, tickets=tickets)
+        for rep in range(max(1, 10 // NW)):
+            for w in packed[name]:
+                ops.gemm_skinny_bf16(a, w, N, grid=grid, ws=ws, tickets=tickets)
 
     with torch.cuda.stream(side):
         chain()
@@ -41,5 +42,5 @@ for name, M, grid in cases:
             gr.replay()
         e1.record(side)
         side.synchronize()
-    us = e0.elapsed_time(e1) / 5 / NW * 1e3
+    us = e0.elapsed_time(e1) / 5 / (NW * max(1, 10 // NW)) * 1e3
     print(f"{name} M={M} grid={grid}: {us:.2f} us/launch, {N * K * 2 / us / 1e3:.0f} GB/s of weights", flush=True)

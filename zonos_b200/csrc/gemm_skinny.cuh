@@ -28,6 +28,8 @@
 //   * M <= 32: 224 threads, <= 112 KB shared memory -> two CTAs per SM, i.e. the next GEMM of the step (launched early
 //     by PDL) prefetches its weights next to the running one.
 #pragma once
+#include <cstdlib>
+
 #include "common.cuh"
 #include "gemm_tc.cuh"
 
@@ -481,7 +483,10 @@ cudaError_t launch_gemm_skinny_n16(const SkinnyCore& g, const ALoader& al, const
 // Mode the launcher picks for (rows, n_tiles, k_blocks); prefer_k1 forces 8 KB single-tile units at M > 32 (smaller
 // fix-up slots when a group is shared by several CTAs).
 inline int skinny_mode(int m, int n_tiles, int k_blocks, bool prefer_k1 = false) {
-  if (m <= 32) return (k_blocks % 2 == 0) ? MODE_K2 : MODE_K1;
+  // An N <= 128 UMMA costs ~77 cycles whatever N is (scripts/exp_umma_rate.cu): with N = 64 (K2 / K1) the MMAs of a
+  // 16 KB stage take 616 cycles, i.e. ~50 GB/s per SM at best; two tiles per MMA (T2) halve that.
+  static const bool small_t2 = getenv("ZB200_SMALL_T2") != nullptr;  // measured slower at batch 1-16: opt-in
+  if (m <= 32 && !(small_t2 && n_tiles % 2 == 0 && !prefer_k1)) return (k_blocks % 2 == 0) ? MODE_K2 : MODE_K1;
   return (n_tiles % 2 == 0 && !prefer_k1) ? MODE_T2 : MODE_K1;
 }
 inline int skinny_tg(int mode) { return mode == MODE_T2 ? 2 : 1; }
@@ -494,11 +499,13 @@ cudaError_t launch_gemm_skinny(const SkinnyCore& g, const ALoader& al, const Epi
                                bool prefer_k1 = false) {
   const int mode = skinny_mode(g.m_valid, g.n_tiles, g.k_blocks, prefer_k1);
   if (g.m_valid <= 8)
-    return mode == MODE_K2 ? launch_gemm_skinny_cfg<8, MODE_K2>(g, al, epi, grid, st)
-                           : launch_gemm_skinny_cfg<8, MODE_K1>(g, al, epi, grid, st);
+    return mode == MODE_K2   ? launch_gemm_skinny_cfg<8, MODE_K2>(g, al, epi, grid, st)
+           : mode == MODE_T2 ? launch_gemm_skinny_cfg<8, MODE_T2>(g, al, epi, grid, st)
+                             : launch_gemm_skinny_cfg<8, MODE_K1>(g, al, epi, grid, st);
   if (g.m_valid <= 32)
-    return mode == MODE_K2 ? launch_gemm_skinny_cfg<32, MODE_K2>(g, al, epi, grid, st)
-                           : launch_gemm_skinny_cfg<32, MODE_K1>(g, al, epi, grid, st);
+    return mode == MODE_K2   ? launch_gemm_skinny_cfg<32, MODE_K2>(g, al, epi, grid, st)
+           : mode == MODE_T2 ? launch_gemm_skinny_cfg<32, MODE_T2>(g, al, epi, grid, st)
+                             : launch_gemm_skinny_cfg<32, MODE_K1>(g, al, epi, grid, st);
   return mode == MODE_T2 ? launch_gemm_skinny_cfg<128, MODE_T2>(g, al, epi, grid, st)
                          : launch_gemm_skinny_cfg<128, MODE_K1>(g, al, epi, grid, st);
 }
