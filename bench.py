@@ -23,7 +23,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 FRAME_RATE = 44100 / 512  # 86.1328 frames per audio second
 # attn_decode_kernel DRAM traffic per launch measured by ncu: key (sequences incl. CFG, kv heads, context)
-NCU_ATTN_TRAFFIC = {(128, 4, 1432): 390_500_000}
+NCU_ATTN_TRAFFIC = {(128, 4, 1432, 2): 390_500_000}  # captured with 2 key splits
 C3_SAMPLING = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0,
                    repetition_penalty_window=2, temperature=1.0)
 
@@ -177,7 +177,7 @@ def attn_roofline(shape, batch, ctx, device, hbm_peak):
     q = torch.randn(n_seq, H * 128, device=device).bfloat16()
     import math
 
-    nsplit = max(1, min(16, math.ceil(2 * 148 * 2 / (n_seq * Hkv)), kv.pages_per_seq))
+    nsplit = max(1, min(8, math.ceil(256 / (n_seq * Hkv)), kv.pages_per_seq))  # the engine's choice (engine.py)
     for l in range(layers):
         ops.attn_decode(q, kv, l, ctx, H, nsplit)
     torch.cuda.synchronize()
@@ -195,8 +195,8 @@ def attn_roofline(shape, batch, ctx, device, hbm_peak):
     # DRAM bytes of one launch from the committed `ncu --set full` capture (dram__bytes_read.sum + dram__bytes_write.sum);
     # only valid for the configuration that was captured, otherwise null.
     traffic = None
-    if (n_seq, Hkv, ctx) in NCU_ATTN_TRAFFIC:
-        traffic = NCU_ATTN_TRAFFIC[(n_seq, Hkv, ctx)]
+    if (n_seq, Hkv, ctx, nsplit) in NCU_ATTN_TRAFFIC:
+        traffic = NCU_ATTN_TRAFFIC[(n_seq, Hkv, ctx, nsplit)]
     return {"kernel": "attn_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
             "frac": round(achieved / hbm_peak, 4), "traffic": traffic,
             "traffic_source": "profiles/r01b_ncu_full_decode_b64.txt" if traffic else None,
@@ -418,6 +418,11 @@ def main_b200(args, world, rank, local):
     if world == 1 and not args.no_dac:
         line["dac_decode"] = dac_section(device, B, args.max_new_tokens)
         torch.cuda.empty_cache()
+        # SURVEY 8(d) metric (i), second form: codes -> waveform included.  The two stages run back to back on the same
+        # GPU, so the pipeline rate is the harmonic composition of the two end-to-end rates measured above.
+        gen, dac = line["e2e"]["value"], line["dac_decode"]["e2e_audio_s_per_s"]
+        line["e2e_waveform"] = {"value": round(1.0 / (1.0 / gen + 1.0 / dac), 2), "unit": "audio-s/s",
+                                "note": "generate (host conditioning in) + DAC decode (waveform to host), sequential"}
     if world == 1 and not args.no_cpu_baseline:
         frames = args.cpu_frames
         v, dt, cores = cpu_reference_sample(frames, args.shape)

@@ -1,6 +1,7 @@
 """Host side of the decode/prefill engine (csrc/engine.cu): weight repack, workspaces, ctypes descriptor."""
 import ctypes
 import math
+import os
 
 import torch
 
@@ -94,8 +95,13 @@ class Engine:
         self.logits = torch.empty(batch, self.pw.emb.shape[0], pw.vocab, dtype=torch.float32, device=dev)
         self.gemm_ws = torch.empty(160 * 32768, dtype=torch.float32, device=dev)  # 160 CTAs x 2 slots x 2 sub-tiles x 32 KB
         self.gemm_tickets = torch.zeros(1024, dtype=torch.int32, device=dev)
-        if attn_nsplit is None:  # enough CTAs for ~2 waves of 2 CTAs/SM
-            attn_nsplit = max(1, min(16, math.ceil(2 * 148 * 2 / (B2 * Hkv)), self.kv.pages_per_seq))
+        if attn_nsplit is None and os.environ.get("ZB200_ATTN_NSPLIT"):
+            attn_nsplit = max(1, min(int(os.environ["ZB200_ATTN_NSPLIT"]), self.kv.pages_per_seq))
+        if attn_nsplit is None:
+            # split the keys only while (sequence, kv head) pairs alone leave SMs idle: measured on B200 (time_step.py),
+            # one CTA per pair is fastest from batch 32 up (every split costs a partial write + a ticketed merge),
+            # 8 splits at batch 1-4, 2 at batch 16
+            attn_nsplit = max(1, min(8, math.ceil(256 / (B2 * Hkv)), self.kv.pages_per_seq))
         self.attn_nsplit = attn_nsplit
         self.attn_ws = torch.empty(B2 * Hkv * attn_nsplit * 520, dtype=torch.float32, device=dev)
         self.attn_tickets = torch.zeros(B2 * Hkv, dtype=torch.int32, device=dev)
