@@ -23,7 +23,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 FRAME_RATE = 44100 / 512  # 86.1328 frames per audio second
 # attn_decode_kernel DRAM traffic per launch measured by ncu: key (sequences incl. CFG, kv heads, context)
-NCU_ATTN_TRAFFIC = {(128, 4, 1432, 2): 390_500_000}  # captured with 2 key splits
+NCU_ATTN_TRAFFIC = {(128, 4, 1432, 1): (390_561_000, "profiles/r01d_ncu_full.txt"),
+                    (128, 4, 1432, 2): (390_500_000, "profiles/r01b_ncu_full_decode_b64.txt")}
 C3_SAMPLING = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0,
                    repetition_penalty_window=2, temperature=1.0)
 
@@ -194,12 +195,10 @@ def attn_roofline(shape, batch, ctx, device, hbm_peak):
     achieved = algo / (ms * 1e-3) / 1e9
     # DRAM bytes of one launch from the committed `ncu --set full` capture (dram__bytes_read.sum + dram__bytes_write.sum);
     # only valid for the configuration that was captured, otherwise null.
-    traffic = None
-    if (n_seq, Hkv, ctx, nsplit) in NCU_ATTN_TRAFFIC:
-        traffic = NCU_ATTN_TRAFFIC[(n_seq, Hkv, ctx, nsplit)]
+    traffic, traffic_src = NCU_ATTN_TRAFFIC.get((n_seq, Hkv, ctx, nsplit), (None, None))
     return {"kernel": "attn_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
             "frac": round(achieved / hbm_peak, 4), "traffic": traffic,
-            "traffic_source": "profiles/r01b_ncu_full_decode_b64.txt" if traffic else None,
+            "traffic_source": traffic_src,
             "bytes_per_launch": algo, "ms_per_launch": round(ms, 5), "ctx": ctx, "nsplit": nsplit}
 
 

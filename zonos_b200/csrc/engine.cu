@@ -127,8 +127,9 @@ SkPlan plan_deferred(int sms, int rows, int n_tiles, int k_blocks, int64_t ws_fl
   const int cap = sms * (rows <= 32 ? 2 : big_m_ctas_per_sm());
   const int mode = skinny_mode(rows, n_tiles, k_blocks);
   const int groups = n_tiles / skinny_tg(mode), kbu = k_blocks / skinny_kg(mode);
+  static const int max_split = getenv("ZB200_DEF_MAXSPLIT") ? atoi(getenv("ZB200_DEF_MAXSPLIT")) : 64;
   int s = 1;
-  for (int c = 1; c <= kbu; ++c)
+  for (int c = 1; c <= kbu && c <= max_split; ++c)
     if (groups * c <= cap && kbu / c >= 2 && (int64_t)c * rows * n <= ws_floats) s = c;
   return SkPlan{groups * s, s, false};
 }
