@@ -269,6 +269,8 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
     const int q = warp & 3, par = warp >> 2;
     const int row = q * 32 + lane;
     const bool has_resid = a.resid != nullptr && a.up == 0;
+    // a 16-column chunk of a row is one aligned 32-byte piece of the output when the channel count is a multiple of 16
+    const bool wide = (a.C_out & 15) == 0 && (a.pitch_out & 15) == 0;
     int it = 0;
     [[maybe_unused]] long long tr_tf = 0, tr_start = clock64();
     for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
@@ -289,8 +291,12 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
         for (int c = 0; c < 8; ++c) {
           const int ch = 2 * c + par;
           if (ch < n_chunks && n0 + ch * 16 < a.n_total) {
-            rbuf[2 * c] = __ldcs(reinterpret_cast<const uint4*>(rrow + ch * 16));
-            rbuf[2 * c + 1] = __ldcs(reinterpret_cast<const uint4*>(rrow + ch * 16 + 8));
+            if (wide) {
+              ldg256_stream(rrow + ch * 16, rbuf[2 * c], rbuf[2 * c + 1]);
+            } else {
+              rbuf[2 * c] = __ldcs(reinterpret_cast<const uint4*>(rrow + ch * 16));
+              if (n0 + ch * 16 + 8 < a.n_total) rbuf[2 * c + 1] = __ldcs(reinterpret_cast<const uint4*>(rrow + ch * 16 + 8));
+            }
           }
         }
       }
@@ -328,13 +334,17 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
           if (lane == 0) mbar_arrive(&t_empty[buf]);
         }
         if (!row_valid) continue;
+        uint4 o_raw[2], o_act[2];
+        size_t offs[2];
+        bool live[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int col = ch * 16 + h * 8;
           const int2 grp = s_grp[cbuf][col >> 3];
           const int t = a.up > 0 ? a.up * j + grp.x : j + grp.x;
-          if (t < 0 || t >= a.T_out) continue;
-          const size_t off = ((size_t)b * a.T_out + t) * a.pitch_out + grp.y;
+          live[h] = t >= 0 && t < a.T_out;
+          offs[h] = ((size_t)b * a.T_out + (live[h] ? t : 0)) * a.pitch_out + grp.y;
+          if (!live[h]) continue;
           const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col]);
           const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col + 4]);
           const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
@@ -352,11 +362,9 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
             }
           }
           if (a.out_raw) {
-            uint4 o;
-            __half2* oh = reinterpret_cast<__half2*>(&o);
+            __half2* oh = reinterpret_cast<__half2*>(&o_raw[h]);
 #pragma unroll
             for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-            *reinterpret_cast<uint4*>(a.out_raw + off) = o;
           }
           if (a.out_act) {
             const float4 a0 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col]);
@@ -365,14 +373,23 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
             const float4 i1 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col + 4]);
             const float al[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
             const float ia[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
-            uint4 o;
-            __half2* oh = reinterpret_cast<__half2*>(&o);
+            __half2* oh = reinterpret_cast<__half2*>(&o_act[h]);
 #pragma unroll
             for (int i = 0; i < 4; ++i)
               oh[i] = __floats2half2_rn(snake_fast(v[2 * i], al[2 * i], ia[2 * i]),
                                         snake_fast(v[2 * i + 1], al[2 * i + 1], ia[2 * i + 1]));
-            *reinterpret_cast<uint4*>(a.out_act + off) = o;
           }
+        }
+        if (wide && live[0] && live[1]) {  // (both halves are in one phase / row: C_out % 16 == 0)
+          if (a.out_raw) stg256(a.out_raw + offs[0], o_raw[0], o_raw[1]);
+          if (a.out_act) stg256(a.out_act + offs[0], o_act[0], o_act[1]);
+        } else {
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            if (live[h]) {
+              if (a.out_raw) *reinterpret_cast<uint4*>(a.out_raw + offs[h]) = o_raw[h];
+              if (a.out_act) *reinterpret_cast<uint4*>(a.out_act + offs[h]) = o_act[h];
+            }
         }
       }
     }
