@@ -121,12 +121,25 @@ struct EpiSwiGLU {
       const float s = bf16_round(gate / (1.0f + expf(-gate)));
       r[c] = val * s;
     }
+    // lane == row: 32 bytes per store instruction and lane (256-bit STG) when the rows allow it
+    const bool wide = (HN % 16 == 0) && ((ldh & 15) == 0) && ((reinterpret_cast<uintptr_t>(h) & 31) == 0);
 #pragma unroll
-    for (int c = 0; c < HN; c += 8) {
-      uint4 v;
-      v.x = pack_bf16x2(r[c], r[c + 1]), v.y = pack_bf16x2(r[c + 2], r[c + 3]);
-      v.z = pack_bf16x2(r[c + 4], r[c + 5]), v.w = pack_bf16x2(r[c + 6], r[c + 7]);
-      *reinterpret_cast<uint4*>(o + c) = v;
+    for (int c = 0; c < HN; c += 16) {
+      uint4 v[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int cc = c + 8 * k;
+        if (cc < HN) {
+          v[k].x = pack_bf16x2(r[cc], r[cc + 1]), v[k].y = pack_bf16x2(r[cc + 2], r[cc + 3]);
+          v[k].z = pack_bf16x2(r[cc + 4], r[cc + 5]), v[k].w = pack_bf16x2(r[cc + 6], r[cc + 7]);
+        }
+      }
+      if (wide) {
+        stg256(o + c, v[0], v[1]);
+      } else {
+        *reinterpret_cast<uint4*>(o + c) = v[0];
+        if (c + 8 < HN) *reinterpret_cast<uint4*>(o + c + 8) = v[1];
+      }
     }
   }
 };

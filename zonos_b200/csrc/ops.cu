@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
         for (int s = 0; s < RLN_BATCH; ++s)
           if (s0 + s < splits) {
             const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)(s0 + s) * rows + row) * d + col);
-            a[s] = __ldcg(p), c[s] = __ldcg(p + 1);
+            ldg256_cg(p, a[s], c[s]);  // 32 contiguous bytes per lane: one 256-bit load
           }
 #pragma unroll
         for (int s = 0; s < RLN_BATCH; ++s)
@@ -213,7 +213,7 @@ __global__ void qkv_finish_kernel(const float* __restrict__ ws, int splits, int 
     for (int s = 0; s < 8; ++s)
       if (s0 + s < splits) {
         const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)(s0 + s) * rows + row) * n_cols + col0);
-        a[s] = __ldcg(p), c[s] = __ldcg(p + 1);
+        ldg256_cg(p, a[s], c[s]);
       }
 #pragma unroll
     for (int s = 0; s < 8; ++s)
