@@ -171,7 +171,8 @@ def test_attn_decode_paged(ops, n_seq, H, Hkv, n_keys, nsplit):
     assert torch.equal(out, out2)
 
 
-@pytest.mark.parametrize("n_seq,H,Hkv,S,pos0", [(2, 16, 4, 24, 0), (3, 4, 2, 70, 0), (2, 16, 4, 5, 130)])
+@pytest.mark.parametrize("n_seq,H,Hkv,S,pos0", [(2, 16, 4, 24, 0), (3, 4, 2, 70, 0), (2, 16, 4, 5, 130), (1, 16, 4, 1, 0),
+                                                (2, 16, 4, 138, 0), (2, 8, 2, 64, 64), (1, 4, 1, 300, 37)])
 def test_attn_prefill_causal(ops, n_seq, H, Hkv, S, pos0):
     g = torch.Generator(device="cuda").manual_seed(S)
     T = pos0 + S

@@ -8,7 +8,7 @@
 //   mma.sync.m16n8k16 (the 4 query heads of the GQA group occupy rows 0-3 of the M=16 tile: the op is bandwidth
 //   bound, tensor throughput is irrelevant), online softmax in fp32.  Splits are merged by the last CTA to arrive.
 //
-// attn_prefill_kernel: causal attention for the (short) prefill: one warp per (sequence, q head, query position).
+// attn_prefill_kernel: causal flash attention for the prefill: 64 query positions of one q head per CTA, mma.sync.
 #include "../../include/zonos_b200.h"
 #include "attention.cuh"
 #include "common.cuh"
@@ -276,47 +276,170 @@ cudaError_t launch_attn_decode(const AttnDecodeArgs& a, int n_seq, int nsplit, c
 }
 
 // ------------------------------------------------------------------------------------------------ prefill
-// One warp per (query position, q head, sequence); keys 0..pos0+s (causal, no padding mask: Appendix B.7).
-// Lane l owns dims 4l..4l+3.  Reads K/V rows straight from the paged pool (un-swizzling the chunk index).
-__global__ void attn_prefill_kernel(AttnPrefillArgs p) {
-  const int warp_in_block = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int s = blockIdx.x * (blockDim.x >> 5) + warp_in_block;
-  const int head = blockIdx.y, seq = blockIdx.z;
-  if (s >= p.seq_len) return;
-  const int group = p.n_heads / p.kv.n_kv_heads;
-  const int kvh = head / group;
-  const int n_keys = p.pos0 + s + 1;
-  const size_t qoff = ((size_t)seq * p.seq_len + s) * p.n_heads * HD + (size_t)head * HD + lane * 4;
-  const uint2 qu = *reinterpret_cast<const uint2*>(p.q + qoff);
-  const float2 q01 = unpack_bf16x2(qu.x), q23 = unpack_bf16x2(qu.y);
-  const float sc = p.scale * 1.4426950408889634f;
-  float m = -INFINITY, l = 0.f, o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
-  const int chunk = lane >> 1, within = (lane & 1) * 4;  // dims 4l..4l+3 live in chunk l/2
-  for (int k = 0; k < n_keys; ++k) {
-    const bf16* krow = p.kv.row(seq, k, 0, kvh);
-    const bf16* vrow = p.kv.row(seq, k, 1, kvh);
-    const int pc = (chunk ^ (k & 7)) * 8 + within;
-    const uint2 ku = *reinterpret_cast<const uint2*>(krow + pc);
-    const uint2 vu = *reinterpret_cast<const uint2*>(vrow + pc);
-    const float2 k01 = unpack_bf16x2(ku.x), k23 = unpack_bf16x2(ku.y);
-    float dot = q01.x * k01.x + q01.y * k01.y + q23.x * k23.x + q23.y * k23.y;
-    dot = warp_sum(dot) * sc;
-    const float m_new = fmaxf(m, dot);
-    const float corr = exp2f(m - m_new), pr = exp2f(dot - m_new);
-    const float prb = bf16_round(pr);  // P is rounded to bf16 before P*V like the fused SDPA kernels
-    const float2 v01 = unpack_bf16x2(vu.x), v23 = unpack_bf16x2(vu.y);
-    l = l * corr + pr;
-    o0 = o0 * corr + prb * v01.x, o1 = o1 * corr + prb * v01.y, o2 = o2 * corr + prb * v23.x, o3 = o3 * corr + prb * v23.y;
-    m = m_new;
+// Causal flash attention over the paged pool for S > 1 query positions (keys 0..pos0+s visible to query s, no padding
+// mask: Appendix B.7).  Grid (query tile of 64 positions, q head, sequence); 4 warps, each 16 query rows x 128 dims
+// (Q fragments in registers).  One thread streams the K and V pages of the kv head (16 KB each, already
+// chunk-swizzled) into a 2-stage shared-memory ring with 1-D TMA bulk copies; S = Q K^T and O += P V run on
+// mma.sync.m16n8k16 with the online softmax in fp32 (P rounded to bf16 for P V like the fused SDPA kernels).
+// The op is 10 GFLOP per layer at the C3 prefill (0.7 % of the layer's flops): mma.sync is ample, what matters is
+// that it is not the scalar one-warp-per-query loop it replaces (2.07 ms -> see DESIGN.md).
+constexpr int PF_QTILE = 64;
+constexpr int PF_THREADS = 128;
+constexpr int PF_STAGES = 2;
+constexpr int PF_DYN_SMEM = PF_STAGES * 2 * PAGE_BYTES + 1024;
+
+__global__ void __launch_bounds__(PF_THREADS) attn_prefill_kernel(AttnPrefillArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t full_bar[PF_STAGES];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q0 = blockIdx.x * PF_QTILE, head = blockIdx.y, seq = blockIdx.z;
+  const int group = p.n_heads / p.kv.n_kv_heads, kvh = head / group;
+  const int q_end = min(q0 + PF_QTILE, p.seq_len);
+  const int n_pages = (p.pos0 + q_end + PAGE - 1) / PAGE;  // pages holding keys visible to the tile's last query
+  if (tid == 0) {
+    for (int s = 0; s < PF_STAGES; ++s) mbar_init(&full_bar[s], 1);
+    fence_barrier_init();
   }
-  const float inv = 1.0f / l;
-  *reinterpret_cast<uint2*>(p.out + qoff) = make_uint2(pack_bf16x2(o0 * inv, o1 * inv), pack_bf16x2(o2 * inv, o3 * inv));
+  __syncthreads();
+  const int* bt = p.kv.block_table + seq * p.kv.pages_per_seq;
+  auto issue = [&](int i) {
+    const int s = i % PF_STAGES;
+    const size_t kbase = ((((size_t)p.kv.layer * p.kv.num_pages + bt[i]) * 2 + 0) * p.kv.n_kv_heads + kvh) * (size_t)(PAGE * HD);
+    const size_t vbase = kbase + (size_t)p.kv.n_kv_heads * PAGE * HD;
+    mbar_arrive_expect_tx(&full_bar[s], 2 * PAGE_BYTES);
+    bulk_g2s(smem + s * 2 * PAGE_BYTES, p.kv.pool + kbase, PAGE_BYTES, &full_bar[s]);
+    bulk_g2s(smem + s * 2 * PAGE_BYTES + PAGE_BYTES, p.kv.pool + vbase, PAGE_BYTES, &full_bar[s]);
+  };
+  if (tid == 0) issue(0);
+
+  // Q fragments (A operand of m16n8k16): rows r0 = lane/4 and r0 + 8 of the warp's 16 query positions
+  const int r0 = q0 + warp * 16 + (lane >> 2), r1 = r0 + 8;
+  const size_t row_stride = (size_t)p.n_heads * HD;
+  uint32_t qa[8][4];
+  {
+    const bf16* qp0 = p.q + ((size_t)seq * p.seq_len + r0) * row_stride + (size_t)head * HD + (lane & 3) * 2;
+    const bf16* qp1 = qp0 + 8 * row_stride;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      qa[ks][0] = qa[ks][1] = qa[ks][2] = qa[ks][3] = 0u;
+      if (r0 < p.seq_len) {
+        qa[ks][0] = *reinterpret_cast<const uint32_t*>(qp0 + ks * 16);
+        qa[ks][2] = *reinterpret_cast<const uint32_t*>(qp0 + ks * 16 + 8);
+      }
+      if (r1 < p.seq_len) {
+        qa[ks][1] = *reinterpret_cast<const uint32_t*>(qp1 + ks * 16);
+        qa[ks][3] = *reinterpret_cast<const uint32_t*>(qp1 + ks * 16 + 8);
+      }
+    }
+  }
+  float o[16][4];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  const float sc = p.scale * 1.4426950408889634f;
+  const int lim0 = p.pos0 + r0 + 1, lim1 = p.pos0 + r1 + 1;  // keys visible to the two rows
+  const int warp_last_key = p.pos0 + q0 + warp * 16 + 15;     // last key any row of this warp may see
+  const int mat = lane >> 3, mrow = lane & 7;
+
+  for (int i = 0; i < n_pages; ++i) {
+    if (tid == 0 && i + 1 < n_pages) issue(i + 1);  // its stage was released by the barrier ending iteration i - 1
+    mbar_wait(&full_bar[i % PF_STAGES], (i / PF_STAGES) & 1);
+    const int page_key0 = i * PAGE;
+    if (page_key0 <= warp_last_key) {
+      const uint32_t kbase = smem_u32(smem + (i % PF_STAGES) * 2 * PAGE_BYTES);
+      const uint32_t vbase = kbase + PAGE_BYTES;
+      // ---- S[16 x 64 keys] = Q K^T
+      float sacc[8][4];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sacc[j][0] = sacc[j][1] = sacc[j][2] = sacc[j][3] = 0.f;
+#pragma unroll
+      for (int kb = 0; kb < 4; ++kb) {
+        const int key = kb * 16 + (mat >> 1) * 8 + mrow;  // matrices 0,1: keys 0-7; 2,3: keys 8-15
+        const uint32_t rowaddr = kbase + key * 256;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const int chunk = ks * 2 + (mat & 1);
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4(rowaddr + ((chunk ^ (key & 7)) << 4), b0, b1, b2, b3);
+          mma_bf16_16816(sacc[2 * kb], qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], b0, b1);
+          mma_bf16_16816(sacc[2 * kb + 1], qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], b2, b3);
+        }
+      }
+      // ---- causal mask + online softmax (row r0: c0,c1; row r1: c2,c3; a row lives in the 4 lanes of a quad)
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int kc = page_key0 + nt * 8 + (lane & 3) * 2;
+        sacc[nt][0] = (kc < lim0) ? sacc[nt][0] * sc : -INFINITY;
+        sacc[nt][1] = (kc + 1 < lim0) ? sacc[nt][1] * sc : -INFINITY;
+        sacc[nt][2] = (kc < lim1) ? sacc[nt][2] * sc : -INFINITY;
+        sacc[nt][3] = (kc + 1 < lim1) ? sacc[nt][3] * sc : -INFINITY;
+        mx0 = fmaxf(mx0, fmaxf(sacc[nt][0], sacc[nt][1]));
+        mx1 = fmaxf(mx1, fmaxf(sacc[nt][2], sacc[nt][3]));
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+      const float ms0 = (mn0 == -INFINITY) ? 0.f : mn0, ms1 = (mn1 == -INFINITY) ? 0.f : mn1;
+      const float corr0 = exp2f(m0 - ms0), corr1 = exp2f(m1 - ms1);
+      float ps0 = 0.f, ps1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        sacc[nt][0] = exp2f(sacc[nt][0] - ms0), sacc[nt][1] = exp2f(sacc[nt][1] - ms0);
+        sacc[nt][2] = exp2f(sacc[nt][2] - ms1), sacc[nt][3] = exp2f(sacc[nt][3] - ms1);
+        ps0 += sacc[nt][0] + sacc[nt][1];
+        ps1 += sacc[nt][2] + sacc[nt][3];
+      }
+      ps0 += __shfl_xor_sync(0xffffffffu, ps0, 1);
+      ps0 += __shfl_xor_sync(0xffffffffu, ps0, 2);
+      ps1 += __shfl_xor_sync(0xffffffffu, ps1, 1);
+      ps1 += __shfl_xor_sync(0xffffffffu, ps1, 2);
+      l0 = l0 * corr0 + ps0, l1 = l1 * corr1 + ps1;
+      m0 = mn0, m1 = mn1;
+#pragma unroll
+      for (int nt = 0; nt < 16; ++nt) o[nt][0] *= corr0, o[nt][1] *= corr0, o[nt][2] *= corr1, o[nt][3] *= corr1;
+      // ---- O[16 x 128] += P V
+#pragma unroll
+      for (int kb = 0; kb < 4; ++kb) {
+        const uint32_t pa0 = pack_bf16x2(sacc[2 * kb][0], sacc[2 * kb][1]), pa1 = pack_bf16x2(sacc[2 * kb][2], sacc[2 * kb][3]);
+        const uint32_t pa2 = pack_bf16x2(sacc[2 * kb + 1][0], sacc[2 * kb + 1][1]);
+        const uint32_t pa3 = pack_bf16x2(sacc[2 * kb + 1][2], sacc[2 * kb + 1][3]);
+        const int key = kb * 16 + (mat & 1) * 8 + mrow;  // matrices 0,2: keys 0-7; 1,3: keys 8-15
+        const uint32_t rowaddr = vbase + key * 256;
+#pragma unroll
+        for (int nt = 0; nt < 16; nt += 2) {
+          const int chunk = nt + (mat >> 1);  // 8 dims per chunk
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(rowaddr + ((chunk ^ (key & 7)) << 4), b0, b1, b2, b3);
+          mma_bf16_16816(o[nt], pa0, pa1, pa2, pa3, b0, b1);
+          mma_bf16_16816(o[nt + 1], pa0, pa1, pa2, pa3, b2, b3);
+        }
+      }
+    }
+    __syncthreads();  // every warp is done with this stage before it is refilled
+  }
+  const float inv0 = 1.0f / l0, inv1 = 1.0f / l1;
+  bf16* op0 = p.out + ((size_t)seq * p.seq_len + r0) * row_stride + (size_t)head * HD + (lane & 3) * 2;
+  bf16* op1 = op0 + 8 * row_stride;
+#pragma unroll
+  for (int nt = 0; nt < 16; ++nt) {
+    if (r0 < p.seq_len) *reinterpret_cast<uint32_t*>(op0 + nt * 8) = pack_bf16x2(o[nt][0] * inv0, o[nt][1] * inv0);
+    if (r1 < p.seq_len) *reinterpret_cast<uint32_t*>(op1 + nt * 8) = pack_bf16x2(o[nt][2] * inv1, o[nt][3] * inv1);
+  }
 }
 
 cudaError_t launch_attn_prefill(const AttnPrefillArgs& a, int n_seq, cudaStream_t st) {
-  const int warps = 4;
-  dim3 grid(ceil_div(a.seq_len, warps), a.n_heads, n_seq);
-  attn_prefill_kernel<<<grid, warps * 32, 0, st>>>(a);
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(attn_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_DYN_SMEM);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid(ceil_div(a.seq_len, PF_QTILE), a.n_heads, n_seq);
+  attn_prefill_kernel<<<grid, PF_THREADS, PF_DYN_SMEM, st>>>(a);
   return cudaGetLastError();
 }
 

@@ -33,7 +33,17 @@ struct EpiStoreBf16 {
     if (!valid) return;
     bf16* o = out + (size_t)(m_tile * GEMM_BM + row) * ldo + n_tile * NT;
     const int n0 = n_tile * NT;
-    if (n0 + NT <= n_valid && (ldo % 8) == 0) {
+    if (n0 + NT <= n_valid && (ldo % 16) == 0 && (NT % 16) == 0 && (reinterpret_cast<uintptr_t>(out) & 31) == 0) {
+#pragma unroll
+      for (int c = 0; c < NT; c += 16) {  // lane == row: 32 bytes per store instruction (256-bit STG)
+        uint4 v, u;
+        v.x = pack_bf16x2(acc[c], acc[c + 1]), v.y = pack_bf16x2(acc[c + 2], acc[c + 3]);
+        v.z = pack_bf16x2(acc[c + 4], acc[c + 5]), v.w = pack_bf16x2(acc[c + 6], acc[c + 7]);
+        u.x = pack_bf16x2(acc[c + 8], acc[c + 9]), u.y = pack_bf16x2(acc[c + 10], acc[c + 11]);
+        u.z = pack_bf16x2(acc[c + 12], acc[c + 13]), u.w = pack_bf16x2(acc[c + 14], acc[c + 15]);
+        stg256(o + c, v, u);
+      }
+    } else if (n0 + NT <= n_valid && (ldo % 8) == 0) {
 #pragma unroll
       for (int c = 0; c < NT; c += 8) {
         uint4 v;
@@ -56,9 +66,11 @@ struct EpiPartial {
   int rows, ldn;
   __device__ void partial(int row, bool valid, int n_tile, int split, const float* acc) const {
     if (!valid) return;
-    float4* o = reinterpret_cast<float4*>(ws + ((size_t)split * rows + row) * ldn + n_tile * 64);
+    float* o = ws + ((size_t)split * rows + row) * ldn + n_tile * 64;
+    const uint32_t* a = reinterpret_cast<const uint32_t*>(acc);
 #pragma unroll
-    for (int c = 0; c < 16; ++c) o[c] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+    for (int c = 0; c < 64; c += 8)  // ws is 256-byte aligned and ldn a multiple of 64: 32-byte pieces
+      stg256(o + c, make_uint4(a[c], a[c + 1], a[c + 2], a[c + 3]), make_uint4(a[c + 4], a[c + 5], a[c + 6], a[c + 7]));
   }
   __device__ void operator()(int, bool, int, int, float*) const {}
   // Warp-collective variant at 128 rows: lane == row would store 16 bytes to 32 different 128-byte lines per
@@ -90,15 +102,28 @@ struct EpiResidual {
   __device__ void operator()(int row, bool valid, int m_tile, int n_tile, float* acc) const {
     if (!valid) return;
     bf16* o = x + (size_t)(m_tile * GEMM_BM + row) * ldx + n_tile * NT;
-#pragma unroll
-    for (int c = 0; c < NT; c += 8) {
-      uint4 r = *reinterpret_cast<const uint4*>(o + c);
+    auto add8 = [&](uint4& r, int c) {
       const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), cc = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
       r.x = pack_bf16x2(a.x + bf16_round(acc[c]), a.y + bf16_round(acc[c + 1]));
       r.y = pack_bf16x2(b.x + bf16_round(acc[c + 2]), b.y + bf16_round(acc[c + 3]));
       r.z = pack_bf16x2(cc.x + bf16_round(acc[c + 4]), cc.y + bf16_round(acc[c + 5]));
       r.w = pack_bf16x2(d.x + bf16_round(acc[c + 6]), d.y + bf16_round(acc[c + 7]));
-      *reinterpret_cast<uint4*>(o + c) = r;
+    };
+    if ((NT % 16) == 0 && (ldx % 16) == 0 && (reinterpret_cast<uintptr_t>(x) & 31) == 0) {
+#pragma unroll
+      for (int c = 0; c < NT; c += 16) {  // lane == row: 32 bytes per instruction (256-bit LDG / STG)
+        uint4 r, q;
+        ldg256(o + c, r, q);
+        add8(r, c), add8(q, c + 8);
+        stg256(o + c, r, q);
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < NT; c += 8) {
+        uint4 r = *reinterpret_cast<const uint4*>(o + c);
+        add8(r, c);
+        *reinterpret_cast<uint4*>(o + c) = r;
+      }
     }
   }
 };
