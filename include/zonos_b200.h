@@ -49,6 +49,9 @@ int64_t zb200_packed_weight_bytes(int n_rows, int k, int tile_n, int row_mode, i
  * may be NULL when splits == 1. */
 int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int splits,
                     float* ws, int* tickets, void* stream);
+/* Same contract (no split-K) through the persistent many-row kernel of the prefill (csrc/gemm_big.cuh): A by 2-D TMA,
+ * two TMEM accumulators.  lda must be a multiple of 8 elements, k a multiple of 64. */
+int zb200_gemm_big_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, void* stream);
 /* Same contract for m <= 128 rows through the weight-streaming stream-K kernel of the decode step (csrc/gemm_skinny.cuh)
  * on `grid` CTAs.  ws: >= grid * 32768 floats, tickets: >= ceil(n/64) zeroed ints. */
 int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int grid,

@@ -46,6 +46,21 @@ def test_gemm_tcgen05(ops, M, N, K, splits):
     assert torch.equal(out, out2)
 
 
+@pytest.mark.parametrize("M,N,K", [(2, 64, 64), (130, 256, 8192), (300, 512, 1024), (700, 1026, 512), (260, 384, 1024),
+                                   (1000, 3072, 2048), (17664, 2048, 2048), (5000, 320, 128), (4096, 16384, 2048)])
+def test_gemm_big_persistent(ops, M, N, K):
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    wp = ops.pack_weight(w)
+    out = ops.gemm_big_bf16(a, wp, N)
+    ref = (a.float() @ w.float().t())
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2 * max(1.0, ref.abs().max().item()), err
+    # same accumulation order as the per-tile kernel (one UMMA chain over K): bitwise equal outputs
+    assert torch.equal(out, ops.gemm_bf16(a, wp, N, splits=1))
+
+
 @pytest.mark.parametrize("M,N,K,grid", [(2, 64, 64, 1), (2, 192, 512, 5), (2, 3072, 2048, 148), (128, 3072, 2048, 148),
                                         (128, 2048, 2048, 148), (7, 1026, 512, 37), (100, 256, 8192, 148), (2, 2048, 8192, 148),
                                         (2, 16384, 2048, 148), (20, 2048, 8192, 111), (128, 16384, 2048, 74), (64, 9792, 2048, 148),

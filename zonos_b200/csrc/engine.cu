@@ -7,12 +7,14 @@
 #include "epilogues.cuh"
 #include "epilogues_t.cuh"
 #include "gemm_skinny.cuh"
+#include "gemm_big.cuh"
 #include "gemm_swap.cuh"
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 #include "sampler.cuh"
 
 #include <algorithm>
+#include <type_traits>
 #include <cstdlib>
 
 using namespace zb;
@@ -180,6 +182,16 @@ cudaError_t gemm_any(const zb200_engine* e, const void* w, int n_tiles, int rows
     return launch_gemm_skinny(g, al, epi, p.grid, st, p.prefer_k1);
   }
   GemmCore g = make_core(d, w, n_tiles, rows, k);
+  if constexpr (std::is_same<ALoader, ARowMajor>::value) {
+    // Many row tiles (the batched prefill): the persistent kernel overlaps each tile's epilogue with the next tile's
+    // MMAs.  Small problems keep the per-tile kernel (split-K fills the SMs there).
+    static const bool no_big = getenv("ZB200_NO_BIG") != nullptr;
+    const int m_tiles = ceil_div(rows, GEMM_BM);
+    if (!no_big && g.splits == 1 && e->sk_sms > 0 && m_tiles * ceil_div(n_tiles, 4) >= e->sk_sms) {
+      const cudaError_t rc = launch_gemm_big<1>(al.base, al.row_bytes, rows, k, w, n_tiles, epi, e->sk_sms, st);
+      if (rc != cudaErrorNotSupported) return rc;
+    }
+  }
   return launch_gemm_tc<NT, STAGES, 1>(g, al, epi, n_tiles, ceil_div(rows, GEMM_BM), st);
 }
 

@@ -5,6 +5,7 @@
 #include "epilogues_t.cuh"
 #include "gemm_skinny.cuh"
 #include "gemm_swap.cuh"
+#include "gemm_big.cuh"
 #include "gemm_tc.cuh"
 #include "ops.cuh"
 
@@ -341,6 +342,18 @@ extern "C" int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_pack
   ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
   EpiStoreBf16<NT> epi{(bf16*)out, ldo, n};
   ZB_CHECK_CUDA((launch_gemm_tc<NT, 6, 1>(g, al, epi, ceil_div(n, NT), ceil_div(m, GEMM_BM), (cudaStream_t)stream)));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_gemm_big_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo,
+                                   void* stream) {
+  ZB_REQUIRE(m > 0 && n > 0 && k > 0 && k % 64 == 0 && lda % 8 == 0, "gemm_big: bad shape m=%d n=%d k=%d lda=%d", m, n, k, lda);
+  ZB_REQUIRE((reinterpret_cast<uintptr_t>(a) & 15) == 0, "gemm_big: A must be 16-byte aligned");
+  int dev = 0, sms = 0;
+  ZB_CHECK_CUDA(cudaGetDevice(&dev));
+  ZB_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  EpiStoreBf16<64> epi{(bf16*)out, ldo, n};
+  ZB_CHECK_CUDA((launch_gemm_big<1>(a, (size_t)lda * 2, m, k, w_packed, ceil_div(n, 64), epi, sms, (cudaStream_t)stream)));
   return ZB200_OK;
 }
 

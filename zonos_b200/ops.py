@@ -70,6 +70,15 @@ def gemm_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, splits: int = 1) 
     return out
 
 
+def gemm_big_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int) -> torch.Tensor:
+    """Test hook: bf16 [M,K] x packed [N,K]^T -> bf16 [M,N] through the persistent many-row kernel of the prefill."""
+    a = _cuda(a, torch.bfloat16)
+    M, K = a.shape
+    out = torch.empty(M, n, dtype=torch.bfloat16, device=a.device)
+    check(lib().zb200_gemm_big_bf16(ptr(a), M, K, ptr(w_packed), n, K, ptr(out), n, stream_ptr()), "gemm_big_bf16")
+    return out
+
+
 def gemm_skinny_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, grid: int = 148, ws=None, tickets=None) -> torch.Tensor:
     """Test hook: bf16 [M<=128,K] x packed [N,K]^T -> bf16 [M,N] through the weight-streaming stream-K kernel."""
     a = _cuda(a, torch.bfloat16)
