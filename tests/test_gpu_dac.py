@@ -63,3 +63,18 @@ def test_dac_decode_rejects_wrong_codebook_count():
     ae = _decoder(shapes.DAC_TINY)
     with pytest.raises(AssertionError):
         ae.decode(torch.zeros(1, 8, 4, dtype=torch.int64, device="cuda"))
+
+
+def test_dac_tma_epilogue_matches_direct_epilogue(monkeypatch):
+    """The 1x1 convs' epilogue through the TMA unit (residual boxes in, raw / activated boxes out) must give the same
+    bits as the direct load / store epilogue, at lengths that leave partial 32-row boxes and partial tiles."""
+    ae = _decoder(shapes.DAC)
+    g = torch.Generator().manual_seed(11)
+    for B, T in [(1, 1), (2, 37), (3, 130)]:
+        codes = torch.randint(0, 1024, (B, 9, T), generator=g).cuda()
+        monkeypatch.setenv("ZB200_DAC_TE", "0")
+        direct = ae.decode(codes).cpu()
+        monkeypatch.setenv("ZB200_DAC_TE", "1")
+        tma = ae.decode(codes).cpu()
+        assert torch.isfinite(tma).all()
+        assert torch.equal(direct, tma), (B, T, float((direct - tma).abs().max()))

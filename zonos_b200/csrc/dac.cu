@@ -12,6 +12,7 @@
 // (:94-99) never makes its own pass over memory.  fp16 storage / fp32 accumulate mirrors the reference's CUDA autocast.
 #include "../../include/zonos_b200.h"
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "dac_conv.cuh"
@@ -100,7 +101,13 @@ static int sm_count() {
   }();
   return n;
 }
-template <int NT>
+// Epilogue traffic through the TMA unit for the layers whose epilogue moves the most bytes per flop: the 1x1 convs that
+// close a residual unit (residual in, raw + activated out).  ZB200_DAC_TE=0 switches back to direct loads / stores.
+static bool dac_te_enabled() {
+  const char* v = getenv("ZB200_DAC_TE");  // read per call: the parity test compares both epilogues in one process
+  return !(v && atoi(v) == 0);
+}
+template <int NT, bool TE>
 static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
   const int T_in = L.t_mul_in * T;
   DacConvArgs a{};
@@ -120,7 +127,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   ZB_REQUIRE(a.halo_rows <= 256, "dac_decode: filter span %d too wide for one TMA box", a.halo_rows - 128);
   a.a_stage_bytes = (a.halo_rows * 128 + 1023) & ~1023;
   a.w_stage_bytes = a.tpc * NT * 128;
-  const int budget = DC_SMEM_BYTES - DC_BAR_BYTES - 1024;
+  const int budget = DC_SMEM_BYTES - DC_BAR_BYTES - 1024 - (TE ? DC_E_EXTRA : 0);
   const int kb = a.taps * a.cblocks;
   a.w_resident = a.n_groups == 1 && kb <= DC_MAX_SW && kb * a.w_stage_bytes + 2 * a.a_stage_bytes <= budget;
   if (a.w_resident) {
@@ -153,14 +160,31 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   ZB_REQUIRE(cr == CUDA_SUCCESS, "dac_decode: cuTensorMapEncodeTiled failed (%d)", (int)cr);
+  CUtensorMap rmap = xmap, rawmap = xmap, actmap = xmap;
+  if (TE) {  // [batch][T_out][C_out] fp16, 32-channel x 32-row boxes, 64-byte swizzle (conflict-free row-per-thread access)
+    ZB_REQUIRE(a.up == 0 && a.pitch_out % 32 == 0 && a.n_total == a.C_out && a.C_out % 32 == 0,
+               "dac_decode: TMA epilogue needs a plain conv with a multiple of 32 output channels");
+    const cuuint64_t odim[3] = {(cuuint64_t)a.C_out, (cuuint64_t)a.T_out, (cuuint64_t)batch};
+    const cuuint64_t ostr[2] = {(cuuint64_t)a.pitch_out * 2, (cuuint64_t)a.T_out * a.pitch_out * 2};
+    const cuuint32_t obox[3] = {32, 32, 1};
+    const void* ptrs[3] = {a.resid, a.out_raw, a.out_act};
+    CUtensorMap* maps[3] = {&rmap, &rawmap, &actmap};
+    for (int i = 0; i < 3; ++i) {
+      if (!ptrs[i]) continue;
+      const CUresult r2 = enc(maps[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(ptrs[i]), odim, ostr, obox, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      ZB_REQUIRE(r2 == CUDA_SUCCESS, "dac_decode: cuTensorMapEncodeTiled (epilogue map %d) failed (%d)", i, (int)r2);
+    }
+  }
 
-  auto kern = dac_conv_kernel<NT>;
+  auto kern = dac_conv_kernel<NT, TE>;
   static bool configured = false;  // per template instantiation
   if (!configured) {
     ZB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DC_SMEM_BYTES));
     configured = true;
   }
-  const int smem = a.sa * a.a_stage_bytes + a.sw * a.w_stage_bytes + DC_BAR_BYTES + 1024;
+  const int smem = a.sa * a.a_stage_bytes + a.sw * a.w_stage_bytes + DC_BAR_BYTES + 1024 + (TE ? DC_E_EXTRA : 0);
   const int grid = a.total_tiles < sm_count() ? a.total_tiles : sm_count();
 #ifdef SK_TRACE
   static long long* trace_buf = nullptr;
@@ -168,7 +192,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   cudaMemsetAsync(trace_buf, 0, 256 * 8 * sizeof(long long), st);
   a.trace = trace_buf;
 #endif
-  kern<<<grid, DC_THREADS, smem, st>>>(xmap, a);
+  kern<<<grid, DC_THREADS, smem, st>>>(xmap, rmap, rawmap, actmap, a);
   ZB_CHECK_LAUNCH("dac_conv_kernel");
 #ifdef SK_TRACE
   {
@@ -211,7 +235,9 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
   }
   for (int i = 0; i < p->n_layers; ++i) {
     const zb200_dac_layer& L = p->layers[i];
-    const int rc = L.tile_n == 96 ? launch_dac_conv<96>(L, batch, t, regions, st) : launch_dac_conv<64>(L, batch, t, regions, st);
+    const bool te = dac_te_enabled() && L.up == 0 && L.taps == 1 && L.c_out % 32 == 0 && L.pitch_out % 32 == 0;
+    const int rc = L.tile_n == 96 ? (te ? launch_dac_conv<96, true>(L, batch, t, regions, st) : launch_dac_conv<96, false>(L, batch, t, regions, st))
+                                  : (te ? launch_dac_conv<64, true>(L, batch, t, regions, st) : launch_dac_conv<64, false>(L, batch, t, regions, st));
     if (rc != ZB200_OK) return rc;
   }
   {

@@ -33,6 +33,13 @@ constexpr int DC_PF_TILES = 3;  // L2 prefetch distance of the activation boxes,
 constexpr int DC_MAX_SW = 16;   // weight ring depth / resident k-blocks
 constexpr int DC_SMEM_BYTES = 216 * 1024;  // dynamic; + 6.6 KB static epilogue constants < 227 KB
 constexpr int DC_BAR_BYTES = (2 * DC_MAX_SA + 2 * DC_MAX_SW + 4) * 8 + 16;
+// TMA epilogue (template flag TE): every epilogue warp owns a ring of DC_E_RS slots (residual box in, raw result out,
+// in place) and DC_E_AS slots for the Snake-activated result; a slot is one 32-row x 32-channel fp16 box (SWIZZLE_64B).
+constexpr int DC_E_RS = 3, DC_E_AS = 2, DC_E_SLOT = 2048;
+constexpr int DC_E_WARP_BYTES = (DC_E_RS + DC_E_AS) * DC_E_SLOT;
+constexpr int DC_E_BYTES = (DC_EPI_THREADS / 32) * DC_E_WARP_BYTES;
+constexpr int DC_E_BAR_BYTES = (DC_EPI_THREADS / 32) * DC_E_RS * 8;
+constexpr int DC_E_EXTRA = DC_E_BAR_BYTES + 1024 + DC_E_BYTES;  // barriers + alignment slack + slots
 
 struct DacConvArgs {
   const uint8_t* Wp;       // packed weights
@@ -68,6 +75,20 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
       "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
       : "memory");
 }
+
+// 3-D tiled TMA store shared -> global (SASS: UTMASTG), bulk-group completion; elements outside the tensor are dropped.
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() {  // at most N groups still reading their shared-memory source
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_group_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // Snake1d (modeling_dac.py:94-99): x + 1/(alpha+1e-9) * sin(alpha*x)^2.  sin^2 has period pi: reduce alpha*x to
 // [-pi/2, pi/2] with a two-constant Cody-Waite step, then the SFU sine (abs. error ~5e-7 there) -- the result is
@@ -114,9 +135,12 @@ __device__ __forceinline__ void dc_tile_coords(const DacConvArgs& a, int tile, i
   group = tile - m_tile * a.n_groups;
 }
 
-template <int NT>
+// TE: epilogue traffic through the TMA unit (plain convs: residual boxes in, raw / activated boxes out); the maps are
+// [batch][T_out][C_out] fp16 with a 32 x 32 x 1 box.  TE == false: direct global loads / stores from the epilogue threads.
+template <int NT, bool TE>
 __global__ void __launch_bounds__(DC_THREADS, 1)
-dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
+dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap rmap,
+                const __grid_constant__ CUtensorMap rawmap, const __grid_constant__ CUtensorMap actmap, const DacConvArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_ring = smem;
@@ -128,6 +152,9 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
   uint64_t* t_full = w_empty + DC_MAX_SW;
   uint64_t* t_empty = t_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+  uint64_t* e_full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(a_full) + DC_BAR_BYTES);  // TE: [warp][DC_E_RS]
+  uint8_t* e_buf = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(e_full) + DC_E_BAR_BYTES + 1023) & ~uintptr_t(1023));            // TE: [warp][slots]
 
   // per-column epilogue constants of the current column group (two copies: tiles alternate when n_groups > 1)
   __shared__ __align__(16) float s_bias[2][256], s_alpha[2][256], s_inv[2][256];
@@ -140,6 +167,8 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
     for (int s = 0; s < DC_MAX_SA; ++s) mbar_init(&a_full[s], 1), mbar_init(&a_empty[s], 1);
     for (int s = 0; s < DC_MAX_SW; ++s) mbar_init(&w_full[s], 1), mbar_init(&w_empty[s], 1);
     for (int s = 0; s < 2; ++s) mbar_init(&t_full[s], 1), mbar_init(&t_empty[s], DC_EPI_THREADS / 32);
+    if constexpr (TE)
+      for (int s = 0; s < (DC_EPI_THREADS / 32) * DC_E_RS; ++s) mbar_init(&e_full[s], 1);
     fence_barrier_init();
   }
   if (warp == 9) tmem_alloc(tmem_slot, 512);
@@ -264,6 +293,169 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const DacConvArgs a) {
       }
 #endif
     }
+  } else if constexpr (TE) {
+    // ---------------------------------------------------------------- epilogue through the TMA unit (plain convs)
+    // Warp (q, par) owns rows 32q.. of every tile and every second 32-channel block of the CTA's block sequence
+    // (tiles in order, blocks in order inside a tile; odd block counts alternate between the two warps of a row
+    // quarter).  Per block: the residual box arrives in a ring slot two blocks ahead, the thread (= row) reads its
+    // 64 bytes, writes the raw result back in place and the activated one to a second slot; one lane stores both boxes
+    // with the TMA unit and refills the slot whose store has finished reading.  No global access goes through the LSU.
+    const int q = warp & 3, par = warp >> 2;
+    uint8_t* my = e_buf + warp * DC_E_WARP_BYTES;
+    uint64_t* my_full = e_full + warp * DC_E_RS;
+    const bool has_resid = a.resid != nullptr, has_raw = a.out_raw != nullptr, has_act = a.out_act != nullptr;
+    const uint32_t row_off = lane * 64, sw_x = (lane >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk ^= (row >> 1) & 3
+    auto blocks_of = [&](int it_) -> int {  // 32-channel blocks of this CTA's it_-th tile (0 past the end)
+      const int tile = blockIdx.x + it_ * gridDim.x;
+      if (tile >= a.total_tiles) return 0;
+      const int group = a.n_groups == 1 ? 0 : tile % a.n_groups;
+      return min(a.tpc, a.n_tiles - group * a.tpc) * (NT / 32);
+    };
+    auto normalize = [&](int& it_, int& cbk_) {
+      for (int nb = blocks_of(it_); nb > 0 && cbk_ >= nb; nb = blocks_of(it_)) cbk_ -= nb, ++it_;
+    };
+    auto box_coords = [&](int it_, int cbk_, int& c0, int& t, int& b) {
+      int m_tile, group;
+      dc_tile_coords(a, blockIdx.x + it_ * gridDim.x, m_tile, group);
+      b = m_tile / a.tiles_per_seq;
+      t = (m_tile - b * a.tiles_per_seq) * 128 + q * 32;
+      c0 = group * a.tpc * NT + cbk_ * 32;
+    };
+    auto issue_load = [&](int it_, int cbk_, int idx_) {  // lane 0
+      if (!has_resid || blocks_of(it_) == 0) return;
+      int c0, t, b;
+      box_coords(it_, cbk_, c0, t, b);
+      const int slot = idx_ % DC_E_RS;
+      mbar_arrive_expect_tx(&my_full[slot], DC_E_SLOT);
+      tma_load_3d(my + slot * DC_E_SLOT, &rmap, c0, t, b, &my_full[slot]);
+    };
+    int cur_it = 0, cur_cbk = par, pf_it, pf_cbk, idx = 0, n_issued = 0;
+    normalize(cur_it, cur_cbk);
+    pf_it = cur_it, pf_cbk = cur_cbk;
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&rmap)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&rawmap)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&actmap)) : "memory");
+    }
+    for (int k = 0; k < DC_E_RS - 1; ++k) {
+      if (lane == 0) issue_load(pf_it, pf_cbk, n_issued);
+      ++n_issued, pf_cbk += 2;
+      normalize(pf_it, pf_cbk);
+    }
+    [[maybe_unused]] long long tr_tf = 0, tr_start = clock64();
+    for (int it = 0;; ++it) {
+      const int tile = blockIdx.x + it * gridDim.x;
+      if (tile >= a.total_tiles) break;
+      int m_tile, group;
+      dc_tile_coords(a, tile, m_tile, group);
+      const int n0 = group * a.tpc * NT;
+      const int n_cols = min(a.tpc, a.n_tiles - group * a.tpc) * NT;
+      const int buf = it & 1;
+      const int cbuf = a.n_groups == 1 ? 0 : buf;
+      if (a.n_groups > 1 || it == 0) {
+        const int col = tid, n = n0 + col;
+        if (col < n_cols) {
+          const bool ok = n < a.n_total;
+          s_bias[cbuf][col] = ok ? __ldg(a.bias + n) : 0.f;
+          s_alpha[cbuf][col] = ok && has_act ? __ldg(a.alpha + n) : 0.f;
+          s_inv[cbuf][col] = ok && has_act ? __ldg(a.inv_alpha + n) : 0.f;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+      }
+      DC_TIMED_WAIT(tr_tf, &t_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
+      bool released = false;
+      while (cur_it == it) {
+        const int cbk = cur_cbk;
+        int nxt_it = cur_it, nxt_cbk = cur_cbk + 2;
+        normalize(nxt_it, nxt_cbk);
+        uint8_t* rs = my + (idx % DC_E_RS) * DC_E_SLOT;
+        uint8_t* as = my + (DC_E_RS + idx % DC_E_AS) * DC_E_SLOT;
+        float acc[2][16];
+        tmem_ld16(taddr + cbk * 32, acc[0]);
+        tmem_ld16(taddr + cbk * 32 + 16, acc[1]);
+        if (has_resid) mbar_wait(&my_full[idx % DC_E_RS], (idx / DC_E_RS) & 1);
+        tmem_ld_wait();
+        if (nxt_it != it) {  // last TMEM read of this warp in this tile: hand the accumulator back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&t_empty[buf]);
+          released = true;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            const int col = cbk * 32 + h * 16 + g * 8;
+            const uint32_t off = row_off + ((uint32_t)((h * 2 + g) ^ sw_x) << 4);
+            const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col + 4]);
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[h][g * 8 + i] + bb[i]));
+            if (has_resid) {
+              const uint4 ru = *reinterpret_cast<const uint4*>(rs + off);
+              const __half2* rh = reinterpret_cast<const __half2*>(&ru);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float2 rf = __half22float2(rh[i]);
+                v[2 * i] = __half2float(__float2half_rn(v[2 * i] + rf.x));
+                v[2 * i + 1] = __half2float(__float2half_rn(v[2 * i + 1] + rf.y));
+              }
+            }
+            if (has_raw) {
+              uint4 o;
+              __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+              *reinterpret_cast<uint4*>(rs + off) = o;
+            }
+            if (has_act) {
+              const float4 a0 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col]);
+              const float4 a1 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col + 4]);
+              const float4 i0 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col]);
+              const float4 i1 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col + 4]);
+              const float al[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+              const float ia[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+              uint4 o;
+              __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                oh[i] = __floats2half2_rn(snake_fast(v[2 * i], al[2 * i], ia[2 * i]),
+                                          snake_fast(v[2 * i + 1], al[2 * i + 1], ia[2 * i + 1]));
+              *reinterpret_cast<uint4*>(as + off) = o;
+            }
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          int c0, t, b;
+          box_coords(it, cbk, c0, t, b);
+          if (has_raw) tma_store_3d(&rawmap, rs, c0, t, b);
+          if (has_act) tma_store_3d(&actmap, as, c0, t, b);
+          bulk_commit_group();
+          bulk_wait_group_read<1>();  // the previous block's boxes have left shared memory: its slots are free
+          issue_load(pf_it, pf_cbk, n_issued);
+        }
+        ++n_issued, pf_cbk += 2;
+        normalize(pf_it, pf_cbk);
+        __syncwarp();
+        cur_it = nxt_it, cur_cbk = nxt_cbk, ++idx;
+      }
+      if (!released) {  // (a tile with a single block belongs to one of the two warps only)
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[buf]);
+      }
+    }
+    if (lane == 0) bulk_wait_group_all();
+#ifdef SK_TRACE
+    if (a.trace && tid == 0) a.trace[blockIdx.x * 8 + 4] = tr_tf, a.trace[blockIdx.x * 8 + 5] = clock64() - tr_start;
+#endif
+    tc_fence_before();
   } else {
     // ---------------------------------------------------------------- epilogue: TMEM -> bias/residual/Snake -> fp16 rows
     const int q = warp & 3, par = warp >> 2;
