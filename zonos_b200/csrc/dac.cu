@@ -136,6 +136,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   } else {
     a.sa = 3;
     a.sw = (budget - a.sa * a.a_stage_bytes) / a.w_stage_bytes;
+    if (a.sw < 2) a.sa = 2, a.sw = (budget - a.sa * a.a_stage_bytes) / a.w_stage_bytes;
   }
   a.sa = a.sa > DC_MAX_SA ? DC_MAX_SA : a.sa;
   a.sw = a.sw > DC_MAX_SW ? DC_MAX_SW : a.sw;
@@ -162,8 +163,8 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   ZB_REQUIRE(cr == CUDA_SUCCESS, "dac_decode: cuTensorMapEncodeTiled failed (%d)", (int)cr);
   CUtensorMap rmap = xmap, rawmap = xmap, actmap = xmap;
   if (TE) {  // [batch][T_out][C_out] fp16, 32-channel x 32-row boxes, 64-byte swizzle (conflict-free row-per-thread access)
-    ZB_REQUIRE(a.up == 0 && a.pitch_out % 32 == 0 && a.n_total == a.C_out && a.C_out % 32 == 0,
-               "dac_decode: TMA epilogue needs a plain conv with a multiple of 32 output channels");
+    ZB_REQUIRE(a.up == 0 && a.pitch_out % 32 == 0 && a.n_total == a.C_out && a.C_out % 32 == 0 && a.n_tiles == a.tpc * a.n_groups,
+               "dac_decode: TMA epilogue needs a plain conv with a multiple of 32 output channels and equal column groups");
     const cuuint64_t odim[3] = {(cuuint64_t)a.C_out, (cuuint64_t)a.T_out, (cuuint64_t)batch};
     const cuuint64_t ostr[2] = {(cuuint64_t)a.pitch_out * 2, (cuuint64_t)a.T_out * a.pitch_out * 2};
     const cuuint32_t obox[3] = {32, 32, 1};
@@ -192,7 +193,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   cudaMemsetAsync(trace_buf, 0, 256 * 8 * sizeof(long long), st);
   a.trace = trace_buf;
 #endif
-  kern<<<grid, DC_THREADS, smem, st>>>(xmap, rmap, rawmap, actmap, a);
+  kern<<<grid, DcCfg<TE>::THREADS, smem, st>>>(xmap, rmap, rawmap, actmap, a);
   ZB_CHECK_LAUNCH("dac_conv_kernel");
 #ifdef SK_TRACE
   {
@@ -235,7 +236,11 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
   }
   for (int i = 0; i < p->n_layers; ++i) {
     const zb200_dac_layer& L = p->layers[i];
-    const bool te = dac_te_enabled() && L.up == 0 && L.taps == 1 && L.c_out % 32 == 0 && L.pitch_out % 32 == 0;
+    bool te = dac_te_enabled() && L.up == 0 && L.taps == 1 && L.c_out % 32 == 0 && L.pitch_out % 32 == 0;
+    if (te) {  // all column groups of a tile must be alike (the epilogue warps walk a fixed block sequence)
+      const int n_tiles = ceil_div(L.c_out, L.tile_n), max_tpc = 256 / L.tile_n, n_groups = ceil_div(n_tiles, max_tpc);
+      te = n_tiles % n_groups == 0 && L.c_out % L.tile_n == 0;
+    }
     const int rc = L.tile_n == 96 ? (te ? launch_dac_conv<96, true>(L, batch, t, regions, st) : launch_dac_conv<96, false>(L, batch, t, regions, st))
                                   : (te ? launch_dac_conv<64, true>(L, batch, t, regions, st) : launch_dac_conv<64, false>(L, batch, t, regions, st));
     if (rc != ZB200_OK) return rc;

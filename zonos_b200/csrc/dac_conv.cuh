@@ -26,19 +26,28 @@ namespace zb {
 
 typedef __half f16;
 
-constexpr int DC_THREADS = 352;
-constexpr int DC_EPI_THREADS = 256;
+#ifndef DC_TE_WARPS
+#define DC_TE_WARPS 12
+#endif
+// Epilogue warps: 8 with the direct epilogue (165 registers per thread), DC_TE_WARPS with the TMA epilogue (the epilogue is
+// bound by the latency of its own arithmetic, so warps per scheduler are what speeds it up).  Three more warps follow:
+// activation TMA, MMA issuer (+ TMEM alloc), weight copies.
+template <bool TE>
+struct DcCfg {
+  static constexpr int EW = TE ? DC_TE_WARPS : 8;
+  static constexpr int THREADS = (EW + 3) * 32;
+};
 constexpr int DC_MAX_SA = 4;    // activation ring depth
 constexpr int DC_PF_TILES = 3;  // L2 prefetch distance of the activation boxes, in tiles of this CTA
 constexpr int DC_MAX_SW = 16;   // weight ring depth / resident k-blocks
-constexpr int DC_SMEM_BYTES = 216 * 1024;  // dynamic; + 6.6 KB static epilogue constants < 227 KB
+constexpr int DC_SMEM_BYTES = 219 * 1024;  // dynamic; + 7.5 KB static epilogue constants < 227 KB
 constexpr int DC_BAR_BYTES = (2 * DC_MAX_SA + 2 * DC_MAX_SW + 4) * 8 + 16;
 // TMA epilogue (template flag TE): every epilogue warp owns a ring of DC_E_RS slots (residual box in, raw result out,
 // in place) and DC_E_AS slots for the Snake-activated result; a slot is one 32-row x 32-channel fp16 box (SWIZZLE_64B).
 constexpr int DC_E_RS = 3, DC_E_AS = 2, DC_E_SLOT = 2048;
 constexpr int DC_E_WARP_BYTES = (DC_E_RS + DC_E_AS) * DC_E_SLOT;
-constexpr int DC_E_BYTES = (DC_EPI_THREADS / 32) * DC_E_WARP_BYTES;
-constexpr int DC_E_BAR_BYTES = (DC_EPI_THREADS / 32) * DC_E_RS * 8;
+constexpr int DC_E_BYTES = DC_TE_WARPS * DC_E_WARP_BYTES;
+constexpr int DC_E_BAR_BYTES = DC_TE_WARPS * DC_E_RS * 8;
 constexpr int DC_E_EXTRA = DC_E_BAR_BYTES + 1024 + DC_E_BYTES;  // barriers + alignment slack + slots
 
 struct DacConvArgs {
@@ -77,10 +86,10 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
 }
 
 // 3-D tiled TMA store shared -> global (SASS: UTMASTG), bulk-group completion; elements outside the tensor are dropped.
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2) {
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t smem_src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(map)),
-               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               "r"(smem_src), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -90,16 +99,42 @@ __device__ __forceinline__ void bulk_wait_group_read() {  // at most N groups st
 }
 __device__ __forceinline__ void bulk_wait_group_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
-// Snake1d (modeling_dac.py:94-99): x + 1/(alpha+1e-9) * sin(alpha*x)^2.  sin^2 has period pi: reduce alpha*x to
-// [-pi/2, pi/2] with a two-constant Cody-Waite step, then the SFU sine (abs. error ~5e-7 there) -- the result is
-// rounded to fp16 by the caller, so this is well inside half an fp16 ulp of the libm path and costs ~8 instructions.
-__device__ __forceinline__ float snake_fast(float x, float alpha, float inv_alpha) {
-  const float y = alpha * x;
-  const float k = rintf(y * 0.318309886183790672f);
-  float r = fmaf(k, -3.14159274101257324f, y);    // pi rounded to fp32
-  r = fmaf(k, 8.74227765734758577e-8f, r);        // fp32(pi) - pi
-  const float s = __sinf(r);
-  return fmaf(inv_alpha, s * s, x);
+// Snake1d (modeling_dac.py:94-99): x + 1/(alpha+1e-9) * sin(alpha*x)^2 = x + h - h*cos(k*x) with k = 2*alpha and
+// h = 0.5/(alpha+1e-9) (both precomputed per channel): one multiply, the SFU cosine (which reduces its argument by
+// taking the fraction of k*x/2pi; abs. error ~5e-7), one add and one FMA.  The result is rounded to fp16 by the caller:
+// the absolute error h*5e-7 is below half an fp16 ulp for every |result| > 1e-3.
+__device__ __forceinline__ float snake_cos(float x, float k, float h) { return fmaf(-h, __cosf(k * x), x + h); }
+
+// Eight columns of one output row: + bias and fp16 rounding (the conv's fp16 output under autocast), + residual in
+// fp16 (HADD2: the fp32 sum of two fp16 numbers rounds to the same fp16 value), Snake in fp32, fp16 again.
+__device__ __forceinline__ void dc_group8(const float* acc, const float4& b0, const float4& b1, const float4& k0,
+                                          const float4& k1, const float4& h0, const float4& h1, bool has_resid,
+                                          const uint4& resid, bool has_act, uint4& raw, uint4& act) {
+  const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+  const float kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
+  const float hh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+  __half2* rw = reinterpret_cast<__half2*>(&raw);
+  __half2* ac = reinterpret_cast<__half2*>(&act);
+  const __half2* rs = reinterpret_cast<const __half2*>(&resid);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __half2 v = __floats2half2_rn(acc[2 * i] + bb[2 * i], acc[2 * i + 1] + bb[2 * i + 1]);
+    if (has_resid) v = __hadd2(v, rs[i]);
+    rw[i] = v;
+    if (has_act) {
+      const float2 f = __half22float2(v);
+      ac[i] = __floats2half2_rn(snake_cos(f.x, kk[2 * i], hh[2 * i]), snake_cos(f.y, kk[2 * i + 1], hh[2 * i + 1]));
+    }
+  }
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 // Same box, L2 only (SASS: UTMAPF): pulls a later tile's activations out of HBM while the ring is still occupied.
@@ -138,7 +173,7 @@ __device__ __forceinline__ void dc_tile_coords(const DacConvArgs& a, int tile, i
 // TE: epilogue traffic through the TMA unit (plain convs: residual boxes in, raw / activated boxes out); the maps are
 // [batch][T_out][C_out] fp16 with a 32 x 32 x 1 box.  TE == false: direct global loads / stores from the epilogue threads.
 template <int NT, bool TE>
-__global__ void __launch_bounds__(DC_THREADS, 1)
+__global__ void __launch_bounds__(DcCfg<TE>::THREADS, 1)
 dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap rmap,
                 const __grid_constant__ CUtensorMap rawmap, const __grid_constant__ CUtensorMap actmap, const DacConvArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -160,24 +195,25 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
   __shared__ __align__(16) float s_bias[2][256], s_alpha[2][256], s_inv[2][256];
   __shared__ int2 s_grp[2][32];  // per 8 columns: (time offset r - pad of the transposed conv's phase, output channel)
 
+  constexpr int EW = DcCfg<TE>::EW;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kb_per_tile = a.cblocks * a.taps;
 
   if (tid == 0) {
     for (int s = 0; s < DC_MAX_SA; ++s) mbar_init(&a_full[s], 1), mbar_init(&a_empty[s], 1);
     for (int s = 0; s < DC_MAX_SW; ++s) mbar_init(&w_full[s], 1), mbar_init(&w_empty[s], 1);
-    for (int s = 0; s < 2; ++s) mbar_init(&t_full[s], 1), mbar_init(&t_empty[s], DC_EPI_THREADS / 32);
+    for (int s = 0; s < 2; ++s) mbar_init(&t_full[s], 1), mbar_init(&t_empty[s], EW);
     if constexpr (TE)
-      for (int s = 0; s < (DC_EPI_THREADS / 32) * DC_E_RS; ++s) mbar_init(&e_full[s], 1);
+      for (int s = 0; s < EW * DC_E_RS; ++s) mbar_init(&e_full[s], 1);
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc(tmem_slot, 512);
+  if (warp == EW + 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 8) {
+  if (warp == EW) {
     // ---------------------------------------------------------------- activation halo tiles: one TMA per channel block
     if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&xmap)) : "memory");
@@ -211,7 +247,7 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
       if (a.trace) a.trace[blockIdx.x * 8 + 6] = tr_wait0, a.trace[blockIdx.x * 8 + 7] = clock64() - tr_start;
 #endif
     }
-  } else if (warp == 10) {
+  } else if (warp == EW + 2) {
     // ---------------------------------------------------------------- weight k-blocks, in the order the MMAs use them
     // Lane jt copies NT tile jt of every stage: one thread only gets a few bulk copies per microsecond through the
     // TMA unit (scripts/exp_stream.cu), a 256-column stage is four of them.
@@ -238,7 +274,7 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
         if (a.w_resident) break;  // the whole filter is in shared memory now and stays
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == EW + 1) {
     // ---------------------------------------------------------------- MMA issuer
     // The whole warp runs the loops (warp-uniform control flow keeps the descriptors in uniform registers and the
     // issue path short: the single issuing thread is the pacing resource of the small-N layers); one elected lane
@@ -295,161 +331,127 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
     }
   } else if constexpr (TE) {
     // ---------------------------------------------------------------- epilogue through the TMA unit (plain convs)
-    // Warp (q, par) owns rows 32q.. of every tile and every second 32-channel block of the CTA's block sequence
-    // (tiles in order, blocks in order inside a tile; odd block counts alternate between the two warps of a row
-    // quarter).  Per block: the residual box arrives in a ring slot two blocks ahead, the thread (= row) reads its
-    // 64 bytes, writes the raw result back in place and the activated one to a second slot; one lane stores both boxes
-    // with the TMA unit and refills the slot whose store has finished reading.  No global access goes through the LSU.
+    // Warp w owns rows 32*(w%4).. of every tile and every (EW/4)-th 32-channel block of the CTA's block sequence (tiles
+    // in order, blocks in order inside a tile; every tile has NB blocks).  Per block: the residual box arrives in a
+    // ring slot two blocks ahead, the thread (= row) reads its 64 bytes, writes the raw result back in place and the
+    // activated one to a second slot; one lane stores both boxes with the TMA unit and refills the slot whose store
+    // has finished reading.  No global access goes through the LSU.
+    constexpr int STRIDE = EW / 4;
     const int q = warp & 3, par = warp >> 2;
-    uint8_t* my = e_buf + warp * DC_E_WARP_BYTES;
+    const uint32_t my = smem_u32(e_buf + warp * DC_E_WARP_BYTES);
     uint64_t* my_full = e_full + warp * DC_E_RS;
     const bool has_resid = a.resid != nullptr, has_raw = a.out_raw != nullptr, has_act = a.out_act != nullptr;
     const uint32_t row_off = lane * 64, sw_x = (lane >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk ^= (row >> 1) & 3
-    auto blocks_of = [&](int it_) -> int {  // 32-channel blocks of this CTA's it_-th tile (0 past the end)
-      const int tile = blockIdx.x + it_ * gridDim.x;
-      if (tile >= a.total_tiles) return 0;
-      const int group = a.n_groups == 1 ? 0 : tile % a.n_groups;
-      return min(a.tpc, a.n_tiles - group * a.tpc) * (NT / 32);
+    const int NB = a.tpc * (NT / 32);                            // 32-channel blocks per tile (all column groups alike)
+    const int n_my_tiles = (a.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    struct Pos {
+      int b, t, n0;
     };
-    auto normalize = [&](int& it_, int& cbk_) {
-      for (int nb = blocks_of(it_); nb > 0 && cbk_ >= nb; nb = blocks_of(it_)) cbk_ -= nb, ++it_;
-    };
-    auto box_coords = [&](int it_, int cbk_, int& c0, int& t, int& b) {
+    auto tile_pos = [&](int it_) {  // box origin of this warp's rows in the CTA's it_-th tile
       int m_tile, group;
       dc_tile_coords(a, blockIdx.x + it_ * gridDim.x, m_tile, group);
-      b = m_tile / a.tiles_per_seq;
-      t = (m_tile - b * a.tiles_per_seq) * 128 + q * 32;
-      c0 = group * a.tpc * NT + cbk_ * 32;
+      Pos p;
+      p.b = m_tile / a.tiles_per_seq;
+      p.t = (m_tile - p.b * a.tiles_per_seq) * 128 + q * 32;
+      p.n0 = group * a.tpc * NT;
+      return p;
     };
-    auto issue_load = [&](int it_, int cbk_, int idx_) {  // lane 0
-      if (!has_resid || blocks_of(it_) == 0) return;
-      int c0, t, b;
-      box_coords(it_, cbk_, c0, t, b);
-      const int slot = idx_ % DC_E_RS;
-      mbar_arrive_expect_tx(&my_full[slot], DC_E_SLOT);
-      tma_load_3d(my + slot * DC_E_SLOT, &rmap, c0, t, b, &my_full[slot]);
+    // prefetch cursor (lane 0 only): block n_issued of this warp = (pf_it, pf_cbk)
+    int pf_it = 0, pf_cbk = par, n_issued = 0;
+    while (pf_cbk >= NB) pf_cbk -= NB, ++pf_it;
+    Pos pf_pos = tile_pos(pf_it < n_my_tiles ? pf_it : 0);
+    auto issue_next_load = [&]() {  // lane 0
+      if (has_resid && pf_it < n_my_tiles) {
+        const int slot = n_issued % DC_E_RS;
+        mbar_arrive_expect_tx(&my_full[slot], DC_E_SLOT);
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                my + slot * DC_E_SLOT),
+            "l"(reinterpret_cast<uint64_t>(&rmap)), "r"(pf_pos.n0 + pf_cbk * 32), "r"(pf_pos.t), "r"(pf_pos.b),
+            "r"(smem_u32(&my_full[slot]))
+            : "memory");
+      }
+      ++n_issued, pf_cbk += STRIDE;
+      if (pf_cbk >= NB) {
+        while (pf_cbk >= NB) pf_cbk -= NB, ++pf_it;
+        if (pf_it < n_my_tiles) pf_pos = tile_pos(pf_it);
+      }
     };
-    int cur_it = 0, cur_cbk = par, pf_it, pf_cbk, idx = 0, n_issued = 0;
-    normalize(cur_it, cur_cbk);
-    pf_it = cur_it, pf_cbk = cur_cbk;
     if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&rmap)) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&rawmap)) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&actmap)) : "memory");
+      for (int k = 0; k < DC_E_RS - 1; ++k) issue_next_load();
     }
-    for (int k = 0; k < DC_E_RS - 1; ++k) {
-      if (lane == 0) issue_load(pf_it, pf_cbk, n_issued);
-      ++n_issued, pf_cbk += 2;
-      normalize(pf_it, pf_cbk);
-    }
+    int cbk = par, idx = 0;  // this warp's next block is block `cbk` of tile `it` (cbk may run past NB: next tile)
     [[maybe_unused]] long long tr_tf = 0, tr_start = clock64();
-    for (int it = 0;; ++it) {
-      const int tile = blockIdx.x + it * gridDim.x;
-      if (tile >= a.total_tiles) break;
-      int m_tile, group;
-      dc_tile_coords(a, tile, m_tile, group);
-      const int n0 = group * a.tpc * NT;
-      const int n_cols = min(a.tpc, a.n_tiles - group * a.tpc) * NT;
+    for (int it = 0; it < n_my_tiles; ++it) {
       const int buf = it & 1;
       const int cbuf = a.n_groups == 1 ? 0 : buf;
+      const Pos pos = tile_pos(it);
       if (a.n_groups > 1 || it == 0) {
-        const int col = tid, n = n0 + col;
-        if (col < n_cols) {
+        const int col = tid, n = pos.n0 + col;
+        if (col < NB * 32) {
           const bool ok = n < a.n_total;
           s_bias[cbuf][col] = ok ? __ldg(a.bias + n) : 0.f;
-          s_alpha[cbuf][col] = ok && has_act ? __ldg(a.alpha + n) : 0.f;
-          s_inv[cbuf][col] = ok && has_act ? __ldg(a.inv_alpha + n) : 0.f;
+          s_alpha[cbuf][col] = ok && has_act ? 2.f * __ldg(a.alpha + n) : 0.f;
+          s_inv[cbuf][col] = ok && has_act ? 0.5f * __ldg(a.inv_alpha + n) : 0.f;
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"r"(EW * 32) : "memory");
       }
       DC_TIMED_WAIT(tr_tf, &t_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
-      bool released = false;
-      while (cur_it == it) {
-        const int cbk = cur_cbk;
-        int nxt_it = cur_it, nxt_cbk = cur_cbk + 2;
-        normalize(nxt_it, nxt_cbk);
-        uint8_t* rs = my + (idx % DC_E_RS) * DC_E_SLOT;
-        uint8_t* as = my + (DC_E_RS + idx % DC_E_AS) * DC_E_SLOT;
-        float acc[2][16];
-        tmem_ld16(taddr + cbk * 32, acc[0]);
-        tmem_ld16(taddr + cbk * 32 + 16, acc[1]);
-        if (has_resid) mbar_wait(&my_full[idx % DC_E_RS], (idx / DC_E_RS) & 1);
-        tmem_ld_wait();
-        if (nxt_it != it) {  // last TMEM read of this warp in this tile: hand the accumulator back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&t_empty[buf]);
-          released = true;
-        }
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-#pragma unroll
-          for (int g = 0; g < 2; ++g) {
-            const int col = cbk * 32 + h * 16 + g * 8;
-            const uint32_t off = row_off + ((uint32_t)((h * 2 + g) ^ sw_x) << 4);
-            const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col]);
-            const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col + 4]);
-            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            float v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[h][g * 8 + i] + bb[i]));
-            if (has_resid) {
-              const uint4 ru = *reinterpret_cast<const uint4*>(rs + off);
-              const __half2* rh = reinterpret_cast<const __half2*>(&ru);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float2 rf = __half22float2(rh[i]);
-                v[2 * i] = __half2float(__float2half_rn(v[2 * i] + rf.x));
-                v[2 * i + 1] = __half2float(__float2half_rn(v[2 * i + 1] + rf.y));
-              }
-            }
-            if (has_raw) {
-              uint4 o;
-              __half2* oh = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-              *reinterpret_cast<uint4*>(rs + off) = o;
-            }
-            if (has_act) {
-              const float4 a0 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col]);
-              const float4 a1 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col + 4]);
-              const float4 i0 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col]);
-              const float4 i1 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col + 4]);
-              const float al[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-              const float ia[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
-              uint4 o;
-              __half2* oh = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-              for (int i = 0; i < 4; ++i)
-                oh[i] = __floats2half2_rn(snake_fast(v[2 * i], al[2 * i], ia[2 * i]),
-                                          snake_fast(v[2 * i + 1], al[2 * i + 1], ia[2 * i + 1]));
-              *reinterpret_cast<uint4*>(as + off) = o;
-            }
-          }
-        }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          int c0, t, b;
-          box_coords(it, cbk, c0, t, b);
-          if (has_raw) tma_store_3d(&rawmap, rs, c0, t, b);
-          if (has_act) tma_store_3d(&actmap, as, c0, t, b);
-          bulk_commit_group();
-          bulk_wait_group_read<1>();  // the previous block's boxes have left shared memory: its slots are free
-          issue_load(pf_it, pf_cbk, n_issued);
-        }
-        ++n_issued, pf_cbk += 2;
-        normalize(pf_it, pf_cbk);
-        __syncwarp();
-        cur_it = nxt_it, cur_cbk = nxt_cbk, ++idx;
-      }
-      if (!released) {  // (a tile with a single block belongs to one of the two warps only)
+      if (cbk >= NB) {  // no block of this tile is this warp's
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&t_empty[buf]);
       }
+      for (; cbk < NB; cbk += STRIDE, ++idx) {
+        const uint32_t rs = my + (idx % DC_E_RS) * DC_E_SLOT + row_off;
+        const uint32_t as = my + (DC_E_RS + idx % DC_E_AS) * DC_E_SLOT + row_off;
+        float acc[32];
+        tmem_ld32(taddr + cbk * 32, acc);
+        // per-column constants of the block's first 8 columns (in flight with the TMEM load and the residual wait)
+        const float* cb = &s_bias[cbuf][cbk * 32];
+        const float* ck = &s_alpha[cbuf][cbk * 32];
+        const float* ch = &s_inv[cbuf][cbk * 32];
+        uint4 res[4];
+        if (has_resid) {
+          mbar_wait(&my_full[idx % DC_E_RS], (idx / DC_E_RS) & 1);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) res[g] = lds128(rs + ((uint32_t)(g ^ sw_x) << 4));
+        }
+        tmem_ld_wait();
+        if (cbk + STRIDE >= NB) {  // last TMEM read of this warp in this tile: hand the accumulator back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&t_empty[buf]);
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const float4 b0 = *reinterpret_cast<const float4*>(cb + g * 8), b1 = *reinterpret_cast<const float4*>(cb + g * 8 + 4);
+          const float4 k0 = *reinterpret_cast<const float4*>(ck + g * 8), k1 = *reinterpret_cast<const float4*>(ck + g * 8 + 4);
+          const float4 h0 = *reinterpret_cast<const float4*>(ch + g * 8), h1 = *reinterpret_cast<const float4*>(ch + g * 8 + 4);
+          uint4 raw, act;
+          dc_group8(acc + g * 8, b0, b1, k0, k1, h0, h1, has_resid, res[g], has_act, raw, act);
+          const uint32_t off = (uint32_t)(g ^ sw_x) << 4;
+          if (has_raw) sts128(rs + off, raw);
+          if (has_act) sts128(as + off, act);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          const int c0 = pos.n0 + cbk * 32;
+          if (has_raw) tma_store_3d(&rawmap, rs - row_off, c0, pos.t, pos.b);
+          if (has_act) tma_store_3d(&actmap, as - row_off, c0, pos.t, pos.b);
+          bulk_commit_group();
+          bulk_wait_group_read<1>();  // the previous block's boxes have left shared memory: its slots are free
+          issue_next_load();
+        }
+        __syncwarp();
+      }
+      cbk -= NB;
     }
     if (lane == 0) bulk_wait_group_all();
 #ifdef SK_TRACE
@@ -502,11 +504,11 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
           int co = n, r = 0;
           if (a.up > 0 && ok) r = n / a.C_out, co = n - r * a.C_out;
           s_bias[cbuf][col] = ok ? __ldg(a.bias + n) : 0.f;
-          s_alpha[cbuf][col] = ok && a.out_act ? __ldg(a.alpha + co) : 0.f;
-          s_inv[cbuf][col] = ok && a.out_act ? __ldg(a.inv_alpha + co) : 0.f;
+          s_alpha[cbuf][col] = ok && a.out_act ? 2.f * __ldg(a.alpha + co) : 0.f;       // k = 2*alpha    (snake_cos)
+          s_inv[cbuf][col] = ok && a.out_act ? 0.5f * __ldg(a.inv_alpha + co) : 0.f;    // h = 0.5/(alpha+1e-9)
           if ((col & 7) == 0) s_grp[cbuf][col >> 3] = make_int2(ok ? (a.up > 0 ? r - a.pad : 0) : (1 << 30), co);
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"r"(EW * 32) : "memory");
       }
       DC_TIMED_WAIT(tr_tf, &t_full[buf], (it >> 1) & 1);
       tc_fence_after();
@@ -539,38 +541,12 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
           if (!live[h]) continue;
           const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col]);
           const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[cbuf][col + 4]);
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-          float v[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = __half2float(__float2half_rn(acc[c & 1][h * 8 + i] + bb[i]));
-          if (has_resid) {
-            const uint4 ru = rbuf[2 * c + h];
-            const __half2* rh = reinterpret_cast<const __half2*>(&ru);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const float2 rf = __half22float2(rh[i]);
-              v[2 * i] = __half2float(__float2half_rn(v[2 * i] + rf.x));
-              v[2 * i + 1] = __half2float(__float2half_rn(v[2 * i + 1] + rf.y));
-            }
-          }
-          if (a.out_raw) {
-            __half2* oh = reinterpret_cast<__half2*>(&o_raw[h]);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-          }
-          if (a.out_act) {
-            const float4 a0 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col]);
-            const float4 a1 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col + 4]);
-            const float4 i0 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col]);
-            const float4 i1 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col + 4]);
-            const float al[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const float ia[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
-            __half2* oh = reinterpret_cast<__half2*>(&o_act[h]);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              oh[i] = __floats2half2_rn(snake_fast(v[2 * i], al[2 * i], ia[2 * i]),
-                                        snake_fast(v[2 * i + 1], al[2 * i + 1], ia[2 * i + 1]));
-          }
+          const float4 k0 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col]);
+          const float4 k1 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col + 4]);
+          const float4 h0 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col]);
+          const float4 h1 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col + 4]);
+          dc_group8(&acc[c & 1][h * 8], b0, b1, k0, k1, h0, h1, has_resid, rbuf[2 * c + h], a.out_act != nullptr, o_raw[h],
+                    o_act[h]);
         }
         if (wide && live[0] && live[1]) {  // (both halves are in one phase / row: C_out % 16 == 0)
           if (a.out_raw) stg256(a.out_raw + offs[0], o_raw[0], o_raw[1]);
@@ -591,7 +567,7 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
     tc_fence_before();
   }
   __syncthreads();
-  if (warp == 9) {
+  if (warp == EW + 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
