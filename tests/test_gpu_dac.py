@@ -65,16 +65,20 @@ def test_dac_decode_rejects_wrong_codebook_count():
         ae.decode(torch.zeros(1, 8, 4, dtype=torch.int64, device="cuda"))
 
 
-def test_dac_tma_epilogue_matches_direct_epilogue(monkeypatch):
-    """The 1x1 convs' epilogue through the TMA unit (residual boxes in, raw / activated boxes out) must give the same
-    bits as the direct load / store epilogue, at lengths that leave partial 32-row boxes and partial tiles."""
+def test_dac_epilogue_variants_give_identical_bits(monkeypatch):
+    """The three epilogues of the conv kernel -- direct with register-held residual rows (8 warps), through the TMA unit
+    (1x1 convs: residual boxes in, raw / activated boxes out, 12 warps) and direct without residual (12 warps) -- must
+    give the same bits, at lengths that leave partial 32-row boxes and partial tiles."""
     ae = _decoder(shapes.DAC)
     g = torch.Generator().manual_seed(11)
     for B, T in [(1, 1), (2, 37), (3, 130)]:
         codes = torch.randint(0, 1024, (B, 9, T), generator=g).cuda()
         monkeypatch.setenv("ZB200_DAC_TE", "0")
-        direct = ae.decode(codes).cpu()
-        monkeypatch.setenv("ZB200_DAC_TE", "1")
-        tma = ae.decode(codes).cpu()
-        assert torch.isfinite(tma).all()
-        assert torch.equal(direct, tma), (B, T, float((direct - tma).abs().max()))
+        monkeypatch.setenv("ZB200_DAC_EW12", "0")
+        base = ae.decode(codes).cpu()
+        assert torch.isfinite(base).all()
+        for te, ew in [("1", "0"), ("0", "1"), ("1", "1")]:
+            monkeypatch.setenv("ZB200_DAC_TE", te)
+            monkeypatch.setenv("ZB200_DAC_EW12", ew)
+            got = ae.decode(codes).cpu()
+            assert torch.equal(base, got), (B, T, te, ew, float((base - got).abs().max()))

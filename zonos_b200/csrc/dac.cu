@@ -107,8 +107,13 @@ static bool dac_te_enabled() {
   const char* v = getenv("ZB200_DAC_TE");  // read per call: the parity test compares both epilogues in one process
   return !(v && atoi(v) == 0);
 }
-template <int NT, bool TE>
+static bool dac_wide_epilogue_enabled() {  // ZB200_DAC_EW12=0: 8-warp direct epilogue everywhere (A/B switch)
+  const char* v = getenv("ZB200_DAC_EW12");
+  return !(v && atoi(v) == 0);
+}
+template <int NT, int MODE>
 static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
+  constexpr bool TE = MODE == DC_TMA;
   const int T_in = L.t_mul_in * T;
   DacConvArgs a{};
   a.m_rows = L.up > 0 ? T_in + 1 : T_in;
@@ -179,7 +184,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
     }
   }
 
-  auto kern = dac_conv_kernel<NT, TE>;
+  auto kern = dac_conv_kernel<NT, MODE>;
   static bool configured = false;  // per template instantiation
   if (!configured) {
     ZB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DC_SMEM_BYTES));
@@ -193,7 +198,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   cudaMemsetAsync(trace_buf, 0, 256 * 8 * sizeof(long long), st);
   a.trace = trace_buf;
 #endif
-  kern<<<grid, DcCfg<TE>::THREADS, smem, st>>>(xmap, rmap, rawmap, actmap, a);
+  kern<<<grid, DcCfg<MODE>::THREADS, smem, st>>>(xmap, rmap, rawmap, actmap, a);
   ZB_CHECK_LAUNCH("dac_conv_kernel");
 #ifdef SK_TRACE
   {
@@ -241,8 +246,17 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
       const int n_tiles = ceil_div(L.c_out, L.tile_n), max_tpc = 256 / L.tile_n, n_groups = ceil_div(n_tiles, max_tpc);
       te = n_tiles % n_groups == 0 && L.c_out % L.tile_n == 0;
     }
-    const int rc = L.tile_n == 96 ? (te ? launch_dac_conv<96, true>(L, batch, t, regions, st) : launch_dac_conv<96, false>(L, batch, t, regions, st))
-                                  : (te ? launch_dac_conv<64, true>(L, batch, t, regions, st) : launch_dac_conv<64, false>(L, batch, t, regions, st));
+    // without a residual input the direct epilogue needs few registers and runs 12 warps (DC_DIRECT)
+    const int mode = te ? DC_TMA : (L.resid_region < 0 && dac_wide_epilogue_enabled() ? DC_DIRECT : DC_DIRECT_RESID);
+    int rc;
+    if (L.tile_n == 96)
+      rc = mode == DC_TMA      ? launch_dac_conv<96, DC_TMA>(L, batch, t, regions, st)
+           : mode == DC_DIRECT ? launch_dac_conv<96, DC_DIRECT>(L, batch, t, regions, st)
+                               : launch_dac_conv<96, DC_DIRECT_RESID>(L, batch, t, regions, st);
+    else
+      rc = mode == DC_TMA      ? launch_dac_conv<64, DC_TMA>(L, batch, t, regions, st)
+           : mode == DC_DIRECT ? launch_dac_conv<64, DC_DIRECT>(L, batch, t, regions, st)
+                               : launch_dac_conv<64, DC_DIRECT_RESID>(L, batch, t, regions, st);
     if (rc != ZB200_OK) return rc;
   }
   {

@@ -29,12 +29,17 @@ typedef __half f16;
 #ifndef DC_TE_WARPS
 #define DC_TE_WARPS 12
 #endif
-// Epilogue warps: 8 with the direct epilogue (165 registers per thread), DC_TE_WARPS with the TMA epilogue (the epilogue is
-// bound by the latency of its own arithmetic, so warps per scheduler are what speeds it up).  Three more warps follow:
-// activation TMA, MMA issuer (+ TMEM alloc), weight copies.
-template <bool TE>
+// Epilogue variants (template MODE).  The epilogue is bound by the latency of its own arithmetic, so warps per scheduler
+// are what speeds it up: 12 epilogue warps wherever the registers allow it.
+//   DC_DIRECT_RESID  direct global loads / stores, residual rows held in registers (165 registers): 8 warps (fallback for
+//                    channel counts the TMA boxes do not divide)
+//   DC_TMA           residual / raw / activated boxes through the TMA unit: DC_TE_WARPS warps
+//   DC_DIRECT        direct stores, no residual input (k = 7 convs, transposed convs): 12 warps
+// Three more warps follow the epilogue warps: activation TMA, MMA issuer (+ TMEM alloc), weight copies.
+constexpr int DC_DIRECT_RESID = 0, DC_TMA = 1, DC_DIRECT = 2;
+template <int MODE>
 struct DcCfg {
-  static constexpr int EW = TE ? DC_TE_WARPS : 8;
+  static constexpr int EW = MODE == DC_TMA ? DC_TE_WARPS : (MODE == DC_DIRECT ? 12 : 8);
   static constexpr int THREADS = (EW + 3) * 32;
 };
 constexpr int DC_MAX_SA = 4;    // activation ring depth
@@ -172,8 +177,8 @@ __device__ __forceinline__ void dc_tile_coords(const DacConvArgs& a, int tile, i
 
 // TE: epilogue traffic through the TMA unit (plain convs: residual boxes in, raw / activated boxes out); the maps are
 // [batch][T_out][C_out] fp16 with a 32 x 32 x 1 box.  TE == false: direct global loads / stores from the epilogue threads.
-template <int NT, bool TE>
-__global__ void __launch_bounds__(DcCfg<TE>::THREADS, 1)
+template <int NT, int MODE>
+__global__ void __launch_bounds__(DcCfg<MODE>::THREADS, 1)
 dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap rmap,
                 const __grid_constant__ CUtensorMap rawmap, const __grid_constant__ CUtensorMap actmap, const DacConvArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -195,7 +200,8 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
   __shared__ __align__(16) float s_bias[2][256], s_alpha[2][256], s_inv[2][256];
   __shared__ int2 s_grp[2][32];  // per 8 columns: (time offset r - pad of the transposed conv's phase, output channel)
 
-  constexpr int EW = DcCfg<TE>::EW;
+  constexpr int EW = DcCfg<MODE>::EW;
+  constexpr bool TE = MODE == DC_TMA, RESID = MODE == DC_DIRECT_RESID;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kb_per_tile = a.cblocks * a.taps;
 
@@ -460,9 +466,10 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
     tc_fence_before();
   } else {
     // ---------------------------------------------------------------- epilogue: TMEM -> bias/residual/Snake -> fp16 rows
+    constexpr int STRIDE = EW / 4;  // warps per row quarter: warp (q, par) takes the 16-column chunks par, par+STRIDE, ...
     const int q = warp & 3, par = warp >> 2;
     const int row = q * 32 + lane;
-    const bool has_resid = a.resid != nullptr && a.up == 0;
+    const bool has_resid = RESID && a.resid != nullptr && a.up == 0;
     // a 16-column chunk of a row is one aligned 32-byte piece of the output when the channel count is a multiple of 16
     const bool wide = (a.C_out & 15) == 0 && (a.pitch_out & 15) == 0;
     int it = 0;
@@ -476,13 +483,13 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
       const bool row_valid = j < a.m_rows;
       const int buf = it & 1;
       const int n_chunks = n_cols >> 4;
-      const int n_mine = (n_chunks - par + 1) >> 1;  // 16-column chunks par, par+2, ...
+      const int n_mine = (n_chunks - par + STRIDE - 1) / STRIDE;  // >= 1: a tile has at least 4 chunks
       // the residual row is streamed from HBM: issue this thread's loads before waiting for the accumulator
-      uint4 rbuf[16];
+      uint4 rbuf[RESID ? 16 : 2];
       if (has_resid && row_valid) {
         const f16* rrow = a.resid + ((size_t)b * a.T_out + j) * a.pitch_out + n0;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 0; c < (RESID ? 8 : 0); ++c) {
           const int ch = 2 * c + par;
           if (ch < n_chunks && n0 + ch * 16 < a.n_total) {
             if (wide) {
@@ -518,10 +525,10 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
         if (c >= n_mine) break;
-        const int ch = 2 * c + par;
+        const int ch = STRIDE * c + par;
         tmem_ld_wait();
         if (c + 1 < n_mine) {
-          tmem_ld16(taddr + (ch + 2) * 16, acc[(c + 1) & 1]);  // in flight while this chunk is processed
+          tmem_ld16(taddr + (ch + STRIDE) * 16, acc[(c + 1) & 1]);  // in flight while this chunk is processed
         } else {  // last TMEM read of this warp: hand the accumulator back to the MMA warp
           tc_fence_before();
           __syncwarp();
@@ -545,8 +552,8 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
           const float4 k1 = *reinterpret_cast<const float4*>(&s_alpha[cbuf][col + 4]);
           const float4 h0 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col]);
           const float4 h1 = *reinterpret_cast<const float4*>(&s_inv[cbuf][col + 4]);
-          dc_group8(&acc[c & 1][h * 8], b0, b1, k0, k1, h0, h1, has_resid, rbuf[2 * c + h], a.out_act != nullptr, o_raw[h],
-                    o_act[h]);
+          dc_group8(&acc[c & 1][h * 8], b0, b1, k0, k1, h0, h1, has_resid, rbuf[RESID ? 2 * c + h : 0], a.out_act != nullptr,
+                    o_raw[h], o_act[h]);
         }
         if (wide && live[0] && live[1]) {  // (both halves are in one phase / row: C_out % 16 == 0)
           if (a.out_raw) stg256(a.out_raw + offs[0], o_raw[0], o_raw[1]);
