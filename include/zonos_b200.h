@@ -186,6 +186,12 @@ typedef struct {
   int32_t final_region, final_c, final_pitch, final_t_mul; /* input of the last conv (k7 -> 1 channel) + tanh */
   const float* final_w;          /* fp32 [7][final_c] */
   float final_bias;
+  /* Optional tensor-core form of the last conv: eight consecutive time steps are one input row of 8*final_c channels,
+   * so the k7 conv is a 3-tap conv with 8 output columns (the 8 time phases).  final_wp: packed fp16 (tile 16)
+   * [8][3][8*final_c], W'[r][s+1][j*final_c + c] = w[8s + j - r + 3][c] (0 outside the 7 taps); final_bias8: fp32 [8].
+   * NULL: scalar kernel. */
+  const void* final_wp;
+  const float* final_bias8;
 } zb200_dac_plan;
 /* codes int64 [batch][n_q][t]  ->  wav fp32 [batch][final_t_mul * t].  regions: 5 device buffers of region_halves fp16. */
 int zb200_dac_decode(const zb200_dac_plan* plan, const int64_t* codes, int batch, int t, void* const* regions,

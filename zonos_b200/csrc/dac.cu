@@ -112,7 +112,8 @@ static bool dac_wide_epilogue_enabled() {  // ZB200_DAC_EW12=0: 8-warp direct ep
   return !(v && atoi(v) == 0);
 }
 template <int NT, int MODE>
-static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st) {
+static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* const* regions, cudaStream_t st,
+                           float* wav = nullptr) {
   constexpr bool TE = MODE == DC_TMA;
   const int T_in = L.t_mul_in * T;
   DacConvArgs a{};
@@ -151,6 +152,7 @@ static int launch_dac_conv(const zb200_dac_layer& L, int batch, int T, void* con
   a.resid = L.resid_region >= 0 ? (const f16*)regions[L.resid_region] : nullptr;
   a.out_raw = L.raw_region >= 0 ? (f16*)regions[L.raw_region] : nullptr;
   a.out_act = L.act_region >= 0 ? (f16*)regions[L.act_region] : nullptr;
+  a.wav = wav;
   a.alpha = L.alpha, a.inv_alpha = L.inv_alpha;
   a.pitch_out = L.pitch_out, a.C_out = L.c_out, a.up = L.up, a.pad = L.up / 2;
   ZB_REQUIRE(!(a.resid && a.up > 0), "dac_decode: residual input on a transposed conv");
@@ -259,7 +261,18 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
                                : launch_dac_conv<64, DC_DIRECT_RESID>(L, batch, t, regions, st);
     if (rc != ZB200_OK) return rc;
   }
-  {
+  static const bool final_scalar = getenv("ZB200_DAC_FINAL_SCALAR") != nullptr;  // A/B switch
+  if (p->final_wp && p->final_bias8 && !final_scalar && p->final_t_mul % 8 == 0 && (8 * p->final_c) % 64 == 0 &&
+      p->final_pitch == p->final_c) {
+    // last conv on the tensor cores: rows of 8 time steps (8*final_c channels), 3 row taps, 8 output phases, tanh
+    zb200_dac_layer L{};
+    L.taps = 3, L.shift0 = -1, L.shift_step = 1, L.up = 0;
+    L.pitch_in = 8 * p->final_c, L.c_out = 8, L.pitch_out = 8, L.tile_n = 16, L.t_mul_in = p->final_t_mul / 8;
+    L.in_region = p->final_region, L.resid_region = L.raw_region = L.act_region = -1;
+    L.w = p->final_wp, L.bias = p->final_bias8, L.alpha = nullptr, L.inv_alpha = nullptr;
+    const int rc = launch_dac_conv<16, DC_DIRECT>(L, batch, t, regions, st, wav);
+    if (rc != ZB200_OK) return rc;
+  } else {
     const int T_out = p->final_t_mul * t;
     const size_t smem = (size_t)(FIN_TILE + 6) * (p->final_c / 2 + 1) * 4 + (size_t)7 * p->final_c * 4;
     static bool configured = false;

@@ -44,7 +44,7 @@ struct DcCfg {
 };
 constexpr int DC_MAX_SA = 4;    // activation ring depth
 constexpr int DC_PF_TILES = 3;  // L2 prefetch distance of the activation boxes, in tiles of this CTA
-constexpr int DC_MAX_SW = 16;   // weight ring depth / resident k-blocks
+constexpr int DC_MAX_SW = 40;   // weight ring depth / resident k-blocks
 constexpr int DC_SMEM_BYTES = 219 * 1024;  // dynamic; + 7.5 KB static epilogue constants < 227 KB
 constexpr int DC_BAR_BYTES = (2 * DC_MAX_SA + 2 * DC_MAX_SW + 4) * 8 + 16;
 // TMA epilogue (template flag TE): every epilogue warp owns a ring of DC_E_RS slots (residual box in, raw result out,
@@ -77,6 +77,7 @@ struct DacConvArgs {
   const float* inv_alpha;  // [C_out] = 1/(alpha + 1e-9)
   int T_out, pitch_out, C_out, n_total;
   int up, pad;             // transposed conv: stride and padding (up == 0: plain conv)
+  float* wav;              // last conv (direct epilogue only): tanh of the fp16-rounded result as fp32 [B][T_out][C_out]
   long long* trace;        // SK_TRACE builds: [grid][8] cycle counters
 };
 
@@ -483,7 +484,7 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
       const bool row_valid = j < a.m_rows;
       const int buf = it & 1;
       const int n_chunks = n_cols >> 4;
-      const int n_mine = (n_chunks - par + STRIDE - 1) / STRIDE;  // >= 1: a tile has at least 4 chunks
+      const int n_mine = (n_chunks - par + STRIDE - 1) / STRIDE;
       // the residual row is streamed from HBM: issue this thread's loads before waiting for the accumulator
       uint4 rbuf[RESID ? 16 : 2];
       if (has_resid && row_valid) {
@@ -520,6 +521,12 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
       DC_TIMED_WAIT(tr_tf, &t_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
+      if (n_mine <= 0) {  // (the 16-column tile of the last conv: one warp per row quarter has work)
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[buf]);
+        continue;
+      }
       float acc[2][16];
       tmem_ld16(taddr + par * 16, acc[0]);
 #pragma unroll
@@ -562,6 +569,18 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
 #pragma unroll
           for (int h = 0; h < 2; ++h)
             if (live[h]) {
+              if (a.wav) {  // modeling_dac.py:436-437: tanh of the (fp16) conv output
+                const __half2* rh = reinterpret_cast<const __half2*>(&o_raw[h]);
+                float w8[8];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float2 f = __half22float2(rh[i]);
+                  w8[2 * i] = tanhf(f.x), w8[2 * i + 1] = tanhf(f.y);
+                }
+                float4* dst = reinterpret_cast<float4*>(a.wav + offs[h]);
+                dst[0] = make_float4(w8[0], w8[1], w8[2], w8[3]);
+                dst[1] = make_float4(w8[4], w8[5], w8[6], w8[7]);
+              }
               if (a.out_raw) *reinterpret_cast<uint4*>(a.out_raw + offs[h]) = o_raw[h];
               if (a.out_act) *reinterpret_cast<uint4*>(a.out_act + offs[h]) = o_act[h];
             }

@@ -31,6 +31,7 @@ class DacPlan(ctypes.Structure):
         ("z_region", ctypes.c_int32), ("final_region", ctypes.c_int32), ("final_c", ctypes.c_int32),
         ("final_pitch", ctypes.c_int32), ("final_t_mul", ctypes.c_int32),
         ("final_w", ctypes.c_void_p), ("final_bias", ctypes.c_float),
+        ("final_wp", ctypes.c_void_p), ("final_bias8", ctypes.c_void_p),
     ]
 
 
@@ -149,6 +150,19 @@ class DacDecoderB200:
         plan.z_region, plan.final_region, plan.final_c = R_Z, R_IN, c
         plan.final_pitch, plan.final_t_mul = c, t_mul
         plan.final_w, plan.final_bias = self.final_w.data_ptr(), self.final_bias
+        plan.final_wp, plan.final_bias8 = None, None
+        if (8 * c) % 64 == 0 and t_mul % 8 == 0:
+            # tensor-core form of the last conv (csrc/dac.cu): rows of 8 time steps, 3 row taps, 8 output phases
+            wp = torch.zeros(8, 3, 8, c, device=self.device)
+            for r in range(8):
+                for s_ in (-1, 0, 1):
+                    for j in range(8):
+                        k = 8 * s_ + j - r + 3
+                        if 0 <= k <= 6:
+                            wp[r, s_ + 1, j] = self.final_w[k]
+            self.final_wp = ops.pack_weight(wp.reshape(8, 3 * 8 * c).half(), tile_n=16)
+            self.final_bias8 = torch.full((8,), self.final_bias, dtype=torch.float32, device=self.device)
+            plan.final_wp, plan.final_bias8 = self.final_wp.data_ptr(), self.final_bias8.data_ptr()
         self.plan = plan
         # halves per code frame of the largest tensor a region ever holds
         per_frame = [self.latent, sd["decoder.conv1.weight"].shape[0]]
