@@ -53,7 +53,7 @@ constexpr int DC_E_RS = 3, DC_E_AS = 2, DC_E_SLOT = 2048;
 constexpr int DC_E_WARP_BYTES = (DC_E_RS + DC_E_AS) * DC_E_SLOT;
 constexpr int DC_E_BYTES = DC_TE_WARPS * DC_E_WARP_BYTES;
 constexpr int DC_E_BAR_BYTES = DC_TE_WARPS * DC_E_RS * 8;
-constexpr int DC_E_EXTRA = DC_E_BAR_BYTES + 1024 + DC_E_BYTES;  // barriers + alignment slack + slots
+constexpr int DC_E_EXTRA = DC_E_BAR_BYTES + DC_E_BYTES;  // barriers + slots
 
 struct DacConvArgs {
   const uint8_t* Wp;       // packed weights
@@ -186,7 +186,10 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_ring = smem;
   uint8_t* w_ring = smem + a.sa * a.a_stage_bytes;
-  uint64_t* a_full = reinterpret_cast<uint64_t*>(w_ring + a.sw * a.w_stage_bytes);
+  // (TE) epilogue slots right after the rings (all ring stages are multiples of 1 KB, so the slots stay 1 KB aligned),
+  // then the barriers
+  uint8_t* e_buf = w_ring + a.sw * a.w_stage_bytes;                                   // TE: [warp][slots]
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(e_buf + (MODE == DC_TMA ? DC_E_BYTES : 0));
   uint64_t* a_empty = a_full + DC_MAX_SA;
   uint64_t* w_full = a_empty + DC_MAX_SA;
   uint64_t* w_empty = w_full + DC_MAX_SW;
@@ -194,8 +197,6 @@ dac_conv_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant_
   uint64_t* t_empty = t_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
   uint64_t* e_full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(a_full) + DC_BAR_BYTES);  // TE: [warp][DC_E_RS]
-  uint8_t* e_buf = reinterpret_cast<uint8_t*>(
-      (reinterpret_cast<uintptr_t>(e_full) + DC_E_BAR_BYTES + 1023) & ~uintptr_t(1023));            // TE: [warp][slots]
 
   // per-column epilogue constants of the current column group (two copies: tiles alternate when n_groups > 1)
   __shared__ __align__(16) float s_bias[2][256], s_alpha[2][256], s_inv[2][256];
