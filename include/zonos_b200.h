@@ -162,6 +162,22 @@ int zb200_engine_run(zb200_engine* e, int n_steps, void* stream);
 /* number of kernel launches in one step (for the bench's gpu_launches claim) */
 int zb200_engine_launches_per_step(const zb200_engine* e);
 
+/* ---- Hybrid backbone, Mamba2 mixer decode step (zonos/backbone/_mamba_ssm.py:18-31 builds the layers
+ * with mamba_ssm's create_block, the per-token arithmetic is mamba_ssm 2.2.4 Mamba2.step).  zxbcdt is the in_proj output
+ * [rows][ld] bf16 = [z (d_inner) | x (d_inner) B (G*N) C (G*N) | dt (H)].  States are caller-owned bf16 tensors
+ * (what allocate_inference_cache returns, _mamba_ssm.py:37-41). */
+/* causal_conv1d_update + SiLU: conv_state bf16 [rows][channels][4] shifted in place, out bf16 [rows][channels]. */
+int zb200_mamba2_conv_update(void* conv_state, const void* zxbcdt, int ld, int col0, const void* w, const void* bias,
+                             void* out, int rows, int channels, int d_conv, void* stream);
+/* selective_state_update (dt_softplus, D skip, no z): ssm_state bf16 [rows][H][P][N] updated in place,
+ * xbc = conv output [rows][ld_xbc], dt = zxbcdt[:, dt_col0 + h], y bf16 [rows][H*P]. */
+int zb200_mamba2_ssd_step(void* ssm_state, const void* xbc, int ld_xbc, const void* zxbcdt, int ld, int dt_col0,
+                          const float* A_log, const float* D, const float* dt_bias, void* y, int rows, int n_heads,
+                          int head_dim, int d_state, int n_groups, void* stream);
+/* RMSNormGated(norm_before_gate=False): out = rmsnorm_group(y * silu(z)) * w, z = zxbcdt[:, :d_inner]. */
+int zb200_mamba2_gated_rmsnorm(const void* y, const void* zxbcdt, int ld, const void* w, void* out, int rows, int d_inner,
+                               int n_groups, float eps, void* stream);
+
 /* ---- DACAutoencoder.decode (zonos/autoencoder.py:44-47 -> transformers DacModel.decode, modeling_dac.py:608-638) ---
  * The decoder is described as a list of implicit-GEMM layers over five caller-owned fp16 work regions (channels-last
  * [batch][time][pitch]); the host shim (zonos_b200/dac.py) builds the list from the HF state dict once. */

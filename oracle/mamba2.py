@@ -1,0 +1,106 @@
+"""CPU restatement of the Mamba2 mixer's single decode step -- TEST INFRASTRUCTURE ONLY (the hybrid
+backbone `MambaSSMZonosBackbone`, zonos/backbone/_mamba_ssm.py:9-57, whose layers are `mamba_ssm` Mamba2 blocks).
+
+Nothing outside tests/, __graft_entry__.smoke() and bench.py's CPU legs may import this module.
+
+The arithmetic lives in a third-party dependency that is absent from /root/reference and from this image:
+`mamba-ssm` 2.2.4 + `causal-conv1d` 1.5.0.post8 (uv.lock:715-717,118-120; call sites _mamba_ssm.py:3-4,18-31).  The
+published algorithm restated here is `Mamba2.step` (mamba_ssm/modules/mamba2.py): in_proj -> causal_conv1d_update (k = 4,
+SiLU) -> selective_state_update (softplus(dt + dt_bias), h = h*exp(dt*A) + dt*B*x, y = C.h + D*x) -> RMSNormGated
+(norm_before_gate=False: rmsnorm(y * silu(z)) * w) -> out_proj.
+
+Pin: `transformers` 5.5 ships a pure-torch statement of the same mixer (models/mamba2/modeling_mamba2.py,
+`Mamba2Mixer.torch_forward`: decode branch :419-503, gated norm :103-118).  tests/test_oracle_golden.py runs that class on
+the CPU (fp32, chunked prefill + cached decode steps) and checks this restatement against it step by step, so the
+recurrence, the conv-state handling and the gating order are pinned to a published implementation; the mamba_ssm Triton
+kernels' own rounding points (bf16 state / activations) are modelled by `storage_dtype` and stay unpinned.
+"""
+import torch
+import torch.nn.functional as F
+
+
+def conv1d_update(conv_state, xbc, weight, bias):
+    """causal_conv1d_update with SiLU.  conv_state [B, C, K] (oldest first), xbc [B, C], weight [C, K], bias [C] or None.
+    Shifts the window by one, appends xbc, returns (silu(sum_k state[k] * w[k] + bias) fp32, new state in its dtype)."""
+    new_state = torch.cat([conv_state[:, :, 1:], xbc.to(conv_state.dtype).unsqueeze(-1)], dim=-1)
+    out = (new_state.float() * weight.float().unsqueeze(0)).sum(-1)
+    if bias is not None:
+        out = out + bias.float()
+    return F.silu(out), new_state
+
+
+def ssd_step(ssm_state, x, dt, A_log, B, C, D, dt_bias, n_groups=1):
+    """selective_state_update for one token.  ssm_state [Bt, H, P, N]; x [Bt, H, P]; dt [Bt, H]; B, C [Bt, G, N];
+    A_log, D, dt_bias [H].  Returns (y fp32 [Bt, H, P], new state in the state's dtype); the output uses the fp32 state
+    before it is rounded to the storage dtype (as the Triton kernel does)."""
+    Bt, H, P, N = ssm_state.shape
+    dt = F.softplus(dt.float() + dt_bias.float())                       # [Bt, H]
+    dA = torch.exp(dt * (-torch.exp(A_log.float())))                    # [Bt, H]
+    rep = H // n_groups
+    Bh = B.float().repeat_interleave(rep, dim=1)                        # [Bt, H, N]
+    Ch = C.float().repeat_interleave(rep, dim=1)
+    xf = x.float()
+    h = ssm_state.float() * dA[..., None, None] + (dt[..., None] * xf)[..., None] * Bh[:, :, None, :]
+    y = (h * Ch[:, :, None, :]).sum(-1) + D.float()[None, :, None] * xf
+    return y, h.to(ssm_state.dtype)
+
+
+def gated_rmsnorm(y, z, weight, eps, n_groups=1):
+    """RMSNormGated(norm_before_gate=False): rmsnorm over each of n_groups channel groups of y * silu(z), times weight."""
+    v = y.float() * F.silu(z.float())
+    Bt, Dn = v.shape
+    g = v.view(Bt, n_groups, Dn // n_groups)
+    g = g * torch.rsqrt(g.pow(2).mean(-1, keepdim=True) + eps)
+    return g.view(Bt, Dn) * weight.float()
+
+
+def mixer_step(p, state, u, storage_dtype=torch.float32):
+    """One token through the mixer.  p: dict of parameters (in_proj.weight [2*Di + 2*G*N + H, d], conv1d.weight [Cd, K],
+    conv1d.bias, dt_bias, A_log, D, norm.weight, out_proj.weight), shapes in p['shape'] = dict(d_inner, n_heads, head_dim,
+    d_state, n_groups, eps); state: dict(conv [B, Cd, K], ssm [B, H, P, N]); u [B, d].  storage_dtype models the points
+    where the reference stores activations (bf16 in the real model, fp32 for the pin against transformers)."""
+    s = p["shape"]
+    Di, H, P, N, G = s["d_inner"], s["n_heads"], s["head_dim"], s["d_state"], s["n_groups"]
+    rnd = lambda t: t.to(storage_dtype).float()
+    zxbcdt = rnd(u.float() @ p["in_proj.weight"].float().t())
+    z, xbc, dt = zxbcdt[:, :Di], zxbcdt[:, Di:Di + Di + 2 * G * N], zxbcdt[:, -H:]
+    xbc_act, state["conv"] = conv1d_update(state["conv"], xbc, p["conv1d.weight"], p.get("conv1d.bias"))
+    xbc_act = rnd(xbc_act)
+    x = xbc_act[:, :Di].reshape(-1, H, P)
+    Bm = xbc_act[:, Di:Di + G * N].reshape(-1, G, N)
+    Cm = xbc_act[:, Di + G * N:].reshape(-1, G, N)
+    y, state["ssm"] = ssd_step(state["ssm"], x, dt, p["A_log"], Bm, Cm, p["D"], p["dt_bias"], G)
+    y = rnd(y).reshape(-1, Di)
+    yn = rnd(gated_rmsnorm(y, z, p["norm.weight"], s["eps"], G))
+    return rnd(yn @ p["out_proj.weight"].float().t())
+
+
+def new_state(p, batch, conv_dtype=torch.float32, ssm_dtype=torch.float32):
+    s = p["shape"]
+    cd = s["d_inner"] + 2 * s["n_groups"] * s["d_state"]
+    return dict(conv=torch.zeros(batch, cd, p["conv1d.weight"].shape[-1], dtype=conv_dtype),
+                ssm=torch.zeros(batch, s["n_heads"], s["head_dim"], s["d_state"], dtype=ssm_dtype))
+
+
+def synth_mixer_params(d_model=256, expand=2, head_dim=64, d_state=128, n_groups=1, d_conv=4, seed=0, dtype=torch.float32):
+    """Random parameters with the ranges of Mamba2's own initialisation (dt in [1e-3, 0.1], A in [1, 16])."""
+    g = torch.Generator().manual_seed(seed)
+    Di = expand * d_model
+    H = Di // head_dim
+    cd = Di + 2 * n_groups * d_state
+    r = lambda *sh: torch.randn(*sh, generator=g)
+    dt = torch.exp(torch.rand(H, generator=g) * (torch.log(torch.tensor(0.1)) - torch.log(torch.tensor(1e-3)))
+                   + torch.log(torch.tensor(1e-3))).clamp(min=1e-4)
+    p = {
+        "in_proj.weight": (r(2 * Di + 2 * n_groups * d_state + H, d_model) / d_model ** 0.5).to(dtype),
+        "conv1d.weight": (r(cd, d_conv) / d_conv ** 0.5).to(dtype),
+        "conv1d.bias": (0.1 * r(cd)).to(dtype),
+        "dt_bias": (dt + torch.log(-torch.expm1(-dt))).float(),
+        "A_log": torch.log(1 + 15 * torch.rand(H, generator=g)).float(),
+        "D": torch.ones(H) + 0.1 * r(H),
+        "norm.weight": (1 + 0.1 * r(Di)).to(dtype),
+        "out_proj.weight": (r(d_model, Di) / Di ** 0.5).to(dtype),
+        "shape": dict(d_inner=Di, n_heads=H, head_dim=head_dim, d_state=d_state, n_groups=n_groups, eps=1e-5,
+                      d_model=d_model, d_conv=d_conv),
+    }
+    return p

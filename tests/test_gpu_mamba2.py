@@ -1,0 +1,81 @@
+"""Mamba2 mixer decode step (hybrid backbone): CUDA kernels vs the CPU oracle, through the C ABI.
+
+The oracle (oracle/mamba2.py) is pinned against transformers' Mamba2Mixer.torch_forward in tests/test_oracle_golden.py;
+here it runs with bf16 storage points (state, in_proj / conv / y / norm outputs), which is how the reference's model
+(bf16 weights, mamba_ssm kernels) stores them."""
+import pytest
+import torch
+
+from oracle import mamba2 as om
+
+pytestmark = pytest.mark.gpu
+BF = torch.bfloat16
+
+
+def _rel_rms(a, b):
+    return float((a.float() - b.float()).pow(2).mean().sqrt() / b.float().pow(2).mean().sqrt().clamp_min(1e-12))
+
+
+@pytest.mark.parametrize("shape", [dict(d_model=256, head_dim=64, n_groups=1), dict(d_model=2048, head_dim=64, n_groups=1),
+                                   dict(d_model=256, head_dim=32, n_groups=2)])
+def test_mamba2_step_kernels_vs_oracle(shape):
+    from zonos_b200 import ops
+
+    p = om.synth_mixer_params(seed=5, dtype=BF, **shape)
+    s = p["shape"]
+    Di, H, P, N, G = s["d_inner"], s["n_heads"], s["head_dim"], s["d_state"], s["n_groups"]
+    rows, steps = 5, 6
+    g = torch.Generator().manual_seed(9)
+    st = om.new_state(p, rows, conv_dtype=BF, ssm_dtype=BF)
+    # a warm, non-trivial state
+    st["conv"] = torch.randn(st["conv"].shape, generator=g).to(BF)
+    st["ssm"] = (0.5 * torch.randn(st["ssm"].shape, generator=g)).to(BF)
+    conv_d, ssm_d = st["conv"].cuda().contiguous(), st["ssm"].cuda().contiguous()
+    for step in range(steps):
+        zx = torch.randn(rows, 2 * Di + 2 * G * N + H, generator=g).to(BF)
+        # oracle, same storage points
+        xbc_ref, st["conv"] = om.conv1d_update(st["conv"], zx[:, Di:2 * Di + 2 * G * N], p["conv1d.weight"], p["conv1d.bias"])
+        xbc_ref = xbc_ref.to(BF)
+        y_ref, st["ssm"] = om.ssd_step(st["ssm"], xbc_ref[:, :Di].reshape(rows, H, P), zx[:, -H:], p["A_log"],
+                                       xbc_ref[:, Di:Di + G * N].reshape(rows, G, N), xbc_ref[:, Di + G * N:].reshape(rows, G, N),
+                                       p["D"], p["dt_bias"], G)
+        y_ref = y_ref.reshape(rows, Di).to(BF)
+        n_ref = om.gated_rmsnorm(y_ref, zx[:, :Di], p["norm.weight"], s["eps"], G).to(BF)
+        # kernels
+        zx_d = zx.cuda()
+        xbc = ops.mamba2_conv_update(conv_d, zx_d, Di, p["conv1d.weight"].cuda(), p["conv1d.bias"].cuda())
+        assert torch.equal(conv_d.cpu(), st["conv"]), "conv state must be bit-exact (a shift and an append)"
+        assert _rel_rms(xbc.cpu(), xbc_ref) < 3e-3 and float((xbc.cpu().float() - xbc_ref.float()).abs().max()) < 0.05
+        # feed the oracle's conv output to the state update so that the comparison isolates that kernel
+        y = ops.mamba2_ssd_step(ssm_d, xbc_ref.cuda(), zx_d, 2 * Di + 2 * G * N, p["A_log"].cuda(), p["D"].cuda(), p["dt_bias"].cuda(), G)
+        assert _rel_rms(y.cpu(), y_ref) < 3e-3, (step, _rel_rms(y.cpu(), y_ref))
+        d_state = (ssm_d.cpu().float() - st["ssm"].float()).abs()
+        assert float((d_state / st["ssm"].float().abs().clamp_min(1e-2)).max()) < 1e-2, "state differs by more than a bf16 ulp"
+        ssm_d.copy_(st["ssm"].cuda())  # carry the oracle's state: no drift between the two recurrences
+        n = ops.mamba2_gated_rmsnorm(y_ref.cuda(), zx_d, p["norm.weight"].cuda(), s["eps"], G)
+        assert _rel_rms(n.cpu(), n_ref) < 3e-3
+
+
+def test_mamba2_mixer_step_end_to_end_vs_oracle():
+    """in_proj (tcgen05 GEMM) -> conv -> state update -> gated norm -> out_proj, free-running for 8 tokens."""
+    from zonos_b200 import ops
+
+    p = om.synth_mixer_params(d_model=512, seed=2, dtype=BF)
+    s = p["shape"]
+    Di, H, P, N, G = s["d_inner"], s["n_heads"], s["head_dim"], s["d_state"], s["n_groups"]
+    rows = 4
+    w_in, w_out = ops.pack_weight(p["in_proj.weight"].cuda()), ops.pack_weight(p["out_proj.weight"].cuda())
+    st = om.new_state(p, rows, conv_dtype=BF, ssm_dtype=BF)
+    conv_d, ssm_d = st["conv"].cuda(), st["ssm"].cuda()
+    g = torch.Generator().manual_seed(1)
+    for step in range(8):
+        u = torch.randn(rows, s["d_model"], generator=g).to(BF)
+        ref = om.mixer_step(p, st, u, storage_dtype=BF)
+        zx = ops.gemm_bf16(u.cuda(), w_in, 2 * Di + 2 * G * N + H)
+        xbc = ops.mamba2_conv_update(conv_d, zx, Di, p["conv1d.weight"].cuda(), p["conv1d.bias"].cuda())
+        y = ops.mamba2_ssd_step(ssm_d, xbc, zx, 2 * Di + 2 * G * N, p["A_log"].cuda(), p["D"].cuda(), p["dt_bias"].cuda(), G)
+        yn = ops.mamba2_gated_rmsnorm(y, zx, p["norm.weight"].cuda(), s["eps"], G)
+        out = ops.gemm_bf16(yn, w_out, s["d_model"])
+        assert torch.isfinite(out).all()
+        assert _rel_rms(out.cpu(), ref) < 1e-2, (step, _rel_rms(out.cpu(), ref))
+    assert _rel_rms(ssm_d.cpu(), st["ssm"]) < 1e-2

@@ -111,3 +111,42 @@ def test_dac_decode(golden):
             assert wav.shape == case["wav"].shape == (case["codes"].shape[0], 1, 512 * case["codes"].shape[2])
             assert float((wav - case["wav"]).abs().max()) < 2e-5  # fp32 conv summation order varies with threading
             assert 0.05 < float(case["wav"].std()) < 0.9  # the fixture is not degenerate / saturated
+
+
+def test_mamba2_oracle_pinned_against_transformers_mixer():
+    """oracle/mamba2.py (restating mamba_ssm's Mamba2.step, which is absent here) against the pure-torch statement of the
+    same mixer that transformers ships (Mamba2Mixer.torch_forward): chunked prefill of 11 tokens, then 5 cached decode
+    steps, fp32 on the CPU.  n_groups = 1 (the hybrid's setting; transformers' gated norm ignores groups)."""
+    transformers = pytest.importorskip("transformers")
+    from transformers.cache_utils import DynamicCache
+    from transformers.models.mamba2.configuration_mamba2 import Mamba2Config
+    from transformers.models.mamba2.modeling_mamba2 import Mamba2Mixer
+
+    from oracle import mamba2 as om
+
+    p = om.synth_mixer_params(d_model=64, expand=2, head_dim=16, d_state=32, n_groups=1, seed=3)
+    s = p["shape"]
+    cfg = Mamba2Config(num_heads=s["n_heads"], head_dim=s["head_dim"], hidden_size=64, state_size=32, expand=2, n_groups=1,
+                       conv_kernel=4, num_hidden_layers=1, chunk_size=8, use_bias=False, use_conv_bias=True,
+                       layer_norm_epsilon=1e-5, vocab_size=16)
+    m = Mamba2Mixer(cfg, layer_idx=0).float().eval()
+    with torch.no_grad():
+        m.in_proj.weight.copy_(p["in_proj.weight"])
+        m.conv1d.weight.copy_(p["conv1d.weight"].unsqueeze(1))
+        m.conv1d.bias.copy_(p["conv1d.bias"])
+        m.dt_bias.copy_(p["dt_bias"])
+        m.A_log.copy_(p["A_log"])
+        m.D.copy_(p["D"])
+        m.norm.weight.copy_(p["norm.weight"])
+        m.out_proj.weight.copy_(p["out_proj.weight"])
+    B, S, steps = 3, 11, 5
+    u = torch.randn(B, S + steps, 64, generator=torch.Generator().manual_seed(0))
+    cache = DynamicCache(config=cfg)
+    with torch.no_grad():
+        pre = m.torch_forward(u[:, :S], cache_params=cache)
+        dec = [m.torch_forward(u[:, S + i:S + i + 1], cache_params=cache)[:, 0] for i in range(steps)]
+    st = om.new_state(p, B)
+    mine = [om.mixer_step(p, st, u[:, t]) for t in range(S + steps)]
+    assert float((torch.stack(mine[:S], 1) - pre).abs().max()) < 2e-5
+    for i in range(steps):
+        assert float((mine[S + i] - dec[i]).abs().max()) < 2e-5, i

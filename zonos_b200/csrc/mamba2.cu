@@ -1,0 +1,205 @@
+// Mamba2 mixer, single decode step (the hybrid backbone, zonos/backbone/_mamba_ssm.py:18-31 builds its
+// layers with mamba_ssm's create_block; the arithmetic restated here is mamba_ssm 2.2.4 `Mamba2.step`:
+// causal_conv1d_update -> selective_state_update -> RMSNormGated).  The projections around these kernels are the
+// weight-streaming tcgen05 GEMMs of the transformer path.
+//
+// All three kernels are HBM-bound; the state update dominates: the SSM state of one (sequence, head) is P x N bf16
+// (64 x 128 = 16 KB), read once and written once per token and layer -- 2 MB per sequence and layer at the hybrid's shape.
+#include "../../include/zonos_b200.h"
+#include "common.cuh"
+
+namespace zb {
+
+__device__ __forceinline__ float silu_f(float v) { return v / (1.f + __expf(-v)); }
+
+// ---------------------------------------------------------------------------------------------- causal_conv1d_update
+// state [rows][C][4] bf16 (oldest first): shift by one, append x[c] = zxbcdt[row][col0 + c], out = silu(sum_k s[k] w[c][k] + b)
+__global__ void __launch_bounds__(256) mamba2_conv_update_kernel(bf16* __restrict__ state, const bf16* __restrict__ zxbcdt,
+                                                                 int ld, int col0, const bf16* __restrict__ w,
+                                                                 const bf16* __restrict__ bias, bf16* __restrict__ out,
+                                                                 int channels) {
+  pdl_launch_dependents();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, row = blockIdx.y;
+  if (c >= channels) return;
+  const uint2 wu = __ldg(reinterpret_cast<const uint2*>(w + (size_t)c * 4));
+  const float b = bias ? __bfloat162float(bias[c]) : 0.f;
+  pdl_wait_prior();
+  uint2* sp = reinterpret_cast<uint2*>(state + ((size_t)row * channels + c) * 4);
+  const uint2 su = *sp;
+  const bf16 xin = zxbcdt[(size_t)row * ld + col0 + c];
+  const float2 s01 = unpack_bf16x2(su.x), s23 = unpack_bf16x2(su.y);
+  const float2 w01 = unpack_bf16x2(wu.x), w23 = unpack_bf16x2(wu.y);
+  const float x = __bfloat162float(xin);
+  // window after the shift: s1, s2, s3, x
+  const float acc = s01.y * w01.x + s23.x * w01.y + s23.y * w23.x + x * w23.y + b;
+  *sp = make_uint2(pack_bf16x2(s01.y, s23.x), pack_bf16x2(s23.y, x));
+  out[(size_t)row * channels + c] = __float2bfloat16_rn(silu_f(acc));
+}
+
+// ---------------------------------------------------------------------------------------------- selective_state_update
+// grid (head, row), 256 threads.  h[p][n] = h[p][n] * exp(dt*A) + dt * x[p] * B[n];  y[p] = sum_n h[p][n] * C[n] + D * x[p]
+// with dt = softplus(dt_raw + dt_bias), A = -exp(A_log).  Lane layout: 16 lanes x 8 states cover one p row (256 B), a
+// warp covers two rows per 16-byte access; each lane keeps its 8 B / C values in registers.
+template <int N>
+__global__ void __launch_bounds__(256) mamba2_ssd_step_kernel(bf16* __restrict__ ssm_state, const bf16* __restrict__ xbc,
+                                                              int ld_xbc, const bf16* __restrict__ zxbcdt, int ld, int dt_col0,
+                                                              const float* __restrict__ A_log, const float* __restrict__ Dp,
+                                                              const float* __restrict__ dt_bias, bf16* __restrict__ y,
+                                                              int n_heads, int head_dim, int n_groups) {
+  static_assert(N == 128, "one p row = 16 lanes x 8 states");
+  pdl_launch_dependents();
+  const int h = blockIdx.x, row = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int psub = lane >> 4, n0 = (lane & 15) * 8;
+  const int d_inner = n_heads * head_dim, grp = h / (n_heads / n_groups);
+  const float A = -__expf(A_log[h]), Dh = Dp[h], dtb = dt_bias[h];
+  bf16* st = ssm_state + ((size_t)row * n_heads + h) * (size_t)head_dim * N;
+  // the state does not depend on the previous kernel of the step: fetch this thread's rows before the dependency resolves
+  constexpr int MAXI = 8;  // head_dim <= 128
+  uint4 hs[MAXI];
+#pragma unroll
+  for (int i = 0; i < MAXI; ++i) {
+    const int p = 2 * (warp + 8 * i) + psub;
+    if (p < head_dim) hs[i] = *reinterpret_cast<const uint4*>(st + (size_t)p * N + n0);
+  }
+  pdl_wait_prior();
+  const bf16* xr = xbc + (size_t)row * ld_xbc;
+  const uint4 bu = *reinterpret_cast<const uint4*>(xr + d_inner + grp * N + n0);
+  const uint4 cu = *reinterpret_cast<const uint4*>(xr + d_inner + n_groups * N + grp * N + n0);
+  float Bv[8], Cv[8];
+  {
+    const uint32_t bw[4] = {bu.x, bu.y, bu.z, bu.w}, cw[4] = {cu.x, cu.y, cu.z, cu.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 b2 = unpack_bf16x2(bw[j]), c2 = unpack_bf16x2(cw[j]);
+      Bv[2 * j] = b2.x, Bv[2 * j + 1] = b2.y, Cv[2 * j] = c2.x, Cv[2 * j + 1] = c2.y;
+    }
+  }
+  const float dtr = __bfloat162float(zxbcdt[(size_t)row * ld + dt_col0 + h]) + dtb;
+  const float dt = dtr <= 20.f ? log1pf(expf(dtr)) : dtr;
+  const float dA = expf(dt * A);
+#pragma unroll
+  for (int i = 0; i < MAXI; ++i) {
+    const int p = 2 * (warp + 8 * i) + psub;
+    if (p >= head_dim) break;  // (warp-uniform up to psub: head_dim is even)
+    const float x = __bfloat162float(xr[h * head_dim + p]);
+    const float dtx = dt * x;
+    const uint32_t hw[4] = {hs[i].x, hs[i].y, hs[i].z, hs[i].w};
+    uint32_t ow[4];
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 h2 = unpack_bf16x2(hw[j]);
+      const float a = fmaf(h2.x, dA, dtx * Bv[2 * j]), b = fmaf(h2.y, dA, dtx * Bv[2 * j + 1]);
+      acc = fmaf(a, Cv[2 * j], acc);
+      acc = fmaf(b, Cv[2 * j + 1], acc);
+      ow[j] = pack_bf16x2(a, b);
+    }
+    *reinterpret_cast<uint4*>(st + (size_t)p * N + n0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((lane & 15) == 0) y[(size_t)row * d_inner + h * head_dim + p] = __float2bfloat16_rn(fmaf(Dh, x, acc));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- RMSNormGated
+// out = rmsnorm_g(y * silu(z)) * w over each of n_groups channel groups (norm_before_gate = False); z = zxbcdt[:, :d_inner]
+__global__ void __launch_bounds__(256) mamba2_gated_rmsnorm_kernel(const bf16* __restrict__ y, const bf16* __restrict__ zxbcdt,
+                                                                   int ld, const bf16* __restrict__ w, bf16* __restrict__ out,
+                                                                   int d_inner, int n_groups, float eps) {
+  pdl_launch_dependents();
+  __shared__ float red[8];
+  __shared__ float bcast;
+  const int row = blockIdx.x / n_groups, g = blockIdx.x % n_groups, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gs = d_inner / n_groups;
+  constexpr int MAXV = 4;  // group size <= 8192
+  uint4 wu[MAXV];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 256 + tid) * 8;
+    if (c < gs) wu[i] = __ldg(reinterpret_cast<const uint4*>(w + g * gs + c));
+  }
+  pdl_wait_prior();
+  float v[MAXV][8];
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 256 + tid) * 8;
+    if (c < gs) {
+      const uint4 yu = *reinterpret_cast<const uint4*>(y + (size_t)row * d_inner + g * gs + c);
+      const uint4 zu = *reinterpret_cast<const uint4*>(zxbcdt + (size_t)row * ld + g * gs + c);
+      const uint32_t yw[4] = {yu.x, yu.y, yu.z, yu.w}, zw[4] = {zu.x, zu.y, zu.z, zu.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 y2 = unpack_bf16x2(yw[j]), z2 = unpack_bf16x2(zw[j]);
+        v[i][2 * j] = y2.x * silu_f(z2.x), v[i][2 * j + 1] = y2.y * silu_f(z2.y);
+        sq += v[i][2 * j] * v[i][2 * j] + v[i][2 * j + 1] * v[i][2 * j + 1];
+      }
+    }
+  }
+  sq = warp_sum(sq);
+  if (lane == 0) red[warp] = sq;
+  __syncthreads();
+  if (tid == 0) {
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a += red[k];
+    bcast = 1.0f / sqrtf(a / (float)gs + eps);
+  }
+  __syncthreads();
+  const float rstd = bcast;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 256 + tid) * 8;
+    if (c < gs) {
+      const uint32_t ww[4] = {wu[i].x, wu[i].y, wu[i].z, wu[i].w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 w2 = unpack_bf16x2(ww[j]);
+        o[j] = pack_bf16x2(v[i][2 * j] * rstd * w2.x, v[i][2 * j + 1] * rstd * w2.y);
+      }
+      *reinterpret_cast<uint4*>(out + (size_t)row * d_inner + g * gs + c) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+}  // namespace zb
+
+using namespace zb;
+
+extern "C" int zb200_mamba2_conv_update(void* conv_state, const void* zxbcdt, int ld, int col0, const void* w, const void* bias,
+                                        void* out, int rows, int channels, int d_conv, void* stream) {
+  ZB_REQUIRE(conv_state && zxbcdt && w && out && rows > 0 && channels > 0, "mamba2_conv_update: bad arguments");
+  ZB_REQUIRE(d_conv == 4, "mamba2_conv_update: d_conv=%d (only the Mamba2 default 4 is built)", d_conv);
+  ZB_REQUIRE(col0 >= 0 && col0 + channels <= ld, "mamba2_conv_update: columns [%d, %d) exceed the row pitch %d", col0, col0 + channels, ld);
+  ZB_CHECK_CUDA(launch_pdl(mamba2_conv_update_kernel, dim3((unsigned)ceil_div(channels, 256), (unsigned)rows), dim3(256), 0,
+                           (cudaStream_t)stream, pdl_enabled(), (bf16*)conv_state, (const bf16*)zxbcdt, ld, col0, (const bf16*)w,
+                           (const bf16*)bias, (bf16*)out, channels));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_mamba2_ssd_step(void* ssm_state, const void* xbc, int ld_xbc, const void* zxbcdt, int ld, int dt_col0,
+                                     const float* A_log, const float* D, const float* dt_bias, void* y, int rows, int n_heads,
+                                     int head_dim, int d_state, int n_groups, void* stream) {
+  ZB_REQUIRE(ssm_state && xbc && zxbcdt && A_log && D && dt_bias && y && rows > 0, "mamba2_ssd_step: bad arguments");
+  ZB_REQUIRE(d_state == 128, "mamba2_ssd_step: d_state=%d (only the Mamba2 default 128 is built)", d_state);
+  ZB_REQUIRE(head_dim > 0 && head_dim <= 128 && head_dim % 8 == 0 && n_heads > 0 && n_groups > 0 && n_heads % n_groups == 0,
+             "mamba2_ssd_step: unsupported head layout H=%d P=%d G=%d", n_heads, head_dim, n_groups);
+  ZB_REQUIRE(ld_xbc >= n_heads * head_dim + 2 * n_groups * d_state && ld_xbc % 8 == 0 && dt_col0 + n_heads <= ld,
+             "mamba2_ssd_step: row pitches too small");
+  ZB_CHECK_CUDA(launch_pdl(mamba2_ssd_step_kernel<128>, dim3((unsigned)n_heads, (unsigned)rows), dim3(256), 0, (cudaStream_t)stream,
+                           pdl_enabled(), (bf16*)ssm_state, (const bf16*)xbc, ld_xbc, (const bf16*)zxbcdt, ld, dt_col0, A_log, D,
+                           dt_bias, (bf16*)y, n_heads, head_dim, n_groups));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_mamba2_gated_rmsnorm(const void* y, const void* zxbcdt, int ld, const void* w, void* out, int rows,
+                                          int d_inner, int n_groups, float eps, void* stream) {
+  ZB_REQUIRE(y && zxbcdt && w && out && rows > 0 && d_inner > 0 && n_groups > 0, "mamba2_gated_rmsnorm: bad arguments");
+  ZB_REQUIRE(d_inner % n_groups == 0 && (d_inner / n_groups) % 8 == 0 && d_inner / n_groups <= 8192 && ld >= d_inner && ld % 8 == 0,
+             "mamba2_gated_rmsnorm: unsupported shape d_inner=%d groups=%d ld=%d", d_inner, n_groups, ld);
+  ZB_CHECK_CUDA(launch_pdl(mamba2_gated_rmsnorm_kernel, dim3((unsigned)(rows * n_groups)), dim3(256), 0, (cudaStream_t)stream,
+                           pdl_enabled(), (const bf16*)y, (const bf16*)zxbcdt, ld, (const bf16*)w, (bf16*)out, d_inner, n_groups,
+                           eps));
+  return ZB200_OK;
+}

@@ -197,3 +197,40 @@ def attn_prefill(q: torch.Tensor, kv: PagedKV, layer: int, pos0: int, n_heads: i
     check(lib().zb200_attn_prefill(ptr(q), ptr(kv.pool), ptr(kv.block_table), kv.pages_per_seq, kv.num_pages, n_heads,
                                    kv.n_kv_heads, layer, n_seq, S, pos0, ptr(out), stream_ptr()), "attn_prefill")
     return out
+
+
+# ---- Mamba2 mixer decode step (hybrid backbone) -------------------------------------------------------
+def mamba2_conv_update(conv_state: torch.Tensor, zxbcdt: torch.Tensor, col0: int, w: torch.Tensor, bias) -> torch.Tensor:
+    """causal_conv1d_update + SiLU.  conv_state bf16 [rows, C, 4] (updated in place), zxbcdt bf16 [rows, ld]."""
+    rows, C, K = conv_state.shape
+    assert conv_state.is_cuda and conv_state.dtype == torch.bfloat16 and conv_state.is_contiguous()
+    assert zxbcdt.dtype == torch.bfloat16 and zxbcdt.is_contiguous() and zxbcdt.shape[0] == rows
+    out = torch.empty(rows, C, dtype=torch.bfloat16, device=conv_state.device)
+    check(lib().zb200_mamba2_conv_update(ptr(conv_state), ptr(zxbcdt), zxbcdt.shape[1], col0, ptr(_cuda(w, torch.bfloat16)),
+                                         ptr(None if bias is None else _cuda(bias, torch.bfloat16)), ptr(out), rows, C, K,
+                                         stream_ptr()), "mamba2_conv_update")
+    return out
+
+
+def mamba2_ssd_step(ssm_state: torch.Tensor, xbc: torch.Tensor, zxbcdt: torch.Tensor, dt_col0: int, A_log, D, dt_bias,
+                    n_groups: int = 1) -> torch.Tensor:
+    """selective_state_update for one token.  ssm_state bf16 [rows, H, P, N] (updated in place) -> y bf16 [rows, H*P]."""
+    rows, H, P, N = ssm_state.shape
+    assert ssm_state.is_cuda and ssm_state.dtype == torch.bfloat16 and ssm_state.is_contiguous()
+    assert xbc.dtype == torch.bfloat16 and xbc.is_contiguous() and zxbcdt.is_contiguous()
+    y = torch.empty(rows, H * P, dtype=torch.bfloat16, device=ssm_state.device)
+    f32 = lambda t: _cuda(t, torch.float32)
+    a, d, b = f32(A_log), f32(D), f32(dt_bias)
+    check(lib().zb200_mamba2_ssd_step(ptr(ssm_state), ptr(xbc), xbc.shape[1], ptr(zxbcdt), zxbcdt.shape[1], dt_col0, ptr(a),
+                                      ptr(d), ptr(b), ptr(y), rows, H, P, N, n_groups, stream_ptr()), "mamba2_ssd_step")
+    return y
+
+
+def mamba2_gated_rmsnorm(y: torch.Tensor, zxbcdt: torch.Tensor, w: torch.Tensor, eps: float, n_groups: int = 1) -> torch.Tensor:
+    """RMSNormGated(norm_before_gate=False) with z = zxbcdt[:, :d_inner]."""
+    rows, Di = y.shape
+    assert y.is_cuda and y.dtype == torch.bfloat16 and y.is_contiguous() and zxbcdt.is_contiguous()
+    out = torch.empty_like(y)
+    check(lib().zb200_mamba2_gated_rmsnorm(ptr(y), ptr(zxbcdt), zxbcdt.shape[1], ptr(_cuda(w, torch.bfloat16)), ptr(out), rows,
+                                           Di, n_groups, ctypes.c_float(eps), stream_ptr()), "mamba2_gated_rmsnorm")
+    return out
