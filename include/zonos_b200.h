@@ -174,6 +174,14 @@ int zb200_mamba2_conv_update(void* conv_state, const void* zxbcdt, int ld, int c
 int zb200_mamba2_ssd_step(void* ssm_state, const void* xbc, int ld_xbc, const void* zxbcdt, int ld, int dt_col0,
                           const float* A_log, const float* D, const float* dt_bias, void* y, int rows, int n_heads,
                           int head_dim, int d_state, int n_groups, void* stream);
+/* Prefill forms of the two kernels above over n_seq sequences of seq_len tokens (rows are sequence-major: row = seq *
+ * seq_len + t): the conv window / SSM state stay in registers over the sequence and the final ones are written to
+ * conv_state / ssm_state (use_initial_state = 0: start from zeros, as a fresh allocate_inference_cache does). */
+int zb200_mamba2_conv_seq(void* conv_state, const void* zxbcdt, int ld, int col0, const void* w, const void* bias,
+                          void* out, int n_seq, int seq_len, int channels, int d_conv, int use_initial_state, void* stream);
+int zb200_mamba2_ssd_scan(void* ssm_state, const void* xbc, int ld_xbc, const void* zxbcdt, int ld, int dt_col0,
+                          const float* A_log, const float* D, const float* dt_bias, void* y, int n_seq, int seq_len,
+                          int n_heads, int head_dim, int d_state, int n_groups, int use_initial_state, void* stream);
 /* RMSNormGated(norm_before_gate=False): out = rmsnorm_group(y * silu(z)) * w, z = zxbcdt[:, :d_inner]. */
 int zb200_mamba2_gated_rmsnorm(const void* y, const void* zxbcdt, int ld, const void* w, void* out, int rows, int d_inner,
                                int n_groups, float eps, void* stream);

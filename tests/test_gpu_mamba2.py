@@ -79,3 +79,48 @@ def test_mamba2_mixer_step_end_to_end_vs_oracle():
         assert torch.isfinite(out).all()
         assert _rel_rms(out.cpu(), ref) < 1e-2, (step, _rel_rms(out.cpu(), ref))
     assert _rel_rms(ssm_d.cpu(), st["ssm"]) < 1e-2
+
+
+@pytest.mark.parametrize("n_groups,head_dim", [(1, 64), (2, 32)])
+def test_mamba2_prefill_scan_then_decode_steps(n_groups, head_dim):
+    """Prefill of S tokens with the sequence kernels (conv window / SSM state in registers), then decode steps that
+    continue from the states the prefill left: outputs and states vs the oracle stepping token by token (fp32 state
+    during the prefix, as in a scan kernel; bf16 once stored)."""
+    from zonos_b200 import ops
+
+    p = om.synth_mixer_params(d_model=256, head_dim=head_dim, n_groups=n_groups, seed=8, dtype=BF)
+    s = p["shape"]
+    Di, H, P, N, G = s["d_inner"], s["n_heads"], s["head_dim"], s["d_state"], s["n_groups"]
+    n_seq, S, steps = 3, 37, 4
+    g = torch.Generator().manual_seed(4)
+    zx_all = torch.randn(n_seq, S + steps, 2 * Di + 2 * G * N + H, generator=g).to(BF)
+    # oracle: token by token
+    st = om.new_state(p, n_seq, conv_dtype=BF, ssm_dtype=torch.float32)
+    y_ref = []
+    for t in range(S + steps):
+        if t == S:
+            st["ssm"] = st["ssm"].to(BF)  # what the prefill stores
+        zx = zx_all[:, t]
+        xbc_ref, st["conv"] = om.conv1d_update(st["conv"], zx[:, Di:2 * Di + 2 * G * N], p["conv1d.weight"], p["conv1d.bias"])
+        xbc_ref = xbc_ref.to(BF)
+        y, st["ssm"] = om.ssd_step(st["ssm"], xbc_ref[:, :Di].reshape(n_seq, H, P), zx[:, -H:], p["A_log"],
+                                   xbc_ref[:, Di:Di + G * N].reshape(n_seq, G, N), xbc_ref[:, Di + G * N:].reshape(n_seq, G, N),
+                                   p["D"], p["dt_bias"], G)
+        y_ref.append(y.reshape(n_seq, Di).to(BF))
+    y_ref = torch.stack(y_ref, 1)  # [n_seq, S+steps, Di]
+    # kernels
+    conv_d = torch.zeros(n_seq, Di + 2 * G * N, 4, dtype=BF, device="cuda")
+    ssm_d = torch.full((n_seq, H, P, N), 7.0, dtype=BF, device="cuda")  # must be ignored (use_initial_state = False)
+    cw, cb = p["conv1d.weight"].cuda(), p["conv1d.bias"].cuda()
+    A, D, dtb = p["A_log"].cuda(), p["D"].cuda(), p["dt_bias"].cuda()
+    zx_pre = zx_all[:, :S].reshape(n_seq * S, -1).contiguous().cuda()
+    xbc = ops.mamba2_conv_seq(conv_d, zx_pre, S, Di, cw, cb)
+    y = ops.mamba2_ssd_scan(ssm_d, xbc, zx_pre, S, 2 * Di + 2 * G * N, A, D, dtb, G)
+    assert _rel_rms(y.cpu().view(n_seq, S, Di), y_ref[:, :S]) < 4e-3
+    for i in range(steps):
+        zx = zx_all[:, S + i].contiguous().cuda()
+        xbc1 = ops.mamba2_conv_update(conv_d, zx, Di, cw, cb)
+        y1 = ops.mamba2_ssd_step(ssm_d, xbc1, zx, 2 * Di + 2 * G * N, A, D, dtb, G)
+        assert _rel_rms(y1.cpu(), y_ref[:, S + i]) < 6e-3, i
+    assert torch.equal(conv_d.cpu(), st["conv"])
+    assert _rel_rms(ssm_d.cpu(), st["ssm"]) < 6e-3

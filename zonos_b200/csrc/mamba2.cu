@@ -101,6 +101,129 @@ __global__ void __launch_bounds__(256) mamba2_ssd_step_kernel(bf16* __restrict__
   }
 }
 
+// ---------------------------------------------------------------------------------------------- prefill: conv over a sequence
+// Rows are sequence-major (row = seq * seq_len + t, the engine's prefill layout).  Thread = (sequence, channel): the 4-tap
+// window lives in registers over the whole sequence; the final window is the conv state the decode steps continue from.
+__global__ void __launch_bounds__(256) mamba2_conv_seq_kernel(bf16* __restrict__ state, const bf16* __restrict__ zxbcdt, int ld,
+                                                              int col0, const bf16* __restrict__ w, const bf16* __restrict__ bias,
+                                                              bf16* __restrict__ out, int seq_len, int channels, int use_init) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, seq = blockIdx.y;
+  if (c >= channels) return;
+  const uint2 wu = __ldg(reinterpret_cast<const uint2*>(w + (size_t)c * 4));
+  const float2 w01 = unpack_bf16x2(wu.x), w23 = unpack_bf16x2(wu.y);
+  const float b = bias ? __bfloat162float(bias[c]) : 0.f;
+  uint2* sp = reinterpret_cast<uint2*>(state + ((size_t)seq * channels + c) * 4);
+  float s1 = 0.f, s2 = 0.f, s3 = 0.f;  // the three most recent inputs (oldest first)
+  if (use_init) {
+    const uint2 su = *sp;
+    s1 = unpack_bf16x2(su.x).y;
+    const float2 s23 = unpack_bf16x2(su.y);
+    s2 = s23.x, s3 = s23.y;
+  }
+  float s0 = 0.f;
+  const bf16* xin = zxbcdt + (size_t)seq * seq_len * ld + col0 + c;
+  bf16* o = out + (size_t)seq * seq_len * channels + c;
+  for (int t = 0; t < seq_len; ++t) {
+    const float x = __bfloat162float(xin[(size_t)t * ld]);
+    const float acc = s1 * w01.x + s2 * w01.y + s3 * w23.x + x * w23.y + b;
+    o[(size_t)t * channels] = __float2bfloat16_rn(silu_f(acc));
+    s0 = s1, s1 = s2, s2 = s3, s3 = x;
+  }
+  *sp = make_uint2(pack_bf16x2(s0, s1), pack_bf16x2(s2, s3));
+}
+
+// ---------------------------------------------------------------------------------------------- prefill: SSD scan
+// Same lane layout as the step kernel; the state of (sequence, head) stays in fp32 registers over the whole sequence
+// (4 rows x 8 states per thread) and is written once at the end, so the scan moves only x / B / C / dt in and y out.
+// The inputs of token t+1 are fetched while token t is computed.  (Sequential in t: the prefix is <= a few hundred
+// tokens; a chunked SSD form on the tensor cores is what a long-prompt prefill would need.)
+template <int N>
+__global__ void __launch_bounds__(256) mamba2_ssd_scan_kernel(bf16* __restrict__ ssm_state, const bf16* __restrict__ xbc,
+                                                              int ld_xbc, const bf16* __restrict__ zxbcdt, int ld, int dt_col0,
+                                                              const float* __restrict__ A_log, const float* __restrict__ Dp,
+                                                              const float* __restrict__ dt_bias, bf16* __restrict__ y,
+                                                              int seq_len, int n_heads, int head_dim, int n_groups, int use_init) {
+  static_assert(N == 128, "one p row = 16 lanes x 8 states");
+  const int h = blockIdx.x, seq = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int psub = lane >> 4, n0 = (lane & 15) * 8;
+  const int d_inner = n_heads * head_dim, grp = h / (n_heads / n_groups);
+  const float A = -__expf(A_log[h]), Dh = Dp[h], dtb = dt_bias[h];
+  bf16* st = ssm_state + ((size_t)seq * n_heads + h) * (size_t)head_dim * N;
+  constexpr int MAXI = 4;  // head_dim <= 64 in this kernel (32 fp32 state registers per thread)
+  float hs[MAXI][8];
+#pragma unroll
+  for (int i = 0; i < MAXI; ++i) {
+    const int p = 2 * (warp + 8 * i) + psub;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) hs[i][j] = 0.f;
+    if (use_init && p < head_dim) {
+      const uint4 u = *reinterpret_cast<const uint4*>(st + (size_t)p * N + n0);
+      const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(uw[j]);
+        hs[i][2 * j] = f.x, hs[i][2 * j + 1] = f.y;
+      }
+    }
+  }
+  const size_t row0 = (size_t)seq * seq_len;
+  const int boff = d_inner + grp * N + n0, coff = d_inner + n_groups * N + grp * N + n0;
+  auto load_tok = [&](int t, uint4& bu, uint4& cu, float (&xv)[MAXI], float& dtr) {
+    const bf16* xr = xbc + (row0 + t) * ld_xbc;
+    bu = *reinterpret_cast<const uint4*>(xr + boff);
+    cu = *reinterpret_cast<const uint4*>(xr + coff);
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+      const int p = 2 * (warp + 8 * i) + psub;
+      xv[i] = p < head_dim ? __bfloat162float(xr[h * head_dim + p]) : 0.f;
+    }
+    dtr = __bfloat162float(zxbcdt[(row0 + t) * ld + dt_col0 + h]);
+  };
+  uint4 bu, cu, bu_n, cu_n;
+  float xv[MAXI], xv_n[MAXI], dtr, dtr_n;
+  load_tok(0, bu, cu, xv, dtr);
+  for (int t = 0; t < seq_len; ++t) {
+    if (t + 1 < seq_len) load_tok(t + 1, bu_n, cu_n, xv_n, dtr_n);
+    float Bv[8], Cv[8];
+    {
+      const uint32_t bw[4] = {bu.x, bu.y, bu.z, bu.w}, cw[4] = {cu.x, cu.y, cu.z, cu.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 b2 = unpack_bf16x2(bw[j]), c2 = unpack_bf16x2(cw[j]);
+        Bv[2 * j] = b2.x, Bv[2 * j + 1] = b2.y, Cv[2 * j] = c2.x, Cv[2 * j + 1] = c2.y;
+      }
+    }
+    const float dts = dtr + dtb;
+    const float dt = dts <= 20.f ? log1pf(expf(dts)) : dts;
+    const float dA = expf(dt * A);
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+      const int p = 2 * (warp + 8 * i) + psub;
+      const float dtx = dt * xv[i];
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        hs[i][j] = fmaf(hs[i][j], dA, dtx * Bv[j]);
+        acc = fmaf(hs[i][j], Cv[j], acc);
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if ((lane & 15) == 0 && p < head_dim) y[(row0 + t) * d_inner + h * head_dim + p] = __float2bfloat16_rn(fmaf(Dh, xv[i], acc));
+    }
+    bu = bu_n, cu = cu_n, dtr = dtr_n;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) xv[i] = xv_n[i];
+  }
+#pragma unroll
+  for (int i = 0; i < MAXI; ++i) {
+    const int p = 2 * (warp + 8 * i) + psub;
+    if (p < head_dim)
+      *reinterpret_cast<uint4*>(st + (size_t)p * N + n0) =
+          make_uint4(pack_bf16x2(hs[i][0], hs[i][1]), pack_bf16x2(hs[i][2], hs[i][3]), pack_bf16x2(hs[i][4], hs[i][5]),
+                     pack_bf16x2(hs[i][6], hs[i][7]));
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- RMSNormGated
 // out = rmsnorm_g(y * silu(z)) * w over each of n_groups channel groups (norm_before_gate = False); z = zxbcdt[:, :d_inner]
 __global__ void __launch_bounds__(256) mamba2_gated_rmsnorm_kernel(const bf16* __restrict__ y, const bf16* __restrict__ zxbcdt,
@@ -201,5 +324,34 @@ extern "C" int zb200_mamba2_gated_rmsnorm(const void* y, const void* zxbcdt, int
   ZB_CHECK_CUDA(launch_pdl(mamba2_gated_rmsnorm_kernel, dim3((unsigned)(rows * n_groups)), dim3(256), 0, (cudaStream_t)stream,
                            pdl_enabled(), (const bf16*)y, (const bf16*)zxbcdt, ld, (const bf16*)w, (bf16*)out, d_inner, n_groups,
                            eps));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_mamba2_conv_seq(void* conv_state, const void* zxbcdt, int ld, int col0, const void* w, const void* bias,
+                                     void* out, int n_seq, int seq_len, int channels, int d_conv, int use_initial_state,
+                                     void* stream) {
+  ZB_REQUIRE(conv_state && zxbcdt && w && out && n_seq > 0 && seq_len > 0 && channels > 0, "mamba2_conv_seq: bad arguments");
+  ZB_REQUIRE(d_conv == 4, "mamba2_conv_seq: d_conv=%d (only the Mamba2 default 4 is built)", d_conv);
+  ZB_REQUIRE(col0 >= 0 && col0 + channels <= ld, "mamba2_conv_seq: columns [%d, %d) exceed the row pitch %d", col0, col0 + channels, ld);
+  mamba2_conv_seq_kernel<<<dim3((unsigned)ceil_div(channels, 256), (unsigned)n_seq), 256, 0, (cudaStream_t)stream>>>(
+      (bf16*)conv_state, (const bf16*)zxbcdt, ld, col0, (const bf16*)w, (const bf16*)bias, (bf16*)out, seq_len, channels,
+      use_initial_state);
+  ZB_CHECK_LAUNCH("mamba2_conv_seq_kernel");
+  return ZB200_OK;
+}
+
+extern "C" int zb200_mamba2_ssd_scan(void* ssm_state, const void* xbc, int ld_xbc, const void* zxbcdt, int ld, int dt_col0,
+                                     const float* A_log, const float* D, const float* dt_bias, void* y, int n_seq, int seq_len,
+                                     int n_heads, int head_dim, int d_state, int n_groups, int use_initial_state, void* stream) {
+  ZB_REQUIRE(ssm_state && xbc && zxbcdt && A_log && D && dt_bias && y && n_seq > 0 && seq_len > 0, "mamba2_ssd_scan: bad arguments");
+  ZB_REQUIRE(d_state == 128, "mamba2_ssd_scan: d_state=%d (only the Mamba2 default 128 is built)", d_state);
+  ZB_REQUIRE(head_dim > 0 && head_dim <= 64 && head_dim % 8 == 0 && n_heads > 0 && n_groups > 0 && n_heads % n_groups == 0,
+             "mamba2_ssd_scan: unsupported head layout H=%d P=%d G=%d (P <= 64)", n_heads, head_dim, n_groups);
+  ZB_REQUIRE(ld_xbc >= n_heads * head_dim + 2 * n_groups * d_state && ld_xbc % 8 == 0 && dt_col0 + n_heads <= ld,
+             "mamba2_ssd_scan: row pitches too small");
+  mamba2_ssd_scan_kernel<128><<<dim3((unsigned)n_heads, (unsigned)n_seq), 256, 0, (cudaStream_t)stream>>>(
+      (bf16*)ssm_state, (const bf16*)xbc, ld_xbc, (const bf16*)zxbcdt, ld, dt_col0, A_log, D, dt_bias, (bf16*)y, seq_len, n_heads,
+      head_dim, n_groups, use_initial_state);
+  ZB_CHECK_LAUNCH("mamba2_ssd_scan_kernel");
   return ZB200_OK;
 }

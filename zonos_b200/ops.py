@@ -234,3 +234,30 @@ def mamba2_gated_rmsnorm(y: torch.Tensor, zxbcdt: torch.Tensor, w: torch.Tensor,
     check(lib().zb200_mamba2_gated_rmsnorm(ptr(y), ptr(zxbcdt), zxbcdt.shape[1], ptr(_cuda(w, torch.bfloat16)), ptr(out), rows,
                                            Di, n_groups, ctypes.c_float(eps), stream_ptr()), "mamba2_gated_rmsnorm")
     return out
+
+
+def mamba2_conv_seq(conv_state: torch.Tensor, zxbcdt: torch.Tensor, seq_len: int, col0: int, w, bias, use_initial_state=False):
+    """Prefill form of mamba2_conv_update: zxbcdt bf16 [n_seq*seq_len, ld] (sequence-major) -> bf16 [n_seq*seq_len, C];
+    conv_state [n_seq, C, 4] receives the final window."""
+    n_seq, C, K = conv_state.shape
+    assert conv_state.dtype == torch.bfloat16 and conv_state.is_contiguous() and zxbcdt.is_contiguous()
+    assert zxbcdt.shape[0] == n_seq * seq_len
+    out = torch.empty(n_seq * seq_len, C, dtype=torch.bfloat16, device=conv_state.device)
+    check(lib().zb200_mamba2_conv_seq(ptr(conv_state), ptr(zxbcdt), zxbcdt.shape[1], col0, ptr(_cuda(w, torch.bfloat16)),
+                                      ptr(None if bias is None else _cuda(bias, torch.bfloat16)), ptr(out), n_seq, seq_len, C, K,
+                                      int(use_initial_state), stream_ptr()), "mamba2_conv_seq")
+    return out
+
+
+def mamba2_ssd_scan(ssm_state: torch.Tensor, xbc: torch.Tensor, zxbcdt: torch.Tensor, seq_len: int, dt_col0: int, A_log, D,
+                    dt_bias, n_groups: int = 1, use_initial_state=False) -> torch.Tensor:
+    """Prefill form of mamba2_ssd_step (sequential scan, state in registers): -> y bf16 [n_seq*seq_len, H*P]."""
+    n_seq, H, P, N = ssm_state.shape
+    assert ssm_state.dtype == torch.bfloat16 and ssm_state.is_contiguous() and xbc.is_contiguous() and zxbcdt.is_contiguous()
+    y = torch.empty(n_seq * seq_len, H * P, dtype=torch.bfloat16, device=ssm_state.device)
+    f32 = lambda t: _cuda(t, torch.float32)
+    a, d, b = f32(A_log), f32(D), f32(dt_bias)
+    check(lib().zb200_mamba2_ssd_scan(ptr(ssm_state), ptr(xbc), xbc.shape[1], ptr(zxbcdt), zxbcdt.shape[1], dt_col0, ptr(a), ptr(d),
+                                      ptr(b), ptr(y), n_seq, seq_len, H, P, N, n_groups, int(use_initial_state), stream_ptr()),
+          "mamba2_ssd_scan")
+    return y
