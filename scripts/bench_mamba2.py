@@ -47,3 +47,11 @@ ssd_bytes = 2 * rows * H * P * N * 2
 print(f"rows {rows}: ssd_step {t_ssd:.2f} us/launch, {ssd_bytes / 1e6:.1f} MB state traffic -> {ssd_bytes / t_ssd / 1e3:.0f} GB/s = "
       f"{ssd_bytes / t_ssd / 1e3 / hbm_peak:.3f} of the measured HBM peak ({hbm_peak:.0f} GB/s); conv_update {t_conv:.2f} us, "
       f"gated_rmsnorm {t_norm:.2f} us (includes the wrappers' torch allocations)")
+
+# prefill scan at the hybrid's C5-like shape: 64 sequences x 138 tokens
+S = 138
+zxs = torch.randn(rows * S, 2 * Di + 2 * G * N + H, device=dev).bfloat16()
+xbcs = ops.mamba2_conv_seq(conv[0], zxs, S, Di, cw, cb)
+t_scan = timed(lambda l: ops.mamba2_ssd_scan(ssm[l], xbcs, zxs, S, 2 * Di + 2 * G * N, A, D, dtb, G), reps=2)
+t_cseq = timed(lambda l: ops.mamba2_conv_seq(conv[l], zxs, S, Di, cw, cb), reps=2)
+print(f"prefill {rows} x {S} tokens: ssd_scan {t_scan:.1f} us/layer, conv_seq {t_cseq:.1f} us/layer")

@@ -8,6 +8,8 @@
 #include "../../include/zonos_b200.h"
 #include "common.cuh"
 
+#include <cstdlib>
+
 namespace zb {
 
 __device__ __forceinline__ float silu_f(float v) { return v / (1.f + __expf(-v)); }
@@ -101,6 +103,83 @@ __global__ void __launch_bounds__(256) mamba2_ssd_step_kernel(bf16* __restrict__
   }
 }
 
+// Persistent form of the step kernel for head_dim 64 (the Mamba2 default): the grid is a multiple of the SM count, each CTA
+// walks (row, head) tiles with a grid stride and fetches the NEXT tile's 16 KB of state while it updates the current one,
+// so the HBM stream never drains between tiles (the one-tile-per-CTA form measured 0.66 of the HBM peak at 64 rows).
+template <int N>
+__global__ void __launch_bounds__(256) mamba2_ssd_step_p64_kernel(bf16* __restrict__ ssm_state, const bf16* __restrict__ xbc,
+                                                                  int ld_xbc, const bf16* __restrict__ zxbcdt, int ld,
+                                                                  int dt_col0, const float* __restrict__ A_log,
+                                                                  const float* __restrict__ Dp, const float* __restrict__ dt_bias,
+                                                                  bf16* __restrict__ y, int n_heads, int n_groups, int n_tiles) {
+  static_assert(N == 128, "one p row = 16 lanes x 8 states");
+  constexpr int P = 64, MAXI = 4;
+  pdl_launch_dependents();
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int psub = lane >> 4, n0 = (lane & 15) * 8;
+  const int d_inner = n_heads * P;
+  int tile = blockIdx.x;
+  if (tile >= n_tiles) return;
+  uint4 hs[MAXI], hn[MAXI];
+  {
+    const bf16* st = ssm_state + (size_t)tile * P * N;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) hs[i] = *reinterpret_cast<const uint4*>(st + (size_t)(2 * (warp + 8 * i) + psub) * N + n0);
+  }
+  pdl_wait_prior();
+  for (; tile < n_tiles; tile += gridDim.x) {
+    const int row = tile / n_heads, h = tile - row * n_heads, grp = h / (n_heads / n_groups);
+    const int nxt = tile + gridDim.x;
+    if (nxt < n_tiles) {
+      const bf16* sn = ssm_state + (size_t)nxt * P * N;
+#pragma unroll
+      for (int i = 0; i < MAXI; ++i) hn[i] = *reinterpret_cast<const uint4*>(sn + (size_t)(2 * (warp + 8 * i) + psub) * N + n0);
+    }
+    bf16* st = ssm_state + (size_t)tile * P * N;
+    const bf16* xr = xbc + (size_t)row * ld_xbc;
+    const uint4 bu = *reinterpret_cast<const uint4*>(xr + d_inner + grp * N + n0);
+    const uint4 cu = *reinterpret_cast<const uint4*>(xr + d_inner + n_groups * N + grp * N + n0);
+    float xv[MAXI];
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) xv[i] = __bfloat162float(xr[h * P + 2 * (warp + 8 * i) + psub]);
+    const float A = -__expf(__ldg(A_log + h)), Dh = __ldg(Dp + h);
+    const float dtr = __bfloat162float(zxbcdt[(size_t)row * ld + dt_col0 + h]) + __ldg(dt_bias + h);
+    const float dt = dtr <= 20.f ? log1pf(expf(dtr)) : dtr;
+    const float dA = expf(dt * A);
+    float Bv[8], Cv[8];
+    {
+      const uint32_t bw[4] = {bu.x, bu.y, bu.z, bu.w}, cw[4] = {cu.x, cu.y, cu.z, cu.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 b2 = unpack_bf16x2(bw[j]), c2 = unpack_bf16x2(cw[j]);
+        Bv[2 * j] = b2.x, Bv[2 * j + 1] = b2.y, Cv[2 * j] = c2.x, Cv[2 * j + 1] = c2.y;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+      const int p = 2 * (warp + 8 * i) + psub;
+      const float dtx = dt * xv[i];
+      const uint32_t hw[4] = {hs[i].x, hs[i].y, hs[i].z, hs[i].w};
+      uint32_t ow[4];
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 h2 = unpack_bf16x2(hw[j]);
+        const float a = fmaf(h2.x, dA, dtx * Bv[2 * j]), b = fmaf(h2.y, dA, dtx * Bv[2 * j + 1]);
+        acc = fmaf(a, Cv[2 * j], acc);
+        acc = fmaf(b, Cv[2 * j + 1], acc);
+        ow[j] = pack_bf16x2(a, b);
+      }
+      *reinterpret_cast<uint4*>(st + (size_t)p * N + n0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if ((lane & 15) == 0) y[(size_t)row * d_inner + h * P + p] = __float2bfloat16_rn(fmaf(Dh, xv[i], acc));
+    }
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) hs[i] = hn[i];
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- prefill: conv over a sequence
 // Rows are sequence-major (row = seq * seq_len + t, the engine's prefill layout).  Thread = (sequence, channel): the 4-tap
 // window lives in registers over the whole sequence; the final window is the conv state the decode steps continue from.
@@ -135,8 +214,11 @@ __global__ void __launch_bounds__(256) mamba2_conv_seq_kernel(bf16* __restrict__
 // ---------------------------------------------------------------------------------------------- prefill: SSD scan
 // Same lane layout as the step kernel; the state of (sequence, head) stays in fp32 registers over the whole sequence
 // (4 rows x 8 states per thread) and is written once at the end, so the scan moves only x / B / C / dt in and y out.
-// The inputs of token t+1 are fetched while token t is computed.  (Sequential in t: the prefix is <= a few hundred
-// tokens; a chunked SSD form on the tensor cores is what a long-prompt prefill would need.)
+// Tokens are staged 16 at a time in shared memory with cp.async (double-buffered: chunk i+1 arrives while chunk i is
+// scanned), dt / exp(dt*A) are computed once per token by 16 threads, y leaves as coalesced 128-byte rows per chunk.
+// (Sequential in t: the prefix is <= a few hundred tokens; a chunked SSD form on the tensor cores is what a long-prompt
+// prefill would need.)
+constexpr int SCAN_TC = 16;
 template <int N>
 __global__ void __launch_bounds__(256) mamba2_ssd_scan_kernel(bf16* __restrict__ ssm_state, const bf16* __restrict__ xbc,
                                                               int ld_xbc, const bf16* __restrict__ zxbcdt, int ld, int dt_col0,
@@ -144,12 +226,14 @@ __global__ void __launch_bounds__(256) mamba2_ssd_scan_kernel(bf16* __restrict__
                                                               const float* __restrict__ dt_bias, bf16* __restrict__ y,
                                                               int seq_len, int n_heads, int head_dim, int n_groups, int use_init) {
   static_assert(N == 128, "one p row = 16 lanes x 8 states");
+  constexpr int MAXI = 4, PMAX = 64;  // head_dim <= 64 in this kernel (32 fp32 state registers per thread)
+  __shared__ __align__(16) bf16 sB[2][SCAN_TC][N], sC[2][SCAN_TC][N], sX[2][SCAN_TC][PMAX], sY[SCAN_TC][PMAX];
+  __shared__ float sDt[2][SCAN_TC], sDa[2][SCAN_TC];
   const int h = blockIdx.x, seq = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int psub = lane >> 4, n0 = (lane & 15) * 8;
   const int d_inner = n_heads * head_dim, grp = h / (n_heads / n_groups);
   const float A = -__expf(A_log[h]), Dh = Dp[h], dtb = dt_bias[h];
   bf16* st = ssm_state + ((size_t)seq * n_heads + h) * (size_t)head_dim * N;
-  constexpr int MAXI = 4;  // head_dim <= 64 in this kernel (32 fp32 state registers per thread)
   float hs[MAXI][8];
 #pragma unroll
   for (int i = 0; i < MAXI; ++i) {
@@ -167,52 +251,80 @@ __global__ void __launch_bounds__(256) mamba2_ssd_scan_kernel(bf16* __restrict__
     }
   }
   const size_t row0 = (size_t)seq * seq_len;
-  const int boff = d_inner + grp * N + n0, coff = d_inner + n_groups * N + grp * N + n0;
-  auto load_tok = [&](int t, uint4& bu, uint4& cu, float (&xv)[MAXI], float& dtr) {
-    const bf16* xr = xbc + (row0 + t) * ld_xbc;
-    bu = *reinterpret_cast<const uint4*>(xr + boff);
-    cu = *reinterpret_cast<const uint4*>(xr + coff);
-#pragma unroll
-    for (int i = 0; i < MAXI; ++i) {
-      const int p = 2 * (warp + 8 * i) + psub;
-      xv[i] = p < head_dim ? __bfloat162float(xr[h * head_dim + p]) : 0.f;
+  const int boff = d_inner + grp * N, coff = d_inner + n_groups * N + grp * N, xoff = h * head_dim;
+  const int xchunks = head_dim / 8;  // 16-byte pieces of a token's x
+  // stage chunk `ck` into buffer `buf`: per token 16 pieces of B, 16 of C, head_dim/8 of x
+  auto stage = [&](int ck, int buf) {
+    const int t0 = ck * SCAN_TC, per_tok = 32 + xchunks;
+    for (int i = tid; i < SCAN_TC * per_tok; i += 256) {
+      const int tt = i / per_tok, piece = i - tt * per_tok;
+      if (t0 + tt >= seq_len) continue;
+      const bf16* xr = xbc + (row0 + t0 + tt) * ld_xbc;
+      if (piece < 16) cp_async16(&sB[buf][tt][piece * 8], xr + boff + piece * 8);
+      else if (piece < 32) cp_async16(&sC[buf][tt][(piece - 16) * 8], xr + coff + (piece - 16) * 8);
+      else cp_async16(&sX[buf][tt][(piece - 32) * 8], xr + xoff + (piece - 32) * 8);
     }
-    dtr = __bfloat162float(zxbcdt[(row0 + t) * ld + dt_col0 + h]);
+    cp_async_commit();
   };
-  uint4 bu, cu, bu_n, cu_n;
-  float xv[MAXI], xv_n[MAXI], dtr, dtr_n;
-  load_tok(0, bu, cu, xv, dtr);
-  for (int t = 0; t < seq_len; ++t) {
-    if (t + 1 < seq_len) load_tok(t + 1, bu_n, cu_n, xv_n, dtr_n);
-    float Bv[8], Cv[8];
-    {
-      const uint32_t bw[4] = {bu.x, bu.y, bu.z, bu.w}, cw[4] = {cu.x, cu.y, cu.z, cu.w};
+  auto load_dt = [&](int ck) -> float {  // threads 0..15: the raw dt of their token in chunk ck
+    const int t = ck * SCAN_TC + tid;
+    return (tid < SCAN_TC && t < seq_len) ? __bfloat162float(zxbcdt[(row0 + t) * ld + dt_col0 + h]) : 0.f;
+  };
+  const int n_chunks = (seq_len + SCAN_TC - 1) / SCAN_TC;
+  stage(0, 0);
+  float dt_raw = load_dt(0);
+  for (int ck = 0; ck < n_chunks; ++ck) {
+    const int buf = ck & 1;
+    if (tid < SCAN_TC) {
+      const float dts = dt_raw + dtb;
+      const float dt = dts <= 20.f ? log1pf(expf(dts)) : dts;
+      sDt[buf][tid] = dt, sDa[buf][tid] = expf(dt * A);
+    }
+    if (ck + 1 < n_chunks) {
+      stage(ck + 1, buf ^ 1);
+      dt_raw = load_dt(ck + 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();  // chunk ck is in shared memory; the previous chunk's y rows have been written out
+    const int nt = min(SCAN_TC, seq_len - ck * SCAN_TC);
+    for (int tt = 0; tt < nt; ++tt) {
+      const uint4 bu = *reinterpret_cast<const uint4*>(&sB[buf][tt][n0]);
+      const uint4 cu = *reinterpret_cast<const uint4*>(&sC[buf][tt][n0]);
+      float Bv[8], Cv[8];
+      {
+        const uint32_t bw[4] = {bu.x, bu.y, bu.z, bu.w}, cw[4] = {cu.x, cu.y, cu.z, cu.w};
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 b2 = unpack_bf16x2(bw[j]), c2 = unpack_bf16x2(cw[j]);
-        Bv[2 * j] = b2.x, Bv[2 * j + 1] = b2.y, Cv[2 * j] = c2.x, Cv[2 * j + 1] = c2.y;
+        for (int j = 0; j < 4; ++j) {
+          const float2 b2 = unpack_bf16x2(bw[j]), c2 = unpack_bf16x2(cw[j]);
+          Bv[2 * j] = b2.x, Bv[2 * j + 1] = b2.y, Cv[2 * j] = c2.x, Cv[2 * j + 1] = c2.y;
+        }
+      }
+      const float dt = sDt[buf][tt], dA = sDa[buf][tt];
+#pragma unroll
+      for (int i = 0; i < MAXI; ++i) {
+        const int p = 2 * (warp + 8 * i) + psub;
+        if (p >= head_dim) break;
+        const float x = __bfloat162float(sX[buf][tt][p]);
+        const float dtx = dt * x;
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          hs[i][j] = fmaf(hs[i][j], dA, dtx * Bv[j]);
+          acc = fmaf(hs[i][j], Cv[j], acc);
+        }
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if ((lane & 15) == 0) sY[tt][p] = __float2bfloat16_rn(fmaf(Dh, x, acc));
       }
     }
-    const float dts = dtr + dtb;
-    const float dt = dts <= 20.f ? log1pf(expf(dts)) : dts;
-    const float dA = expf(dt * A);
-#pragma unroll
-    for (int i = 0; i < MAXI; ++i) {
-      const int p = 2 * (warp + 8 * i) + psub;
-      const float dtx = dt * xv[i];
-      float acc = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        hs[i][j] = fmaf(hs[i][j], dA, dtx * Bv[j]);
-        acc = fmaf(hs[i][j], Cv[j], acc);
-      }
-#pragma unroll
-      for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-      if ((lane & 15) == 0 && p < head_dim) y[(row0 + t) * d_inner + h * head_dim + p] = __float2bfloat16_rn(fmaf(Dh, xv[i], acc));
+    __syncthreads();
+    for (int i = tid; i < nt * xchunks; i += 256) {  // y rows of the chunk: head_dim*2 contiguous bytes per token
+      const int tt = i / xchunks, piece = i - tt * xchunks;
+      *reinterpret_cast<uint4*>(y + (row0 + ck * SCAN_TC + tt) * d_inner + xoff + piece * 8) =
+          *reinterpret_cast<const uint4*>(&sY[tt][piece * 8]);
     }
-    bu = bu_n, cu = cu_n, dtr = dtr_n;
-#pragma unroll
-    for (int i = 0; i < MAXI; ++i) xv[i] = xv_n[i];
   }
 #pragma unroll
   for (int i = 0; i < MAXI; ++i) {
@@ -310,6 +422,18 @@ extern "C" int zb200_mamba2_ssd_step(void* ssm_state, const void* xbc, int ld_xb
              "mamba2_ssd_step: unsupported head layout H=%d P=%d G=%d", n_heads, head_dim, n_groups);
   ZB_REQUIRE(ld_xbc >= n_heads * head_dim + 2 * n_groups * d_state && ld_xbc % 8 == 0 && dt_col0 + n_heads <= ld,
              "mamba2_ssd_step: row pitches too small");
+  static const bool one_tile = getenv("ZB200_SSD_ONE_TILE") != nullptr;  // A/B switch
+  if (head_dim == 64 && !one_tile) {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int n_tiles = rows * n_heads;
+    static const int per_sm = getenv("ZB200_SSD_CTAS_PER_SM") ? atoi(getenv("ZB200_SSD_CTAS_PER_SM")) : 6;
+    const int grid = n_tiles < sms * per_sm ? n_tiles : sms * per_sm;
+    ZB_CHECK_CUDA(launch_pdl(mamba2_ssd_step_p64_kernel<128>, dim3((unsigned)grid), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(),
+                             (bf16*)ssm_state, (const bf16*)xbc, ld_xbc, (const bf16*)zxbcdt, ld, dt_col0, A_log, D, dt_bias,
+                             (bf16*)y, n_heads, n_groups, n_tiles));
+    return ZB200_OK;
+  }
   ZB_CHECK_CUDA(launch_pdl(mamba2_ssd_step_kernel<128>, dim3((unsigned)n_heads, (unsigned)rows), dim3(256), 0, (cudaStream_t)stream,
                            pdl_enabled(), (bf16*)ssm_state, (const bf16*)xbc, ld_xbc, (const bf16*)zxbcdt, ld, dt_col0, A_log, D,
                            dt_bias, (bf16*)y, n_heads, head_dim, n_groups));
