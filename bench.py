@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--no-dac", action="store_true")
+    ap.add_argument("--no-mamba", action="store_true", help="skip the Mamba2 state-update micro-section (hybrid, first slice)")
     ap.add_argument("--cpu-frames", type=int, default=32, help="decode frames in the CPU baseline sample")
     return ap.parse_args()
 
@@ -243,6 +244,38 @@ def dac_section(device, batch, frames):
             "launches": 31 * reps * 2, "finite": bool(torch.isfinite(wav_host).all())}
 
 
+def mamba2_section(device, hbm_peak, rows=64, layers=24):
+    """First slice of BASELINE configs[4] (hybrid, batch 32 per GPU = 64 rows with CFG): the Mamba2 SSD state update of the
+    decode step alone, at the hybrid's mixer shape, over `layers` distinct states (3.2 GB: nothing stays in L2)."""
+    from zonos_b200 import ops
+
+    H, P, N, Di = 64, 64, 128, 4096
+    g = torch.Generator(device=device).manual_seed(9)
+    ssm = [(0.1 * torch.randn(rows, H, P, N, generator=g, device=device)).bfloat16() for _ in range(layers)]
+    xbc = torch.randn(rows, Di + 2 * N, generator=g, device=device).bfloat16()
+    zx = torch.randn(rows, 2 * Di + 2 * N + H, generator=g, device=device).bfloat16()
+    A = torch.rand(H, generator=g, device=device).float()
+    D, dtb = torch.ones(H, device=device), torch.zeros(H, device=device)
+    step = lambda l: ops.mamba2_ssd_step(ssm[l], xbc, zx, 2 * Di + 2 * N, A, D, dtb, 1)
+    for l in range(layers):
+        step(l)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        for l in range(layers):
+            step(l)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / (reps * layers) * 1e3
+    nbytes = 2 * rows * H * P * N * 2
+    return {"workload": f"Mamba2 SSD state update, {rows} rows x 64 heads x 64 x 128 bf16 state, one layer per launch",
+            "kernel": "mamba2_ssd_step_p64_kernel", "us_per_layer": round(us, 2), "bytes_per_layer": nbytes, "bound": "hbm",
+            "achieved_gbs": round(nbytes / us / 1e3, 1), "hbm_frac": round(nbytes / us / 1e3 / hbm_peak, 4),
+            "launches": layers * reps, "finite": bool(torch.isfinite(ssm[0].float()).all())}
+
+
 def latency_batch1(model, shape, args, device, hbm_peak):
     """BASELINE configs[1]: batch 1, L_cond 23, greedy, 30 s: per-frame latency of the graph-replayed decode step."""
     from zonos_b200 import synth
@@ -418,6 +451,8 @@ def main_b200(args, world, rank, local):
     torch.cuda.empty_cache()
     if world == 1 and not args.no_dac:
         line["dac_decode"] = dac_section(device, B, args.max_new_tokens)
+    if world == 1 and not args.no_mamba:
+        line["mamba2_ssd_step"] = mamba2_section(device, hbm_peak)
         torch.cuda.empty_cache()
         # SURVEY 8(d) metric (i), second form: codes -> waveform included.  The two stages run back to back on the same
         # GPU, so the pipeline rate is the harmonic composition of the two end-to-end rates measured above.
