@@ -23,7 +23,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 FRAME_RATE = 44100 / 512  # 86.1328 frames per audio second
 # attn_decode_kernel DRAM traffic per launch measured by ncu: key (sequences incl. CFG, kv heads, context)
-NCU_ATTN_TRAFFIC = {(128, 4, 1432, 1): (390_561_000, "profiles/r01d_ncu_full.txt"),
+NCU_ATTN_TRAFFIC = {(128, 4, 1432, 1): (390_587_000, "profiles/r01f_ncu_full.txt"),
                     (128, 4, 1432, 2): (390_500_000, "profiles/r01b_ncu_full_decode_b64.txt")}
 C3_SAMPLING = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0,
                    repetition_penalty_window=2, temperature=1.0)
