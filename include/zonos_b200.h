@@ -186,6 +186,12 @@ int zb200_mamba2_ssd_scan(void* ssm_state, const void* xbc, int ld_xbc, const vo
 int zb200_mamba2_gated_rmsnorm(const void* y, const void* zxbcdt, int ld, const void* w, void* out, int rows, int d_inner,
                                int n_groups, float eps, void* stream);
 
+/* Block wiring of the hybrid backbone with fused_add_norm (mamba_ssm layer_norm_fn, prenorm=True, residual_in_fp32=True;
+ * _mamba_ssm.py:18-31,46-57): residual fp32 [rows][d] <- x + residual (has_residual = 0: residual <- x), out bf16 =
+ * norm(residual) * w (+ b); rms != 0: RMSNorm, else LayerNorm.  b may be NULL. */
+int zb200_add_norm(const void* x, float* residual, int has_residual, const void* w, const void* b, void* out, int rows,
+                   int d, float eps, int rms, void* stream);
+
 /* ---- DACAutoencoder.decode (zonos/autoencoder.py:44-47 -> transformers DacModel.decode, modeling_dac.py:608-638) ---
  * The decoder is described as a list of implicit-GEMM layers over five caller-owned fp16 work regions (channels-last
  * [batch][time][pitch]); the host shim (zonos_b200/dac.py) builds the list from the HF state dict once. */

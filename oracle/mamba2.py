@@ -104,3 +104,30 @@ def synth_mixer_params(d_model=256, expand=2, head_dim=64, d_state=128, n_groups
                       d_model=d_model, d_conv=d_conv),
     }
     return p
+
+
+def add_norm(x, residual, weight, bias, eps, rms):
+    """mamba_ssm layer_norm_fn(prenorm=True, residual_in_fp32=True) as the hybrid blocks call it (fused_add_norm,
+    zonos/backbone/_mamba_ssm.py:18-31,46-57): residual <- x + residual in fp32, y = norm(residual) * w (+ b) in x's dtype."""
+    r = x.float() if residual is None else x.float() + residual.float()
+    if rms:
+        y = r * torch.rsqrt(r.pow(2).mean(-1, keepdim=True) + eps) * weight.float()
+    else:
+        mu = r.mean(-1, keepdim=True)
+        y = (r - mu) * torch.rsqrt((r - mu).pow(2).mean(-1, keepdim=True) + eps) * weight.float()
+    if bias is not None:
+        y = y + bias.float()
+    return y.to(x.dtype), r
+
+
+def stack_step(layers, norm_f, states, u, rms=True, eps=1e-5, storage_dtype=torch.bfloat16):
+    """One token through a stack of Mamba2 blocks wired like mamba_ssm's Block with fused_add_norm and an fp32 residual
+    (zonos/backbone/_mamba_ssm.py:18-31,46-57): (hidden, residual) -> add + norm -> mixer; finally add + norm_f."""
+    residual, hidden = None, u.to(storage_dtype)
+    for p, st in zip(layers, states):
+        hn, residual = add_norm(hidden, residual, p["norm.weight"], p.get("norm.bias"), eps, rms)
+        q = dict(p)
+        q["norm.weight"] = p["mixer_norm.weight"]
+        hidden = mixer_step(q, st, hn.float(), storage_dtype=storage_dtype).to(storage_dtype)
+    out, _ = add_norm(hidden, residual, norm_f["weight"], norm_f.get("bias"), eps, rms)
+    return out

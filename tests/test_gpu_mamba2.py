@@ -124,3 +124,61 @@ def test_mamba2_prefill_scan_then_decode_steps(n_groups, head_dim):
         assert _rel_rms(y1.cpu(), y_ref[:, S + i]) < 6e-3, i
     assert torch.equal(conv_d.cpu(), st["conv"])
     assert _rel_rms(ssm_d.cpu(), st["ssm"]) < 6e-3
+
+
+@pytest.mark.parametrize("rms", [True, False])
+@pytest.mark.parametrize("d", [256, 2048])
+def test_add_norm_vs_oracle(rms, d):
+    """Fused residual add + norm of the hybrid blocks: the fp32 residual stream must be exact, the normed rows within bf16."""
+    from zonos_b200 import ops
+
+    g = torch.Generator().manual_seed(3)
+    rows = 7
+    w, b = (1 + 0.1 * torch.randn(d, generator=g)).to(BF), (0.1 * torch.randn(d, generator=g)).to(BF)
+    x0, x1 = torch.randn(rows, d, generator=g).to(BF), torch.randn(rows, d, generator=g).to(BF)
+    y_ref0, r_ref = om.add_norm(x0, None, w, None if rms else b, 1e-5, rms)
+    y0, r = ops.add_norm(x0.cuda(), None, w.cuda(), None if rms else b.cuda(), 1e-5, rms)
+    assert torch.equal(r.cpu(), r_ref)
+    assert _rel_rms(y0.cpu(), y_ref0) < 3e-3
+    y_ref1, r_ref = om.add_norm(x1, r_ref, w, None if rms else b, 1e-5, rms)
+    y1, r = ops.add_norm(x1.cuda(), r, w.cuda(), None if rms else b.cuda(), 1e-5, rms)
+    assert torch.equal(r.cpu(), r_ref), "x + residual in fp32 is exact"
+    assert _rel_rms(y1.cpu(), y_ref1) < 3e-3
+
+
+def test_mamba2_layer_stack_prefill_then_decode_vs_oracle():
+    """Three Mamba2 blocks wired like the hybrid backbone (fused add + RMSNorm with an fp32 residual, final norm_f),
+    sequenced on the host over the C-ABI kernels: prefill of 21 tokens, then 4 decode steps, vs the oracle stepping token
+    by token.  Free-running (each implementation carries its own states)."""
+    from zonos_b200.hybrid import Mamba2StackB200
+
+    n_layers, n_seq, S, steps, d = 3, 2, 21, 4, 256
+    layers = []
+    for l in range(n_layers):
+        p = om.synth_mixer_params(d_model=d, seed=20 + l, dtype=BF)
+        p["mixer_norm.weight"] = p.pop("norm.weight")
+        p["norm.weight"] = (1 + 0.1 * torch.randn(d, generator=torch.Generator().manual_seed(40 + l))).to(BF)
+        layers.append(p)
+    norm_f = dict(weight=(1 + 0.1 * torch.randn(d, generator=torch.Generator().manual_seed(50))).to(BF))
+    shape = layers[0]["shape"]
+    stack = Mamba2StackB200(layers, norm_f, shape, "cuda")
+    g = torch.Generator().manual_seed(6)
+    u = torch.randn(n_seq, S + steps, d, generator=g).to(BF)
+    # oracle: token by token (fp32 SSM state during the prefix like a scan kernel, bf16 once stored)
+    st_ref = [om.new_state(p, n_seq, conv_dtype=BF, ssm_dtype=torch.float32) for p in layers]
+    ref = []
+    for t in range(S + steps):
+        if t == S:
+            for st in st_ref:
+                st["ssm"] = st["ssm"].to(BF)
+        ref.append(om.stack_step(layers, norm_f, st_ref, u[:, t]))
+    ref = torch.stack(ref, 1)
+    states = stack.allocate_inference_cache(n_seq)
+    pre = stack.prefill(u[:, :S].reshape(n_seq * S, d).contiguous().cuda(), states, S).cpu().view(n_seq, S, d)
+    assert _rel_rms(pre, ref[:, :S]) < 1.5e-2, _rel_rms(pre, ref[:, :S])
+    for i in range(steps):
+        out = stack.step(u[:, S + i].contiguous().cuda(), states).cpu()
+        assert torch.isfinite(out).all()
+        assert _rel_rms(out, ref[:, S + i]) < 1.5e-2, (i, _rel_rms(out, ref[:, S + i]))
+    for st, sr in zip(states, st_ref):
+        assert _rel_rms(st["ssm"].cpu(), sr["ssm"]) < 1.5e-2

@@ -398,6 +398,92 @@ __global__ void __launch_bounds__(256) mamba2_gated_rmsnorm_kernel(const bf16* _
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------- fused add + norm (prenorm)
+// mamba_ssm Block with fused_add_norm (layer_norm_fn, prenorm=True, residual_in_fp32=True; _mamba_ssm.py:18-31,46-57):
+//   residual <- x + residual (fp32, written back; residual = x for the first layer),  out = norm(residual) * w (+ b)  in bf16
+// rms != 0: RMSNorm (no mean subtraction, bias optional), else LayerNorm.  One CTA per row, fp32 statistics.
+__global__ void __launch_bounds__(256) add_norm_kernel(const bf16* __restrict__ x, float* __restrict__ residual, int has_residual,
+                                                       const bf16* __restrict__ w, const bf16* __restrict__ b,
+                                                       bf16* __restrict__ out, int d, float eps, int rms) {
+  pdl_launch_dependents();
+  __shared__ float red[8];
+  __shared__ float bcast;
+  const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int MAXV = 4;  // d <= 8192
+  uint4 wu[MAXV], bu[MAXV];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 256 + tid) * 8;
+    if (c < d) {
+      wu[i] = __ldg(reinterpret_cast<const uint4*>(w + c));
+      bu[i] = b ? __ldg(reinterpret_cast<const uint4*>(b + c)) : make_uint4(0, 0, 0, 0);
+    }
+  }
+  pdl_wait_prior();
+  float v[MAXV][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 256 + tid) * 8;
+    if (c < d) {
+      const uint4 xu = *reinterpret_cast<const uint4*>(x + (size_t)row * d + c);
+      const uint32_t xw[4] = {xu.x, xu.y, xu.z, xu.w};
+      float4* rp = reinterpret_cast<float4*>(residual + (size_t)row * d + c);
+      float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0;
+      if (has_residual) r0 = rp[0], r1 = rp[1];
+      const float rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 x2 = unpack_bf16x2(xw[j]);
+        v[i][2 * j] = x2.x + rr[2 * j], v[i][2 * j + 1] = x2.y + rr[2 * j + 1];
+        sum += v[i][2 * j] + v[i][2 * j + 1];
+      }
+      rp[0] = make_float4(v[i][0], v[i][1], v[i][2], v[i][3]);
+      rp[1] = make_float4(v[i][4], v[i][5], v[i][6], v[i][7]);
+    }
+  }
+  auto block_sum = [&](float t) {
+    t = warp_sum(t);
+    __syncthreads();
+    if (lane == 0) red[warp] = t;
+    __syncthreads();
+    if (tid == 0) {
+      float a = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a += red[k];
+      bcast = a;
+    }
+    __syncthreads();
+    return bcast;
+  };
+  const float mean = rms ? 0.f : block_sum(sum) / (float)d;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i)
+    if ((i * 256 + tid) * 8 < d)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float t = v[i][j] - mean;
+        sq += t * t;
+      }
+  const float rstd = 1.0f / sqrtf(block_sum(sq) / (float)d + eps);
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 256 + tid) * 8;
+    if (c < d) {
+      const uint32_t ww[4] = {wu[i].x, wu[i].y, wu[i].z, wu[i].w}, bw[4] = {bu[i].x, bu[i].y, bu[i].z, bu[i].w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 w2 = unpack_bf16x2(ww[j]), b2 = unpack_bf16x2(bw[j]);
+        o[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * w2.x + b2.x, (v[i][2 * j + 1] - mean) * rstd * w2.y + b2.y);
+      }
+      *reinterpret_cast<uint4*>(out + (size_t)row * d + c) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
 }  // namespace zb
 
 using namespace zb;
@@ -477,5 +563,14 @@ extern "C" int zb200_mamba2_ssd_scan(void* ssm_state, const void* xbc, int ld_xb
       (bf16*)ssm_state, (const bf16*)xbc, ld_xbc, (const bf16*)zxbcdt, ld, dt_col0, A_log, D, dt_bias, (bf16*)y, seq_len, n_heads,
       head_dim, n_groups, use_initial_state);
   ZB_CHECK_LAUNCH("mamba2_ssd_scan_kernel");
+  return ZB200_OK;
+}
+
+extern "C" int zb200_add_norm(const void* x, float* residual, int has_residual, const void* w, const void* b, void* out, int rows,
+                              int d, float eps, int rms, void* stream) {
+  ZB_REQUIRE(x && residual && w && out && rows > 0, "add_norm: bad arguments");
+  ZB_REQUIRE(d > 0 && d % 8 == 0 && d <= 8192, "add_norm: d=%d must be a multiple of 8 (<= 8192)", d);
+  ZB_CHECK_CUDA(launch_pdl(add_norm_kernel, dim3((unsigned)rows), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(), (const bf16*)x,
+                           residual, has_residual, (const bf16*)w, (const bf16*)b, (bf16*)out, d, eps, rms));
   return ZB200_OK;
 }

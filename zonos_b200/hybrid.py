@@ -1,0 +1,78 @@
+"""Hybrid backbone, first slice: the Mamba2 layers of `MambaSSMZonosBackbone`
+(zonos/backbone/_mamba_ssm.py:9-57) sequenced on the host over the C-ABI kernels of csrc/mamba2.cu and the tcgen05 GEMMs.
+
+Per layer (mamba_ssm Block with fused_add_norm, residual_in_fp32):  (hidden, residual) -> add + norm -> Mamba2 mixer
+(in_proj -> conv -> SSD -> gated RMSNorm -> out_proj); after the last layer add + norm_f.  States are what
+`allocate_inference_cache` (_mamba_ssm.py:37-41) returns: conv [rows, C, 4] and SSM [rows, H, P, N] per layer, bf16.
+
+Not here yet: the attention layers of the hybrid (`attn_layer_idx`), GatedMLP, a C-side engine with its own CUDA graph
+(`step()` is capturable with `torch.cuda.graph`: it allocates through torch and never synchronises), `generate`.
+There is no CPU fallback: every operation is a kernel of libzonos_b200.so.
+"""
+import torch
+
+from . import ops
+
+
+class Mamba2StackB200:
+    def __init__(self, layers, norm_f, shape, device, rms_norm=True, eps=1e-5):
+        """layers: list of dicts with norm.weight (+ norm.bias), in_proj.weight, conv1d.weight, conv1d.bias, dt_bias, A_log,
+        D, mixer_norm.weight, out_proj.weight; norm_f: dict(weight, bias or None); shape: d_model, d_inner, n_heads,
+        head_dim, d_state, n_groups."""
+        self.device = torch.device(device)
+        self.s, self.rms, self.eps = dict(shape), bool(rms_norm), float(eps)
+        bf = lambda t: None if t is None else t.detach().to(self.device, torch.bfloat16).contiguous()
+        f32 = lambda t: t.detach().to(self.device, torch.float32).contiguous()
+        self.layers = []
+        for p in layers:
+            self.layers.append(dict(
+                nw=bf(p["norm.weight"]), nb=bf(p.get("norm.bias")),
+                w_in=ops.pack_weight(bf(p["in_proj.weight"])), w_out=ops.pack_weight(bf(p["out_proj.weight"])),
+                cw=bf(p["conv1d.weight"]), cb=bf(p.get("conv1d.bias")), dtb=f32(p["dt_bias"]), A=f32(p["A_log"]), D=f32(p["D"]),
+                gw=bf(p["mixer_norm.weight"])))
+        self.fw, self.fb = bf(norm_f["weight"]), bf(norm_f.get("bias"))
+        s = self.s
+        self.n_in = 2 * s["d_inner"] + 2 * s["n_groups"] * s["d_state"] + s["n_heads"]
+        self.conv_dim = s["d_inner"] + 2 * s["n_groups"] * s["d_state"]
+        self._ws = self._tickets = None
+
+    def allocate_inference_cache(self, rows):
+        s = self.s
+        return [dict(conv=torch.zeros(rows, self.conv_dim, 4, dtype=torch.bfloat16, device=self.device),
+                     ssm=torch.zeros(rows, s["n_heads"], s["head_dim"], s["d_state"], dtype=torch.bfloat16, device=self.device))
+                for _ in self.layers]
+
+    def _gemm(self, a, w, n):
+        if a.shape[0] <= 128:  # decode: weight-streaming stream-K kernel
+            if self._ws is None:
+                self._ws = torch.empty(148 * 32768, dtype=torch.float32, device=self.device)
+                self._tickets = torch.zeros(1024, dtype=torch.int32, device=self.device)
+            return ops.gemm_skinny_bf16(a, w, n, 148, self._ws, self._tickets)
+        return ops.gemm_bf16(a, w, n)
+
+    def _forward(self, x, states, seq_len):
+        s = self.s
+        Di, G, N = s["d_inner"], s["n_groups"], s["d_state"]
+        residual, hidden = None, x
+        for L, st in zip(self.layers, states):
+            hn, residual = ops.add_norm(hidden, residual, L["nw"], L["nb"], self.eps, self.rms)
+            zx = self._gemm(hn, L["w_in"], self.n_in)
+            if seq_len is None:
+                xbc = ops.mamba2_conv_update(st["conv"], zx, Di, L["cw"], L["cb"])
+                y = ops.mamba2_ssd_step(st["ssm"], xbc, zx, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G)
+            else:
+                xbc = ops.mamba2_conv_seq(st["conv"], zx, seq_len, Di, L["cw"], L["cb"])
+                y = ops.mamba2_ssd_scan(st["ssm"], xbc, zx, seq_len, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G)
+            yn = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
+            hidden = self._gemm(yn, L["w_out"], s["d_model"])
+        out, _ = ops.add_norm(hidden, residual, self.fw, self.fb, self.eps, self.rms)
+        return out
+
+    def prefill(self, x, states, seq_len):
+        """x bf16 [n_seq*seq_len, d_model] (sequence-major) -> norm_f output for every row; states receive the final
+        conv windows / SSM states."""
+        return self._forward(x, states, seq_len)
+
+    def step(self, x, states):
+        """One token per sequence: x bf16 [rows, d_model] -> norm_f output [rows, d_model]; states updated in place."""
+        return self._forward(x, states, None)

@@ -261,3 +261,19 @@ def mamba2_ssd_scan(ssm_state: torch.Tensor, xbc: torch.Tensor, zxbcdt: torch.Te
                                       ptr(b), ptr(y), n_seq, seq_len, H, P, N, n_groups, int(use_initial_state), stream_ptr()),
           "mamba2_ssd_scan")
     return y
+
+
+def add_norm(x: torch.Tensor, residual, w: torch.Tensor, b, eps: float, rms: bool):
+    """Fused residual add + (RMS|Layer)Norm of the hybrid blocks (fp32 residual stream).  x bf16 [rows, d]; residual fp32
+    [rows, d] updated in place, or None for the first layer.  Returns (normed bf16, residual fp32)."""
+    x = _cuda(x, torch.bfloat16)
+    rows, d = x.shape
+    has = residual is not None
+    if not has:
+        residual = torch.empty(rows, d, dtype=torch.float32, device=x.device)
+    assert residual.dtype == torch.float32 and residual.is_contiguous()
+    out = torch.empty_like(x)
+    check(lib().zb200_add_norm(ptr(x), ptr(residual), int(has), ptr(_cuda(w, torch.bfloat16)),
+                               ptr(None if b is None else _cuda(b, torch.bfloat16)), ptr(out), rows, d, ctypes.c_float(eps),
+                               int(rms), stream_ptr()), "add_norm")
+    return out, residual
