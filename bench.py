@@ -244,36 +244,76 @@ def dac_section(device, batch, frames):
             "launches": 31 * reps * 2, "finite": bool(torch.isfinite(wav_host).all())}
 
 
-def mamba2_section(device, hbm_peak, rows=64, layers=24):
-    """First slice of BASELINE configs[4] (hybrid, batch 32 per GPU = 64 rows with CFG): the Mamba2 SSD state update of the
-    decode step alone, at the hybrid's mixer shape, over `layers` distinct states (3.2 GB: nothing stays in L2)."""
+def mamba2_section(device, hbm_peak, rows=64, n_layers=40):
+    """First slice of BASELINE configs[4] (hybrid, batch 32 per GPU = 64 rows with CFG) at the hybrid's mixer shape
+    (d_model 2048, d_inner 4096, 64 heads x 64, d_state 128): (1) the SSD state update alone over distinct layer states
+    (nothing stays in L2); (2) the decode step of a stack of Mamba2 blocks (fused add + norm, in_proj, conv, SSD, gated
+    norm, out_proj), host-sequenced C-ABI kernels replayed from a torch CUDA graph.  Attention layers / engine: not yet."""
+    from oracle import mamba2 as om  # synthetic parameters only (the stack under test is the CUDA one)
+    from zonos_b200.hybrid import Mamba2StackB200
+
+    d = 2048
+    base = om.synth_mixer_params(d_model=d, seed=0, dtype=torch.bfloat16)
+    s = base["shape"]
+    layers = []
+    for _ in range(n_layers):  # distinct tensors per layer: the HBM traffic must be real
+        p = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in base.items()}
+        p["mixer_norm.weight"] = p.pop("norm.weight")
+        p["norm.weight"] = torch.ones(d, dtype=torch.bfloat16)
+        layers.append(p)
+    stack = Mamba2StackB200(layers, dict(weight=torch.ones(d, dtype=torch.bfloat16)), s, device)
+    states = stack.allocate_inference_cache(rows)
+    x = torch.randn(rows, d, device=device).bfloat16()
     from zonos_b200 import ops
 
-    H, P, N, Di = 64, 64, 128, 4096
-    g = torch.Generator(device=device).manual_seed(9)
-    ssm = [(0.1 * torch.randn(rows, H, P, N, generator=g, device=device)).bfloat16() for _ in range(layers)]
-    xbc = torch.randn(rows, Di + 2 * N, generator=g, device=device).bfloat16()
-    zx = torch.randn(rows, 2 * Di + 2 * N + H, generator=g, device=device).bfloat16()
-    A = torch.rand(H, generator=g, device=device).float()
-    D, dtb = torch.ones(H, device=device), torch.zeros(H, device=device)
-    step = lambda l: ops.mamba2_ssd_step(ssm[l], xbc, zx, 2 * Di + 2 * N, A, D, dtb, 1)
-    for l in range(layers):
-        step(l)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 5
-    e0.record()
-    for _ in range(reps):
-        for l in range(layers):
-            step(l)
-    e1.record()
-    torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) / (reps * layers) * 1e3
-    nbytes = 2 * rows * H * P * N * 2
-    return {"workload": f"Mamba2 SSD state update, {rows} rows x 64 heads x 64 x 128 bf16 state, one layer per launch",
-            "kernel": "mamba2_ssd_step_p64_kernel", "us_per_layer": round(us, 2), "bytes_per_layer": nbytes, "bound": "hbm",
-            "achieved_gbs": round(nbytes / us / 1e3, 1), "hbm_frac": round(nbytes / us / 1e3 / hbm_peak, 4),
-            "launches": layers * reps, "finite": bool(torch.isfinite(ssm[0].float()).all())}
+    Di, N, H = s["d_inner"], s["d_state"], s["n_heads"]
+    xbc = torch.randn(rows, Di + 2 * N, device=device).bfloat16()
+    zx = torch.randn(rows, 2 * Di + 2 * N + H, device=device).bfloat16()
+    L0 = stack.layers[0]
+    ssd = lambda l: ops.mamba2_ssd_step(states[l]["ssm"], xbc, zx, 2 * Di + 2 * N, L0["A"], L0["D"], L0["dtb"], 1)
+    side = torch.cuda.Stream(device=device)
+    with torch.cuda.stream(side):
+        for l in range(n_layers):
+            ssd(l)
+        side.synchronize()
+        e0, e1, e2, e3 = (torch.cuda.Event(enable_timing=True) for _ in range(4))
+        reps = 5
+        e0.record(side)
+        for _ in range(reps):
+            for l in range(n_layers):
+                ssd(l)
+        e1.record(side)
+        for st in states:
+            st["ssm"].zero_()
+        for _ in range(3):
+            out = stack.step(x, states)
+        side.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            out = stack.step(x, states)
+        for _ in range(5):
+            graph.replay()
+        n = 30
+        e2.record(side)
+        for _ in range(n):
+            graph.replay()
+        e3.record(side)
+        side.synchronize()
+    us = e0.elapsed_time(e1) / (reps * n_layers) * 1e3
+    ms_step = e2.elapsed_time(e3) / n
+    st_bytes = 2 * rows * H * s["head_dim"] * N * 2
+    w_bytes = (stack.n_in * d + d * Di) * 2
+    algo = n_layers * (w_bytes + st_bytes)
+    res = {"workload": f"hybrid first slice: {n_layers} Mamba2 blocks, {rows} rows (batch 32 x CFG), d_model 2048, state 64 x 64 x 128 bf16",
+           "ssd_step": {"kernel": "mamba2_ssd_step_p64_kernel", "us_per_layer": round(us, 2), "bytes_per_layer": st_bytes,
+                        "bound": "hbm", "achieved_gbs": round(st_bytes / us / 1e3, 1), "hbm_frac": round(st_bytes / us / 1e3 / hbm_peak, 4)},
+           "stack_decode_step": {"ms_per_step": round(ms_step, 3), "us_per_layer": round(ms_step / n_layers * 1e3, 1),
+                                 "launches_per_step": 6 * n_layers + 1, "algorithmic_bytes": algo, "bound": "hbm",
+                                 "hbm_frac": round(algo / (ms_step * 1e-3) / 1e9 / hbm_peak, 4),
+                                 "note": "host-sequenced kernels in a torch CUDA graph; attention layers and the C-side engine are not built yet"},
+           "finite": bool(torch.isfinite(out).all())}
+    del stack, states, graph
+    return res
 
 
 def latency_batch1(model, shape, args, device, hbm_peak):
@@ -452,7 +492,7 @@ def main_b200(args, world, rank, local):
     if world == 1 and not args.no_dac:
         line["dac_decode"] = dac_section(device, B, args.max_new_tokens)
     if world == 1 and not args.no_mamba:
-        line["mamba2_ssd_step"] = mamba2_section(device, hbm_peak)
+        line["hybrid_mamba2"] = mamba2_section(device, hbm_peak)
         torch.cuda.empty_cache()
         # SURVEY 8(d) metric (i), second form: codes -> waveform included.  The two stages run back to back on the same
         # GPU, so the pipeline rate is the harmonic composition of the two end-to-end rates measured above.
