@@ -192,6 +192,14 @@ int zb200_mamba2_gated_rmsnorm(const void* y, const void* zxbcdt, int ld, const 
 int zb200_add_norm(const void* x, float* residual, int has_residual, const void* w, const void* b, void* out, int rows,
                    int d, float eps, int rms, void* stream);
 
+/* Hybrid attention layers (mamba_ssm MHA; _mamba_ssm.py:18-31 with attn_layer_idx / attn_cfg): splits the Wqkv output
+ * [rows][(H + 2*Hkv)*128] into q [rows][H*128], k and v [rows][Hkv*128] and applies the non-interleaved rotary embedding
+ * (pairs (i, i+64), cos / sin rounded to bf16) at position pos0 + (row % seq_len); inv_freq fp32 [64]. */
+int zb200_rope_split(const void* qkv, const float* inv_freq, void* q, void* k, void* v, int rows, int seq_len, int pos0,
+                     int n_heads, int n_kv_heads, void* stream);
+/* mamba_ssm GatedMLP activation: fc1_out bf16 [rows][2*d_ff] -> out[r][c] = fc1_out[r][c] * silu(fc1_out[r][d_ff + c]). */
+int zb200_gated_mlp_act(const void* fc1_out, void* out, int rows, int d_ff, void* stream);
+
 /* ---- DACAutoencoder.decode (zonos/autoencoder.py:44-47 -> transformers DacModel.decode, modeling_dac.py:608-638) ---
  * The decoder is described as a list of implicit-GEMM layers over five caller-owned fp16 work regions (channels-last
  * [batch][time][pitch]); the host shim (zonos_b200/dac.py) builds the list from the HF state dict once. */

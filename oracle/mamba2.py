@@ -131,3 +131,50 @@ def stack_step(layers, norm_f, states, u, rms=True, eps=1e-5, storage_dtype=torc
         hidden = mixer_step(q, st, hn.float(), storage_dtype=storage_dtype).to(storage_dtype)
     out, _ = add_norm(hidden, residual, norm_f["weight"], norm_f.get("bias"), eps, rms)
     return out
+
+
+def rope_half(x, pos, base=10000.0):
+    """Non-interleaved rotary embedding (flash-attn RotaryEmbedding, interleaved=False, as mamba_ssm's MHA uses it;
+    recalled: the package is absent): x [B, S, H, D], pairs (i, i + D/2), cos / sin cached in x's dtype, fp32 math."""
+    D = x.shape[-1]
+    inv = 1.0 / (base ** (torch.arange(0, D, 2, dtype=torch.float32) / D))
+    ang = torch.outer(pos.float(), inv)                               # [S, D/2]
+    c, sn = torch.cos(ang).to(x.dtype).float(), torch.sin(ang).to(x.dtype).float()
+    x1, x2 = x.float()[..., : D // 2], x.float()[..., D // 2:]
+    c, sn = c[None, :, None, :], sn[None, :, None, :]
+    return torch.cat([x1 * c - x2 * sn, x1 * sn + x2 * c], dim=-1).to(x.dtype)
+
+
+def hybrid_forward(layers, norm_f, u, n_heads, n_kv_heads, rms=True, eps=1e-5, dt=torch.bfloat16):
+    """`MambaSSMZonosBackbone.forward` (zonos/backbone/_mamba_ssm.py:46-57) over whole sequences u [B, T, d]: mamba_ssm
+    Blocks with fused add + norm and an fp32 residual; "mamba2" layers run the mixer token by token from a zero state,
+    "attn" layers are mamba_ssm MHA (Wqkv = [q | k | v], non-interleaved rotary, causal GQA softmax(qk/sqrt(D))v) followed by
+    the GatedMLP (y, gate = fc1(x).chunk(2); fc2(y * silu(gate))) behind norm2.  bf16 at every stored activation."""
+    B, T, d = u.shape
+    lin = lambda x, w: (x.float() @ w.float().t()).to(dt)
+    residual, hidden = None, u.to(dt)
+    for p in layers:
+        hn, residual = add_norm(hidden, residual, p["norm.weight"], p.get("norm.bias"), eps, rms)
+        if p["kind"] == "mamba2":
+            q = dict(p)
+            q["norm.weight"] = p["mixer_norm.weight"]
+            st = new_state(p, B, conv_dtype=dt, ssm_dtype=torch.float32)
+            hidden = torch.stack([mixer_step(q, st, hn[:, t].float(), storage_dtype=dt).to(dt) for t in range(T)], 1)
+        else:
+            D = 128
+            qkv = lin(hn, p["in_proj.weight"])
+            qh, kh, vh = qkv.split([n_heads * D, n_kv_heads * D, n_kv_heads * D], dim=-1)
+            pos = torch.arange(T)
+            qh = rope_half(qh.view(B, T, n_heads, D), pos).transpose(1, 2).float()
+            kh = rope_half(kh.view(B, T, n_kv_heads, D), pos).transpose(1, 2).float()
+            vh = vh.view(B, T, n_kv_heads, D).transpose(1, 2).float()
+            rep = n_heads // n_kv_heads
+            kh, vh = kh.repeat_interleave(rep, dim=1), vh.repeat_interleave(rep, dim=1)
+            att = F.scaled_dot_product_attention(qh, kh, vh, is_causal=True).transpose(1, 2).reshape(B, T, n_heads * D).to(dt)
+            hidden = lin(att, p["out_proj.weight"])
+        if "fc1.weight" in p:
+            hn2, residual = add_norm(hidden, residual, p["norm2.weight"], p.get("norm2.bias"), eps, rms)
+            y, gate = lin(hn2, p["fc1.weight"]).float().chunk(2, dim=-1)
+            hidden = lin((y * F.silu(gate)).to(dt), p["fc2.weight"])
+    out, _ = add_norm(hidden, residual, norm_f["weight"], norm_f.get("bias"), eps, rms)
+    return out

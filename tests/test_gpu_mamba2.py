@@ -182,3 +182,42 @@ def test_mamba2_layer_stack_prefill_then_decode_vs_oracle():
         assert _rel_rms(out, ref[:, S + i]) < 1.5e-2, (i, _rel_rms(out, ref[:, S + i]))
     for st, sr in zip(states, st_ref):
         assert _rel_rms(st["ssm"].cpu(), sr["ssm"]) < 1.5e-2
+
+
+def test_hybrid_backbone_prefill_then_decode_vs_oracle():
+    """A small hybrid backbone wired like MambaSSMZonosBackbone -- [Mamba2, attention + GatedMLP, Mamba2, attention + GatedMLP]
+    -- on the B200 kernels: prefill of 70 tokens (more than one KV page), then 5 decode steps, against the oracle run
+    over the whole sequence."""
+    from zonos_b200.hybrid import HybridBackboneB200
+
+    d, H, Hkv, F_ = 256, 2, 1, 512
+    n_seq, S, steps = 2, 70, 5
+    g = torch.Generator().manual_seed(12)
+    r = lambda *sh: torch.randn(*sh, generator=g)
+    layers = []
+    for l, kind in enumerate(["mamba2", "attn", "mamba2", "attn"]):
+        if kind == "mamba2":
+            p = om.synth_mixer_params(d_model=d, seed=30 + l, dtype=BF)
+            p["mixer_norm.weight"] = p.pop("norm.weight")
+        else:
+            p = {"in_proj.weight": (r((H + 2 * Hkv) * 128, d) / d ** 0.5).to(BF), "out_proj.weight": (r(d, H * 128) / (H * 128) ** 0.5).to(BF),
+                 "norm2.weight": (1 + 0.1 * r(d)).to(BF), "fc1.weight": (r(2 * F_, d) / d ** 0.5).to(BF),
+                 "fc2.weight": (r(d, F_) / F_ ** 0.5).to(BF)}
+        p["kind"] = kind
+        p["norm.weight"] = (1 + 0.1 * r(d)).to(BF)
+        layers.append(p)
+    norm_f = dict(weight=(1 + 0.1 * r(d)).to(BF))
+    shape = layers[0]["shape"]
+    u = r(n_seq, S + steps, d).to(BF)
+    ref = om.hybrid_forward(layers, norm_f, u, H, Hkv)
+    net = HybridBackboneB200(layers, norm_f, shape, "cuda", H, Hkv)
+    cache = net.allocate_inference_cache(n_seq, S + steps + 3)
+    pre = net.forward(u[:, :S].reshape(n_seq * S, d).contiguous().cuda(), cache, S).cpu().view(n_seq, S, d)
+    assert _rel_rms(pre, ref[:, :S]) < 2e-2, _rel_rms(pre, ref[:, :S])
+    for i in range(steps):
+        out = net.forward(u[:, S + i].contiguous().cuda(), cache, 1).cpu()
+        assert torch.isfinite(out).all()
+        assert _rel_rms(out, ref[:, S + i]) < 2e-2, (i, _rel_rms(out, ref[:, S + i]))
+    assert cache["seqlen_offset"] == S + steps
+    with pytest.raises(AssertionError):
+        net.forward(u[:, :4].reshape(n_seq * 4, d).contiguous().cuda(), cache, 4)  # KV cache overflow, as _torch.py:44-45

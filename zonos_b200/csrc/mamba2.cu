@@ -484,6 +484,50 @@ __global__ void __launch_bounds__(256) add_norm_kernel(const bf16* __restrict__ 
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------- hybrid attention / MLP glue
+// The hybrid's attention layers are mamba_ssm MHA modules: Wqkv output [q (H*128) | k (Hkv*128) | v (Hkv*128)], rotary on
+// q and k in the NON-interleaved form (pairs (i, i + 64) of a head), cos / sin cached in the activation dtype (bf16).
+// This kernel splits a row of the projection into q, k, v and rotates q and k at position pos0 + (row % seq_len); the
+// paged-KV write and the attention itself are the transformer path's kernels.  (In a C-side engine this is one more
+// epilogue of the in_proj GEMM, or -- with the q/k weight rows permuted at pack time -- the existing interleaved one.)
+__global__ void __launch_bounds__(256) rope_split_kernel(const bf16* __restrict__ qkv, const float* __restrict__ inv_freq,
+                                                         bf16* __restrict__ q, bf16* __restrict__ k, bf16* __restrict__ v,
+                                                         int seq_len, int pos0, int n_heads, int n_kv_heads) {
+  pdl_launch_dependents();
+  const int row = blockIdx.x, tid = threadIdx.x;
+  const float pos = (float)(pos0 + row % seq_len);
+  const int ld = (n_heads + 2 * n_kv_heads) * 128;
+  pdl_wait_prior();
+  const bf16* src = qkv + (size_t)row * ld;
+  const int n_rot = (n_heads + n_kv_heads) * 64;  // rotated pairs of the row
+  for (int i = tid; i < n_rot; i += 256) {
+    const int head = i >> 6, j = i & 63;
+    const float ang = pos * inv_freq[j];
+    const float c = bf16_round(cosf(ang)), sn = bf16_round(sinf(ang));
+    const float x1 = __bfloat162float(src[head * 128 + j]), x2 = __bfloat162float(src[head * 128 + j + 64]);
+    const bf16 o1 = __float2bfloat16_rn(x1 * c - x2 * sn), o2 = __float2bfloat16_rn(x1 * sn + x2 * c);
+    bf16* dst = head < n_heads ? q + (size_t)row * n_heads * 128 + head * 128
+                               : k + (size_t)row * n_kv_heads * 128 + (head - n_heads) * 128;
+    dst[j] = o1, dst[j + 64] = o2;
+  }
+  const bf16* vs = src + (n_heads + n_kv_heads) * 128;
+  for (int i = tid; i < n_kv_heads * 128; i += 256) v[(size_t)row * n_kv_heads * 128 + i] = vs[i];
+}
+
+// mamba_ssm GatedMLP between fc1 and fc2: y, gate = fc1(x).chunk(2, -1); out = y * silu(gate)
+__global__ void __launch_bounds__(256) gated_mlp_act_kernel(const bf16* __restrict__ a, bf16* __restrict__ out, int d_ff,
+                                                            long long total) {
+  pdl_launch_dependents();
+  pdl_wait_prior();
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const long long r = i / d_ff;
+    const int c = (int)(i - r * d_ff);
+    const float y = __bfloat162float(a[r * 2 * d_ff + c]), g = __bfloat162float(a[r * 2 * d_ff + d_ff + c]);
+    out[i] = __float2bfloat16_rn(y * (g / (1.f + expf(-g))));
+  }
+}
+
 }  // namespace zb
 
 using namespace zb;
@@ -572,5 +616,24 @@ extern "C" int zb200_add_norm(const void* x, float* residual, int has_residual, 
   ZB_REQUIRE(d > 0 && d % 8 == 0 && d <= 8192, "add_norm: d=%d must be a multiple of 8 (<= 8192)", d);
   ZB_CHECK_CUDA(launch_pdl(add_norm_kernel, dim3((unsigned)rows), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(), (const bf16*)x,
                            residual, has_residual, (const bf16*)w, (const bf16*)b, (bf16*)out, d, eps, rms));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_rope_split(const void* qkv, const float* inv_freq, void* q, void* k, void* v, int rows, int seq_len, int pos0,
+                                int n_heads, int n_kv_heads, void* stream) {
+  ZB_REQUIRE(qkv && inv_freq && q && k && v && rows > 0 && seq_len > 0 && rows % seq_len == 0 && pos0 >= 0 && n_heads > 0 &&
+                 n_kv_heads > 0,
+             "rope_split: bad arguments");
+  ZB_CHECK_CUDA(launch_pdl(rope_split_kernel, dim3((unsigned)rows), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(),
+                           (const bf16*)qkv, inv_freq, (bf16*)q, (bf16*)k, (bf16*)v, seq_len, pos0, n_heads, n_kv_heads));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_gated_mlp_act(const void* fc1_out, void* out, int rows, int d_ff, void* stream) {
+  ZB_REQUIRE(fc1_out && out && rows > 0 && d_ff > 0, "gated_mlp_act: bad arguments");
+  const long long total = (long long)rows * d_ff;
+  const int grid = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  ZB_CHECK_CUDA(launch_pdl(gated_mlp_act_kernel, dim3((unsigned)grid), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(),
+                           (const bf16*)fc1_out, (bf16*)out, d_ff, total));
   return ZB200_OK;
 }

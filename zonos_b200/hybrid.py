@@ -5,8 +5,10 @@ Per layer (mamba_ssm Block with fused_add_norm, residual_in_fp32):  (hidden, res
 (in_proj -> conv -> SSD -> gated RMSNorm -> out_proj); after the last layer add + norm_f.  States are what
 `allocate_inference_cache` (_mamba_ssm.py:37-41) returns: conv [rows, C, 4] and SSM [rows, H, P, N] per layer, bf16.
 
-Not here yet: the attention layers of the hybrid (`attn_layer_idx`), GatedMLP, a C-side engine with its own CUDA graph
-(`step()` is capturable with `torch.cuda.graph`: it allocates through torch and never synchronises), `generate`.
+`Mamba2StackB200` is the Mamba2-only stack (its `step()` is capturable with `torch.cuda.graph`: it allocates through torch
+and never synchronises); `HybridBackboneB200` adds the attention layers (`attn_layer_idx`: mamba_ssm MHA with
+non-interleaved rotary, paged-KV attention of the transformer path) and their GatedMLP, sequenced eagerly with
+host-side positions.  Not here yet: a C-side engine with its own CUDA graph for the hybrid, `generate` on it.
 There is no CPU fallback: every operation is a kernel of libzonos_b200.so.
 """
 import torch
@@ -76,3 +78,89 @@ class Mamba2StackB200:
     def step(self, x, states):
         """One token per sequence: x bf16 [rows, d_model] -> norm_f output [rows, d_model]; states updated in place."""
         return self._forward(x, states, None)
+
+
+class HybridBackboneB200:
+    """`MambaSSMZonosBackbone.forward` (zonos/backbone/_mamba_ssm.py:46-57) on the B200 kernels, host-sequenced.
+
+    layers: list of dicts.  Every layer has kind ("mamba2" | "attn") and norm.weight (+ norm.bias); "mamba2" layers carry the
+    Mamba2StackB200 parameters; "attn" layers carry in_proj.weight [(H + 2*Hkv)*128, d] and out_proj.weight [d, H*128].  A
+    layer with fc1.weight [2F, d] / fc2.weight [d, F] has the GatedMLP behind norm2.weight (+ norm2.bias)."""
+
+    def __init__(self, layers, norm_f, shape, device, n_heads, n_kv_heads, rms_norm=True, eps=1e-5, rope_base=10000.0):
+        self.device = torch.device(device)
+        self.s, self.rms, self.eps = dict(shape), bool(rms_norm), float(eps)
+        self.H, self.Hkv = n_heads, n_kv_heads
+        bf = lambda t: None if t is None else t.detach().to(self.device, torch.bfloat16).contiguous()
+        f32 = lambda t: t.detach().to(self.device, torch.float32).contiguous()
+        self.layers = []
+        for p in layers:
+            L = dict(kind=p["kind"], nw=bf(p["norm.weight"]), nb=bf(p.get("norm.bias")),
+                     w_in=ops.pack_weight(bf(p["in_proj.weight"])), w_out=ops.pack_weight(bf(p["out_proj.weight"])))
+            if p["kind"] == "mamba2":
+                L.update(cw=bf(p["conv1d.weight"]), cb=bf(p.get("conv1d.bias")), dtb=f32(p["dt_bias"]), A=f32(p["A_log"]),
+                         D=f32(p["D"]), gw=bf(p["mixer_norm.weight"]))
+            if "fc1.weight" in p:
+                L.update(n2w=bf(p["norm2.weight"]), n2b=bf(p.get("norm2.bias")), w_fc1=ops.pack_weight(bf(p["fc1.weight"])),
+                         w_fc2=ops.pack_weight(bf(p["fc2.weight"])), d_ff=p["fc2.weight"].shape[1])
+            self.layers.append(L)
+        self.fw, self.fb = bf(norm_f["weight"]), bf(norm_f.get("bias"))
+        s = self.s
+        self.n_in = 2 * s["d_inner"] + 2 * s["n_groups"] * s["d_state"] + s["n_heads"]
+        self.conv_dim = s["d_inner"] + 2 * s["n_groups"] * s["d_state"]
+        self.inv_freq = (1.0 / (rope_base ** (torch.arange(0, 128, 2, dtype=torch.float32) / 128))).to(self.device)
+        self._ws = self._tickets = None
+
+    _gemm = Mamba2StackB200._gemm
+
+    def allocate_inference_cache(self, n_seq, max_seqlen):
+        s = self.s
+        kv = ops.PagedKV(len(self.layers), n_seq, max_seqlen, self.Hkv, self.device)
+        states = []
+        for L in self.layers:
+            if L["kind"] == "mamba2":
+                states.append(dict(conv=torch.zeros(n_seq, self.conv_dim, 4, dtype=torch.bfloat16, device=self.device),
+                                   ssm=torch.zeros(n_seq, s["n_heads"], s["head_dim"], s["d_state"], dtype=torch.bfloat16,
+                                                   device=self.device)))
+            else:
+                states.append(None)
+        return dict(kv=kv, layers=states, seqlen_offset=0, max_seqlen=max_seqlen)
+
+    def forward(self, x, cache, seq_len=1):
+        """x bf16 [n_seq*seq_len, d_model] (sequence-major) at positions cache['seqlen_offset'].. -> norm_f output for every
+        row; the cache advances by seq_len (InferenceParams.seqlen_offset, zonos/config.py:8-25)."""
+        s, pos0 = self.s, cache["seqlen_offset"]
+        Di, G, N = s["d_inner"], s["n_groups"], s["d_state"]
+        n_seq = x.shape[0] // seq_len
+        decode = seq_len == 1 and pos0 > 0
+        if pos0 + seq_len > cache["max_seqlen"]:
+            raise AssertionError(f"sequence length {pos0 + seq_len} exceeds the KV cache ({cache['max_seqlen']})")
+        residual, hidden = None, x
+        for li, (L, st) in enumerate(zip(self.layers, cache["layers"])):
+            hn, residual = ops.add_norm(hidden, residual, L["nw"], L["nb"], self.eps, self.rms)
+            if L["kind"] == "mamba2":
+                zx = self._gemm(hn, L["w_in"], self.n_in)
+                if decode:
+                    xbc = ops.mamba2_conv_update(st["conv"], zx, Di, L["cw"], L["cb"])
+                    y = ops.mamba2_ssd_step(st["ssm"], xbc, zx, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G)
+                else:
+                    xbc = ops.mamba2_conv_seq(st["conv"], zx, seq_len, Di, L["cw"], L["cb"], use_initial_state=pos0 > 0)
+                    y = ops.mamba2_ssd_scan(st["ssm"], xbc, zx, seq_len, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G,
+                                            use_initial_state=pos0 > 0)
+                mixed = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
+            else:
+                qkv = self._gemm(hn, L["w_in"], (self.H + 2 * self.Hkv) * 128)
+                q, k, v = ops.rope_split(qkv, self.inv_freq, seq_len, pos0, self.H, self.Hkv)
+                ops.kv_write(cache["kv"], li, k.view(n_seq, seq_len, self.Hkv, 128), v.view(n_seq, seq_len, self.Hkv, 128), pos0)
+                if decode:
+                    mixed = ops.attn_decode(q, cache["kv"], li, pos0 + 1, self.H)
+                else:
+                    mixed = ops.attn_prefill(q.view(n_seq, seq_len, self.H * 128), cache["kv"], li, pos0, self.H).view(-1, self.H * 128)
+            hidden = self._gemm(mixed, L["w_out"], s["d_model"])
+            if "w_fc1" in L:
+                hn2, residual = ops.add_norm(hidden, residual, L["n2w"], L["n2b"], self.eps, self.rms)
+                h1 = ops.gated_mlp_act(self._gemm(hn2, L["w_fc1"], 2 * L["d_ff"]))
+                hidden = self._gemm(h1, L["w_fc2"], s["d_model"])
+        out, _ = ops.add_norm(hidden, residual, self.fw, self.fb, self.eps, self.rms)
+        cache["seqlen_offset"] = pos0 + seq_len
+        return out

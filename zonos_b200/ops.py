@@ -277,3 +277,26 @@ def add_norm(x: torch.Tensor, residual, w: torch.Tensor, b, eps: float, rms: boo
                                ptr(None if b is None else _cuda(b, torch.bfloat16)), ptr(out), rows, d, ctypes.c_float(eps),
                                int(rms), stream_ptr()), "add_norm")
     return out, residual
+
+
+def rope_split(qkv: torch.Tensor, inv_freq: torch.Tensor, seq_len: int, pos0: int, n_heads: int, n_kv_heads: int):
+    """Hybrid attention layers: Wqkv output bf16 [rows, (H+2Hkv)*128] -> rotated q [rows, H*128], rotated k and v
+    [rows, Hkv*128] (non-interleaved rotary at position pos0 + row % seq_len)."""
+    qkv = _cuda(qkv, torch.bfloat16)
+    rows = qkv.shape[0]
+    assert qkv.shape[1] == (n_heads + 2 * n_kv_heads) * 128
+    q = torch.empty(rows, n_heads * 128, dtype=torch.bfloat16, device=qkv.device)
+    k = torch.empty(rows, n_kv_heads * 128, dtype=torch.bfloat16, device=qkv.device)
+    v = torch.empty_like(k)
+    check(lib().zb200_rope_split(ptr(qkv), ptr(_cuda(inv_freq, torch.float32)), ptr(q), ptr(k), ptr(v), rows, seq_len, pos0,
+                                 n_heads, n_kv_heads, stream_ptr()), "rope_split")
+    return q, k, v
+
+
+def gated_mlp_act(fc1_out: torch.Tensor) -> torch.Tensor:
+    """mamba_ssm GatedMLP: y, gate = fc1_out.chunk(2, -1) -> y * silu(gate)."""
+    fc1_out = _cuda(fc1_out, torch.bfloat16)
+    rows, two_f = fc1_out.shape
+    out = torch.empty(rows, two_f // 2, dtype=torch.bfloat16, device=fc1_out.device)
+    check(lib().zb200_gated_mlp_act(ptr(fc1_out), ptr(out), rows, two_f // 2, stream_ptr()), "gated_mlp_act")
+    return out
