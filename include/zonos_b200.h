@@ -65,6 +65,13 @@ int zb200_gemm_swap_bf16(const void* a, int m, int lda, const void* w_packed, in
  * residual + LayerNorm kernel.  m <= 128, n % 256 == 0 (<= 4096); ws: >= splits*m*n floats. */
 int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_packed, int n, int k, int splits, float* ws,
                         int64_t ws_floats, void* x, const void* ln_w, const void* ln_b, void* xn, float eps, void* stream);
+/* apply_heads + CFG mix of _compute_logits (zonos/model.py:100-116) as one weight-streaming GEMM (the kernel the engine
+ * runs at the end of its step): xn bf16 [2*batch][d] (cond rows, then uncond rows), heads packed with row_mode 2 ->
+ * logits fp32 [batch][n_q][vocab] = uncond + (cond - uncond) * cfg_scale, slots >= 1025 = -inf.  2*batch <= 128;
+ * ws / tickets as zb200_gemm_skinny_bf16. */
+int zb200_heads_cfg(const void* xn, int batch, int d, const void* w_heads_packed, int n_q, int vocab, int head_rows_padded,
+                    float cfg_scale, float* logits, int grid, float* ws, int64_t ws_floats, int* tickets, int n_tickets,
+                    void* stream);
 /* Debug (libraries built with ZB200_TRACE=1 only, ZB200_ERR_STATE otherwise): device_buf uint64 [64][160][12] receives the
  * in-kernel globaltimer timeline of the following zb200_gemm_skinny_bf16 launches (NULL: off); returns the number of
  * launches traced since the previous call. */

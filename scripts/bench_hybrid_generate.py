@@ -1,0 +1,53 @@
+"""BASELINE configs[4]-like run (hybrid, batch 32 per GPU): Zonos.generate on a random-init hybrid model of the recalled
+Zonos-v0.1-hybrid shape (d_model 2048; 46 blocks, attention + GatedMLP(8192) at every 9th, Mamba2 elsewhere: d_inner 4096,
+64 heads x 64, d_state 128 -- the real config.json is not available offline) through zonos_b200.hybrid.ZonosHybridB200,
+i.e. host-driven eager launches (no per-frame CUDA graph yet): the number is host-bound and says so.
+usage: python scripts/bench_hybrid_generate.py [batch] [new_frames]"""
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, ".")
+from oracle import mamba2 as om
+from zonos_b200.hybrid import HybridBackboneB200, ZonosHybridB200
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
+N_new = int(sys.argv[2]) if len(sys.argv) > 2 else 256
+d, H, Hkv, F_, n_layers = 2048, 16, 4, 8192, 46
+g = torch.Generator().manual_seed(0)
+r = lambda *sh: torch.randn(*sh, generator=g)
+BF = torch.bfloat16
+base = om.synth_mixer_params(d_model=d, seed=0, dtype=BF)
+layers = []
+for l in range(n_layers):
+    if l % 9 == 8:
+        p = {"kind": "attn", "in_proj.weight": (r((H + 2 * Hkv) * 128, d) / d ** 0.5).to(BF),
+             "out_proj.weight": (r(d, H * 128) / (H * 128) ** 0.5).to(BF), "norm2.weight": torch.ones(d, dtype=BF),
+             "fc1.weight": (r(2 * F_, d) / d ** 0.5).to(BF), "fc2.weight": (r(d, F_) / F_ ** 0.5).to(BF)}
+    else:
+        p = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in base.items()}
+        p["mixer_norm.weight"] = p.pop("norm.weight")
+        p["kind"] = "mamba2"
+    p["norm.weight"] = torch.ones(d, dtype=BF)
+    layers.append(p)
+sd = {}
+for k in range(9):
+    sd[f"embeddings.{k}.weight"] = r(1026, d).to(BF)
+    hw = (4.0 * r(1026, d) / d ** 0.5).to(BF)
+    hw[1024:] = 0
+    sd[f"heads.{k}.weight"] = hw
+net = HybridBackboneB200(layers, dict(weight=torch.ones(d, dtype=BF)), base["shape"], "cuda", H, Hkv)
+model = ZonosHybridB200(sd, net)
+cond = torch.nn.functional.layer_norm(r(2 * B, 128, d), (d,)).to(BF).cuda()
+sp = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0, repetition_penalty_window=2, temperature=1.0)
+model.generate(cond, None, max_new_tokens=16, batch_size=B, sampling_params=sp, seed=1)
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+out = model.generate(cond, None, max_new_tokens=N_new, batch_size=B, sampling_params=sp, seed=1)
+torch.cuda.synchronize()
+dt = time.perf_counter() - t0
+frames = sum(o.shape[1] for o in out)
+print(f"hybrid generate (eager, host-driven): batch {B}, {N_new} new frames, {n_layers} blocks: {dt:.2f} s -> "
+      f"{frames / 86.1328 / dt:.1f} audio-s/s, {dt / max(1, model.last_generate_stats['steps']) * 1e3:.2f} ms per frame "
+      f"(prefill included); codes finite/in range: {all(int(o.max()) < 1024 and int(o.min()) >= 0 for o in out)}")

@@ -221,3 +221,67 @@ def test_hybrid_backbone_prefill_then_decode_vs_oracle():
     assert cache["seqlen_offset"] == S + steps
     with pytest.raises(AssertionError):
         net.forward(u[:, :4].reshape(n_seq * 4, d).contiguous().cuda(), cache, 4)  # KV cache overflow, as _torch.py:44-45
+
+
+def test_hybrid_generate_greedy_teacher_forced_logits_vs_oracle():
+    """Zonos.generate on a small hybrid model (Mamba2 / attention + GatedMLP blocks, 9 codebook embeddings and heads, CFG):
+    greedy decoding of 10 frames on the B200 kernels; at every frame the CFG logits must match the oracle run on the same
+    token history (teacher-forced: the oracle recomputes the whole sequence each frame)."""
+    from oracle import delay as odelay
+    from zonos_b200.hybrid import HybridBackboneB200, ZonosHybridB200
+
+    d, H, Hkv, F_ = 256, 2, 1, 512
+    B, Lc, N_new = 2, 5, 10
+    g = torch.Generator().manual_seed(21)
+    r = lambda *sh: torch.randn(*sh, generator=g)
+    layers = []
+    for l, kind in enumerate(["mamba2", "attn", "mamba2"]):
+        if kind == "mamba2":
+            p = om.synth_mixer_params(d_model=d, seed=60 + l, dtype=BF)
+            p["mixer_norm.weight"] = p.pop("norm.weight")
+        else:
+            p = {"in_proj.weight": (r((H + 2 * Hkv) * 128, d) / d ** 0.5).to(BF), "out_proj.weight": (r(d, H * 128) / (H * 128) ** 0.5).to(BF),
+                 "norm2.weight": (1 + 0.1 * r(d)).to(BF), "fc1.weight": (r(2 * F_, d) / d ** 0.5).to(BF),
+                 "fc2.weight": (r(d, F_) / F_ ** 0.5).to(BF)}
+        p["kind"] = kind
+        p["norm.weight"] = (1 + 0.1 * r(d)).to(BF)
+        layers.append(p)
+    norm_f = dict(weight=(1 + 0.1 * r(d)).to(BF))
+    sd = {}
+    for k in range(9):
+        sd[f"embeddings.{k}.weight"] = r(1026, d).to(BF)
+        hw = (4.0 * r(1026, d) / d ** 0.5).to(BF)
+        hw[1024:] = 0  # no early EOS with random weights (SURVEY 8(c) caveat); slot 1025 is the pad row
+        sd[f"heads.{k}.weight"] = hw
+    net = HybridBackboneB200(layers, norm_f, layers[0]["shape"], "cuda", H, Hkv)
+    model = ZonosHybridB200(sd, net)
+    cond = torch.nn.functional.layer_norm(r(2 * B, Lc, d), (d,)).to(BF)
+    taps = []
+    out = model.generate(cond.cuda(), None, max_new_tokens=N_new, batch_size=B,
+                         sampling_params=dict(temperature=0.0, repetition_penalty=1.0),
+                         _tap=lambda s, l, f: taps.append((l.cpu(), f.cpu())))
+    assert len(out) == B and all(o.shape == (9, N_new) for o in out)
+
+    def oracle_logits(frames):  # frames: list of int64 [B, 9, 1] delayed columns 0..t
+        ids = torch.cat(frames, dim=2)
+        emb = torch.zeros(ids.shape[0], ids.shape[2], d, dtype=BF)  # [B, T, d], bf16 adds in codebook order
+        for k in range(9):
+            emb = (emb.float() + sd[f"embeddings.{k}.weight"][ids[:, k]].float()).to(BF)
+        hid = torch.cat([cond, torch.cat([emb, emb], 0)], dim=1)
+        last = om.hybrid_forward(layers, norm_f, hid, H, Hkv)[:, -1]
+        lg = torch.stack([(last.float() @ sd[f"heads.{k}.weight"].float().t()).to(BF) for k in range(9)], 1).float()
+        c, u = lg.chunk(2)
+        o = u + (c - u) * 2.0
+        o[..., 1025:] = -torch.inf
+        return o
+
+    delayed0 = odelay.apply_delay_pattern(torch.full((B, 9, N_new), -1, dtype=torch.int64), 1025)
+    history = [delayed0[..., :1]]
+    worst = 0.0
+    for step, (got, frame) in enumerate(taps[:8]):
+        want = oracle_logits(history)
+        fin = torch.isfinite(want)
+        assert torch.equal(fin, torch.isfinite(got))
+        worst = max(worst, float((got[fin] - want[fin]).abs().max()))
+        history.append(frame)
+    assert worst <= 0.25, f"hybrid logits differ from the oracle by {worst}"

@@ -391,6 +391,30 @@ extern "C" int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void*
   return ZB200_OK;
 }
 
+/* apply_heads + the classifier-free-guidance mix of _compute_logits (zonos/model.py:100-116) as one weight-streaming GEMM:
+ * xn bf16 [2*batch][d] (rows [0,B) cond, [B,2B) uncond) x packed heads (row_mode 2) -> logits fp32 [batch][n_q][vocab],
+ * uncond + (cond - uncond) * cfg_scale, pad slots (>= 1025) = -inf.  The engine runs the same kernel inside its step. */
+extern "C" int zb200_heads_cfg(const void* xn, int batch, int d, const void* w_heads_packed, int n_q, int vocab,
+                               int head_rows_padded, float cfg_scale, float* logits, int grid, float* ws, int64_t ws_floats,
+                               int* tickets, int n_tickets, void* stream) {
+  ZB_REQUIRE(xn && w_heads_packed && logits && batch > 0 && 2 * batch <= GEMM_BM && d > 0 && d % 64 == 0,
+             "heads_cfg: bad shape batch=%d d=%d (2*batch <= 128)", batch, d);
+  ZB_REQUIRE(n_q > 0 && vocab > 1025 && vocab <= head_rows_padded && head_rows_padded % SK_NT == 0, "heads_cfg: bad head layout");
+  const int tiles_per_head = head_rows_padded / SK_NT, n_tiles = n_q * tiles_per_head;
+  ZB_REQUIRE(grid >= 1 && grid <= 1024, "heads_cfg: grid=%d out of range", grid);
+  ZB_REQUIRE(ws && tickets && ws_floats >= (int64_t)grid * 2 * skinny_tg(skinny_mode(2 * batch, n_tiles, d / 64)) * SK_PARTIAL_F4 * 4 &&
+                 n_tickets >= n_tiles,
+             "heads_cfg: workspace too small (needs grid*2*tg*32 KB and n_tiles tickets)");
+  SkinnyCore g{};
+  g.Wp = w_heads_packed, g.n_tiles = n_tiles, g.k_blocks = d / 64, g.m_valid = 2 * batch, g.partial_ws = ws, g.tickets = tickets;
+  g.n_splits = 1;
+  g.trace = nullptr, g.trace_id = -1;
+  ARowCfgPairs al{(const uint8_t*)xn, (size_t)d * 2, batch};
+  EpiHeadsCfg<SK_NT> epi{logits, batch, n_q, vocab, tiles_per_head, cfg_scale};
+  ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, grid, (cudaStream_t)stream));
+  return ZB200_OK;
+}
+
 /* x <- bf16(x + bf16(a * w^T)); xn <- LayerNorm(x) * ln_w + ln_b: the out_proj / fc2 + residual + next-norm group of the
  * decode step as the engine runs it (deferred split-K GEMM -> resid_ln_kernel).  ws: >= splits*m*n floats. */
 extern "C" int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_packed, int n, int k, int splits, float* ws,

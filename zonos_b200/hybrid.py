@@ -164,3 +164,73 @@ class HybridBackboneB200:
         out, _ = ops.add_norm(hidden, residual, self.fw, self.fb, self.eps, self.rms)
         cache["seqlen_offset"] = pos0 + seq_len
         return out
+
+
+class ZonosHybridB200:
+    """`Zonos.generate` (zonos/model.py:224-457) on the hybrid backbone, host-driven: embedding sum, HybridBackboneB200,
+    heads + CFG GEMM, fused sampler + EOS state machine -- every operation a kernel of libzonos_b200.so, one frame per
+    loop iteration, positions kept on the host (eager launches: this is the functional path of the hybrid; the per-frame CUDA
+    graph of the transformer engine is not built for it yet).
+
+    sd: `embeddings.{k}.weight` [1026, d] and `heads.{k}.weight` [1026, d] like the reference state dict (model.py:57-62)."""
+
+    N_Q, VOCAB = 9, 1026
+
+    def __init__(self, sd, backbone: HybridBackboneB200):
+        self.backbone, self.device = backbone, backbone.device
+        bf = lambda t: t.detach().to(self.device, torch.bfloat16).contiguous()
+        self.emb = torch.stack([bf(sd[f"embeddings.{k}.weight"]) for k in range(self.N_Q)]).contiguous()
+        heads = torch.stack([bf(sd[f"heads.{k}.weight"]) for k in range(self.N_Q)]).contiguous()
+        self.w_heads = ops.pack_weight(heads, row_mode=2, rows_per_head=self.VOCAB, rows_per_head_padded=ops.HEAD_ROWS_PADDED)
+        self.masked_token_id = 1025
+
+    def _logits(self, last_rows, B, cfg_scale):
+        return ops.heads_cfg(last_rows, self.w_heads, B, self.N_Q, self.VOCAB, cfg_scale)
+
+    @torch.inference_mode()
+    def generate(self, prefix_conditioning, audio_prefix_codes=None, max_new_tokens=86 * 30, cfg_scale=2.0, batch_size=1,
+                 sampling_params=None, seed=0, row_base=0, _tap=None, _poll_every=16):
+        from .sampler import UNKNOWN_ID, LoopState
+
+        assert cfg_scale != 1, "TODO: add support for cfg_scale=1"
+        if batch_size * 2 != prefix_conditioning.shape[0]:
+            raise ValueError(f"Batch size mismatch: {batch_size} * 2 != {prefix_conditioning.shape[0]}")
+        dev, B, Q = self.device, batch_size, self.N_Q
+        d = self.emb.shape[2]
+        P = 0 if audio_prefix_codes is None else audio_prefix_codes.shape[2]
+        L_cond = prefix_conditioning.shape[1]
+        S = L_cond + P + 1
+        codes = torch.full((B, Q, P + max_new_tokens), UNKNOWN_ID, dtype=torch.int64, device=dev)
+        if audio_prefix_codes is not None:
+            codes[..., :P] = audio_prefix_codes.to(dev)
+        delayed = ops.apply_delay_pattern(codes, self.masked_token_id).to(torch.int32)
+        loop = LoopState(B, Q, self.VOCAB, delayed, P, L_cond, sampling_params, seed=seed, row_base=row_base, device=dev)
+        cache = self.backbone.allocate_inference_cache(2 * B, L_cond + P + max_new_tokens + 9)
+        # hidden = [prefix ; embed(delayed[..., :P+1])], cond rows then uncond rows (model.py:196-201)
+        hid = torch.empty(2 * B, S, d, dtype=torch.bfloat16, device=dev)
+        hid[:, :L_cond] = prefix_conditioning.to(device=dev, dtype=torch.bfloat16)
+        emb0 = ops.embed_codes(delayed[..., : P + 1].contiguous(), self.emb)
+        hid[:B, L_cond:], hid[B:, L_cond:] = emb0, emb0
+        out = self.backbone.forward(hid.view(2 * B * S, d), cache, S).view(2 * B, S, d)
+        logits = self._logits(out[:, -1].contiguous(), B, cfg_scale)
+        loop.sample_first(logits)
+        if _tap is not None:
+            torch.cuda.synchronize(dev)
+            _tap(0, logits.clone(), delayed[..., loop.first_offset:loop.first_offset + 1].to(torch.int64))
+        steps = 0
+        while steps < loop.max_steps:
+            col = loop.first_offset + steps  # the frame sampled by the previous iteration (state[offset] - 1 on the device)
+            e = ops.embed_codes(delayed[..., col:col + 1].contiguous(), self.emb).view(B, d)
+            out = self.backbone.forward(torch.cat([e, e], 0), cache, 1)
+            logits = self._logits(out, B, cfg_scale)
+            loop.sample_step(logits)
+            steps += 1
+            if _tap is not None or steps % _poll_every == 0 or steps == loop.max_steps:
+                torch.cuda.synchronize(dev)
+                if _tap is not None:
+                    c = loop.first_offset + steps
+                    _tap(steps, logits.clone(), delayed[..., c:c + 1].to(torch.int64))
+                if int(loop.host_flags[0]):
+                    break
+        self.last_generate_stats = dict(steps=steps)
+        return loop.finish()

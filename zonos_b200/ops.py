@@ -300,3 +300,20 @@ def gated_mlp_act(fc1_out: torch.Tensor) -> torch.Tensor:
     out = torch.empty(rows, two_f // 2, dtype=torch.bfloat16, device=fc1_out.device)
     check(lib().zb200_gated_mlp_act(ptr(fc1_out), ptr(out), rows, two_f // 2, stream_ptr()), "gated_mlp_act")
     return out
+
+
+def heads_cfg(xn: torch.Tensor, w_heads_packed: torch.Tensor, batch: int, n_q: int, vocab: int, cfg_scale: float, ws=None,
+              tickets=None) -> torch.Tensor:
+    """apply_heads + CFG mix (zonos/model.py:100-116): xn bf16 [2B, d] -> fp32 logits [B, n_q, vocab]."""
+    xn = _cuda(xn, torch.bfloat16)
+    d = xn.shape[1]
+    n_tiles = n_q * (HEAD_ROWS_PADDED // 64)
+    logits = torch.empty(batch, n_q, vocab, dtype=torch.float32, device=xn.device)
+    if ws is None:
+        ws = torch.empty(148 * 32768, dtype=torch.float32, device=xn.device)
+    if tickets is None:
+        tickets = torch.zeros(n_tiles, dtype=torch.int32, device=xn.device)
+    check(lib().zb200_heads_cfg(ptr(xn), batch, d, ptr(w_heads_packed), n_q, vocab, HEAD_ROWS_PADDED, ctypes.c_float(cfg_scale),
+                                ptr(logits), 148, ptr(ws), ctypes.c_int64(ws.numel()), ptr(tickets), tickets.numel(), stream_ptr()),
+          "heads_cfg")
+    return logits
