@@ -302,7 +302,7 @@ def mamba2_section(device, hbm_peak, rows=64, n_layers=40):
     us = e0.elapsed_time(e1) / (reps * n_layers) * 1e3
     ms_step = e2.elapsed_time(e3) / n
     st_bytes = 2 * rows * H * s["head_dim"] * N * 2
-    w_bytes = (stack.n_in * d + d * Di) * 2
+    w_bytes = (stack.n_in_real * d + d * Di) * 2
     algo = n_layers * (w_bytes + st_bytes)
     res = {"workload": f"hybrid first slice: {n_layers} Mamba2 blocks, {rows} rows (batch 32 x CFG), d_model 2048, state 64 x 64 x 128 bf16",
            "ssd_step": {"kernel": "mamba2_ssd_step_p64_kernel", "us_per_layer": round(us, 2), "bytes_per_layer": st_bytes,

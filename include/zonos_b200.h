@@ -53,7 +53,8 @@ int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_packed, int n, 
  * two TMEM accumulators.  lda must be a multiple of 8 elements, k a multiple of 64. */
 int zb200_gemm_big_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, void* stream);
 /* Same contract for m <= 128 rows through the weight-streaming stream-K kernel of the decode step (csrc/gemm_skinny.cuh)
- * on `grid` CTAs.  ws: >= grid * 32768 floats, tickets: >= ceil(n/64) zeroed ints. */
+ * on `grid` CTAs (grid <= 0: planned like the engine's ticketed GEMMs, at most 2 CTAs per SM).  ws: >= grid * 32768
+ * floats, tickets: >= ceil(n/64) zeroed ints. */
 int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo, int grid,
                            float* ws, int64_t ws_floats, int* tickets, int n_tickets, void* stream);
 /* Same contract for m <= 8 rows through the operand-swapped weight-streaming kernel (csrc/gemm_swap.cuh: weights are the

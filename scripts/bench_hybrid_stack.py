@@ -44,7 +44,7 @@ with torch.cuda.stream(side):
     side.synchronize()
 ms = e0.elapsed_time(e1) / n
 s = base["shape"]
-w_bytes = (stack.n_in * d + d * s["d_inner"]) * 2
+w_bytes = (stack.n_in_real * d + d * s["d_inner"]) * 2
 st_bytes = 2 * rows * s["n_heads"] * s["head_dim"] * s["d_state"] * 2
 algo = n_layers * (w_bytes + st_bytes)
 hbm_peak, _ = bench.peaks()

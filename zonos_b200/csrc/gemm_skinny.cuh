@@ -510,4 +510,41 @@ cudaError_t launch_gemm_skinny(const SkinnyCore& g, const ALoader& al, const Epi
                          : launch_gemm_skinny_cfg<128, MODE_K1>(g, al, epi, grid, st);
 }
 
+// ---- grid planning for ticketed epilogues (shared by the engine and the single-GEMM hooks) ----------------------------
+// Every CTA should be exactly one fragment, so grids are aligned to the group structure: whole groups per CTA when there
+// are enough groups; otherwise each group is shared by at most 3 CTAs (the last one to arrive reduces, so the
+// contributor count is the fix-up latency).  `sms` CTAs are resident at M > 32 (192 KB of shared memory each), 2 * sms at
+// M <= 32.
+struct SkPlan {
+  int grid, splits;
+  bool prefer_k1;
+};
+inline int big_m_ctas_per_sm() {  // experiment knob: CTAs per SM the planners assume at rows > 32
+  static const int v = getenv("ZB200_SK_CAP2") ? 2 : 1;
+  return v;
+}
+inline SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
+  const int cap = sms * (rows <= 32 ? 2 : big_m_ctas_per_sm());
+  SkPlan p{cap, 1, false};
+  int mode = skinny_mode(rows, n_tiles, k_blocks);
+  int groups = n_tiles / skinny_tg(mode);
+  if (groups * 2 <= cap && mode == MODE_T2) {  // few, shared groups: single-tile units keep the fix-up slots at 32 KB
+    p.prefer_k1 = true;
+    mode = MODE_K1, groups = n_tiles;
+  }
+  if (groups >= cap) {
+    for (int r = 1; r <= 2; ++r)
+      if (groups % r == 0 && groups / r <= cap) {
+        p.grid = groups / r;
+        return p;
+      }
+    p.grid = cap;  // unaligned stream-K: most groups end up with two contributors
+  } else {
+    static const int max_split = getenv("ZB200_SK_MAXSPLIT") ? atoi(getenv("ZB200_SK_MAXSPLIT")) : 3;
+    const int s = std::max(1, std::min(max_split, cap / groups));
+    p.grid = groups * s;
+  }
+  return p;
+}
+
 }  // namespace zb

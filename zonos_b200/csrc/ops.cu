@@ -378,8 +378,16 @@ extern "C" int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void*
   ZB_REQUIRE(m > 0 && m <= GEMM_BM && n > 0 && k > 0 && k % 64 == 0 && lda % 8 == 0,
              "gemm_skinny: bad shape m=%d n=%d k=%d lda=%d (m <= 128)", m, n, k, lda);
   const int n_tiles = ceil_div(n, SK_NT);
+  bool prefer_k1 = false;
+  if (grid <= 0) {  // plan the grid the way the engine does for its ticketed GEMMs (aligned to the tile groups)
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const SkPlan p = plan_ticketed(sms, m, n_tiles, k / 64);
+    grid = p.grid, prefer_k1 = p.prefer_k1;
+  }
   ZB_REQUIRE(grid >= 1 && grid <= 1024, "gemm_skinny: grid=%d out of range", grid);
-  ZB_REQUIRE(ws && tickets && ws_floats >= (int64_t)grid * 2 * skinny_tg(skinny_mode(m, n_tiles, k / 64)) * SK_PARTIAL_F4 * 4 && n_tickets >= n_tiles,
+  ZB_REQUIRE(ws && tickets && ws_floats >= (int64_t)grid * 2 * skinny_tg(skinny_mode(m, n_tiles, k / 64, prefer_k1)) * SK_PARTIAL_F4 * 4 &&
+                 n_tickets >= n_tiles,
              "gemm_skinny: workspace too small (needs grid*2*tg*32 KB and n_tiles tickets)");
   SkinnyCore g{};
   g.Wp = w_packed, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = m, g.partial_ws = ws, g.tickets = tickets;
@@ -387,7 +395,7 @@ extern "C" int zb200_gemm_skinny_bf16(const void* a, int m, int lda, const void*
   g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
   ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
   EpiStoreBf16<SK_NT> epi{(bf16*)out, ldo, n};
-  ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, grid, (cudaStream_t)stream));
+  ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, grid, (cudaStream_t)stream, prefer_k1));
   return ZB200_OK;
 }
 

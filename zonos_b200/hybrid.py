@@ -16,6 +16,16 @@ import torch
 from . import ops
 
 
+def _pack_even(w):
+    """Packs a projection with its output rows zero-padded to a multiple of 128, so that the weight-streaming GEMM can
+    pair N tiles (two 64-row tiles per UMMA); returns (packed, padded N)."""
+    n = w.shape[0]
+    n_pad = (n + 127) // 128 * 128
+    if n_pad != n:
+        w = torch.cat([w, torch.zeros(n_pad - n, w.shape[1], dtype=w.dtype, device=w.device)], 0)
+    return ops.pack_weight(w.contiguous()), n_pad
+
+
 class Mamba2StackB200:
     def __init__(self, layers, norm_f, shape, device, rms_norm=True, eps=1e-5):
         """layers: list of dicts with norm.weight (+ norm.bias), in_proj.weight, conv1d.weight, conv1d.bias, dt_bias, A_log,
@@ -29,12 +39,13 @@ class Mamba2StackB200:
         for p in layers:
             self.layers.append(dict(
                 nw=bf(p["norm.weight"]), nb=bf(p.get("norm.bias")),
-                w_in=ops.pack_weight(bf(p["in_proj.weight"])), w_out=ops.pack_weight(bf(p["out_proj.weight"])),
+                w_in=_pack_even(bf(p["in_proj.weight"]))[0], w_out=ops.pack_weight(bf(p["out_proj.weight"])),
                 cw=bf(p["conv1d.weight"]), cb=bf(p.get("conv1d.bias")), dtb=f32(p["dt_bias"]), A=f32(p["A_log"]), D=f32(p["D"]),
                 gw=bf(p["mixer_norm.weight"])))
         self.fw, self.fb = bf(norm_f["weight"]), bf(norm_f.get("bias"))
         s = self.s
-        self.n_in = 2 * s["d_inner"] + 2 * s["n_groups"] * s["d_state"] + s["n_heads"]
+        self.n_in = (2 * s["d_inner"] + 2 * s["n_groups"] * s["d_state"] + s["n_heads"] + 127) // 128 * 128  # padded (_pack_even)
+        self.n_in_real = 2 * s["d_inner"] + 2 * s["n_groups"] * s["d_state"] + s["n_heads"]
         self.conv_dim = s["d_inner"] + 2 * s["n_groups"] * s["d_state"]
         self._ws = self._tickets = None
 
@@ -47,9 +58,9 @@ class Mamba2StackB200:
     def _gemm(self, a, w, n):
         if a.shape[0] <= 128:  # decode: weight-streaming stream-K kernel
             if self._ws is None:
-                self._ws = torch.empty(148 * 32768, dtype=torch.float32, device=self.device)
+                self._ws = torch.empty(296 * 2 * 32768, dtype=torch.float32, device=self.device)
                 self._tickets = torch.zeros(1024, dtype=torch.int32, device=self.device)
-            return ops.gemm_skinny_bf16(a, w, n, 148, self._ws, self._tickets)
+            return ops.gemm_skinny_bf16(a, w, n, 0, self._ws, self._tickets)  # grid planned like the engine's GEMMs
         return ops.gemm_bf16(a, w, n)
 
     def _forward(self, x, states, seq_len):
@@ -96,7 +107,7 @@ class HybridBackboneB200:
         self.layers = []
         for p in layers:
             L = dict(kind=p["kind"], nw=bf(p["norm.weight"]), nb=bf(p.get("norm.bias")),
-                     w_in=ops.pack_weight(bf(p["in_proj.weight"])), w_out=ops.pack_weight(bf(p["out_proj.weight"])))
+                     w_in=_pack_even(bf(p["in_proj.weight"]))[0], w_out=ops.pack_weight(bf(p["out_proj.weight"])))
             if p["kind"] == "mamba2":
                 L.update(cw=bf(p["conv1d.weight"]), cb=bf(p.get("conv1d.bias")), dtb=f32(p["dt_bias"]), A=f32(p["A_log"]),
                          D=f32(p["D"]), gw=bf(p["mixer_norm.weight"]))
@@ -106,7 +117,7 @@ class HybridBackboneB200:
             self.layers.append(L)
         self.fw, self.fb = bf(norm_f["weight"]), bf(norm_f.get("bias"))
         s = self.s
-        self.n_in = 2 * s["d_inner"] + 2 * s["n_groups"] * s["d_state"] + s["n_heads"]
+        self.n_in = (2 * s["d_inner"] + 2 * s["n_groups"] * s["d_state"] + s["n_heads"] + 127) // 128 * 128  # padded (_pack_even)
         self.conv_dim = s["d_inner"] + 2 * s["n_groups"] * s["d_state"]
         self.inv_freq = (1.0 / (rope_base ** (torch.arange(0, 128, 2, dtype=torch.float32) / 128))).to(self.device)
         self._ws = self._tickets = None

@@ -84,10 +84,10 @@ def gemm_skinny_bf16(a: torch.Tensor, w_packed: torch.Tensor, n: int, grid: int 
     a = _cuda(a, torch.bfloat16)
     M, K = a.shape
     n_tiles = (n + 63) // 64
-    grid = max(1, min(grid, 1024))
+    grid = min(grid, 1024)  # <= 0: the library plans the grid like the engine (needs ws for 296 CTAs)
     out = torch.empty(M, n, dtype=torch.bfloat16, device=a.device)
     if ws is None:
-        ws = torch.empty(grid * 32768, dtype=torch.float32, device=a.device)
+        ws = torch.empty((grid if grid > 0 else 296) * 32768, dtype=torch.float32, device=a.device)
     if tickets is None:
         tickets = torch.zeros(n_tiles, dtype=torch.int32, device=a.device)
     check(lib().zb200_gemm_skinny_bf16(ptr(a), M, K, ptr(w_packed), n, K, ptr(out), n, grid, ptr(ws),
