@@ -204,7 +204,18 @@ int zb200_add_norm(const void* x, float* residual, int has_residual, const void*
  * [rows][(H + 2*Hkv)*128] into q [rows][H*128], k and v [rows][Hkv*128] and applies the non-interleaved rotary embedding
  * (pairs (i, i+64), cos / sin rounded to bf16) at position pos0 + (row % seq_len); inv_freq fp32 [64]. */
 int zb200_rope_split(const void* qkv, const float* inv_freq, void* q, void* k, void* v, int rows, int seq_len, int pos0,
-                     int n_heads, int n_kv_heads, void* stream);
+                     const int* pos_ptr, int n_heads, int n_kv_heads, void* stream);
+/* Decode-step forms with the position / column in DEVICE memory, so that a host-sequenced step can be replayed from a
+ * CUDA graph (the engine's own kernels take the same pointers): one token per sequence at position *pos_ptr; the column
+ * of `ids` embedded is *col_ptr + col_add (out bf16 [batch][d], written again dup_rows_offset rows further if > 0).
+ * zb200_rope_split takes pos_ptr too (NULL: pos0). */
+int zb200_kv_write_at(const void* k, const void* v, void* pool, const int* block_table, int pages_per_seq, int num_pages,
+                      int n_kv_heads, int layer, int n_seq, const int* pos_ptr, void* stream);
+int zb200_attn_decode_at(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,
+                         int n_heads, int n_kv_heads, int layer, int n_seq, const int* pos_ptr, int nsplit, float* ws,
+                         int* tickets, void* out, void* stream);
+int zb200_embed_sum_at(const int32_t* ids, int ids_stride_b, int ids_stride_q, const int* col_ptr, int col_add,
+                       const void* emb, void* out, int batch, int n_q, int vocab, int d, int dup_rows_offset, void* stream);
 /* mamba_ssm GatedMLP activation: fc1_out bf16 [rows][2*d_ff] -> out[r][c] = fc1_out[r][c] * silu(fc1_out[r][d_ff + c]). */
 int zb200_gated_mlp_act(const void* fc1_out, void* out, int rows, int d_ff, void* stream);
 

@@ -285,3 +285,8 @@ def test_hybrid_generate_greedy_teacher_forced_logits_vs_oracle():
         worst = max(worst, float((got[fin] - want[fin]).abs().max()))
         history.append(frame)
     assert worst <= 0.25, f"hybrid logits differ from the oracle by {worst}"
+    # CUDA-graph replay of the decode step (no tap: 16 frames per host poll) and eager launches give the same tokens
+    sp = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0, repetition_penalty_window=2, temperature=1.0)
+    a = model.generate(cond.cuda(), None, max_new_tokens=40, batch_size=B, sampling_params=sp, seed=5)
+    b = model.generate(cond.cuda(), None, max_new_tokens=40, batch_size=B, sampling_params=sp, seed=5, _graph=False)
+    assert all(torch.equal(x, y) for x, y in zip(a, b)) and all(x.shape == (9, 40) for x in a)

@@ -456,6 +456,18 @@ __global__ void kv_write_kernel(const bf16* __restrict__ k, const bf16* __restri
   *reinterpret_cast<uint4*>(kv.row(seq, pos, 1, head) + pc) = *reinterpret_cast<const uint4*>(v + src);
 }
 
+// Decode form with the position in device memory (graph replay): one token per sequence at position *pos_ptr.
+__global__ void kv_write_at_kernel(const bf16* __restrict__ k, const bf16* __restrict__ v, KvLayout kv, const int* __restrict__ pos_ptr) {
+  const int seq = blockIdx.x;
+  const int head = threadIdx.x / 16, chunk = threadIdx.x % 16;
+  const int pos = *pos_ptr;
+  if (pos < 0 || pos >= kv.pages_per_seq * ZB200_PAGE) return;
+  const size_t src = ((size_t)seq * kv.n_kv_heads + head) * HD + chunk * 8;
+  const int pc = (chunk ^ (pos & 7)) * 8;
+  *reinterpret_cast<uint4*>(kv.row(seq, pos, 0, head) + pc) = *reinterpret_cast<const uint4*>(k + src);
+  *reinterpret_cast<uint4*>(kv.row(seq, pos, 1, head) + pc) = *reinterpret_cast<const uint4*>(v + src);
+}
+
 }  // namespace zb
 
 using namespace zb;
@@ -489,6 +501,31 @@ extern "C" int zb200_attn_decode(const void* q, const void* pool, const int* blo
   a.q = (const bf16*)q, a.out = (bf16*)out;
   a.kv = make_kv((void*)pool, block_table, pages_per_seq, num_pages, n_kv_heads, layer);
   a.pos_ptr = nullptr, a.pos_add = n_keys - 1, a.n_heads = n_heads, a.n_kv_heads = n_kv_heads;
+  a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
+  a.partial_ws = ws, a.tickets = tickets;
+  ZB_CHECK_CUDA(launch_attn_decode(a, n_seq, nsplit, (cudaStream_t)stream));
+  return ZB200_OK;
+}
+
+extern "C" int zb200_kv_write_at(const void* k, const void* v, void* pool, const int* block_table, int pages_per_seq,
+                                 int num_pages, int n_kv_heads, int layer, int n_seq, const int* pos_ptr, void* stream) {
+  ZB_REQUIRE(k && v && pool && pos_ptr && n_seq > 0 && n_kv_heads > 0 && n_kv_heads <= 64, "kv_write_at: bad arguments");
+  kv_write_at_kernel<<<n_seq, n_kv_heads * 16, 0, (cudaStream_t)stream>>>(
+      (const bf16*)k, (const bf16*)v, make_kv(pool, block_table, pages_per_seq, num_pages, n_kv_heads, layer), pos_ptr);
+  ZB_CHECK_LAUNCH("kv_write_at_kernel");
+  return ZB200_OK;
+}
+
+extern "C" int zb200_attn_decode_at(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,
+                                    int n_heads, int n_kv_heads, int layer, int n_seq, const int* pos_ptr, int nsplit, float* ws,
+                                    int* tickets, void* out, void* stream) {
+  ZB_REQUIRE(n_seq > 0 && pos_ptr && nsplit >= 1 && n_heads % n_kv_heads == 0 && n_heads / n_kv_heads <= 4,
+             "attn_decode_at: bad shape (GQA group must be <= 4)");
+  ZB_REQUIRE(nsplit == 1 || (ws && tickets), "attn_decode_at: split-KV needs workspace and tickets");
+  AttnDecodeArgs a;
+  a.q = (const bf16*)q, a.out = (bf16*)out;
+  a.kv = make_kv((void*)pool, block_table, pages_per_seq, num_pages, n_kv_heads, layer);
+  a.pos_ptr = pos_ptr, a.pos_add = 0, a.n_heads = n_heads, a.n_kv_heads = n_kv_heads;
   a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
   a.partial_ws = ws, a.tickets = tickets;
   ZB_CHECK_CUDA(launch_attn_decode(a, n_seq, nsplit, (cudaStream_t)stream));

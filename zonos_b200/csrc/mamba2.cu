@@ -493,12 +493,13 @@ __global__ void __launch_bounds__(256) add_norm_kernel(const bf16* __restrict__ 
 // epilogue of the in_proj GEMM, or -- with the q/k weight rows permuted at pack time -- the existing interleaved one.)
 __global__ void __launch_bounds__(256) rope_split_kernel(const bf16* __restrict__ qkv, const float* __restrict__ inv_freq,
                                                          bf16* __restrict__ q, bf16* __restrict__ k, bf16* __restrict__ v,
-                                                         int seq_len, int pos0, int n_heads, int n_kv_heads) {
+                                                         int seq_len, int pos0, const int* __restrict__ pos_ptr, int n_heads,
+                                                         int n_kv_heads) {
   pdl_launch_dependents();
   const int row = blockIdx.x, tid = threadIdx.x;
-  const float pos = (float)(pos0 + row % seq_len);
   const int ld = (n_heads + 2 * n_kv_heads) * 128;
   pdl_wait_prior();
+  const float pos = (float)((pos_ptr ? *pos_ptr : pos0) + row % seq_len);  // pos_ptr: device-side position (graph replay)
   const bf16* src = qkv + (size_t)row * ld;
   const int n_rot = (n_heads + n_kv_heads) * 64;  // rotated pairs of the row
   for (int i = tid; i < n_rot; i += 256) {
@@ -620,12 +621,12 @@ extern "C" int zb200_add_norm(const void* x, float* residual, int has_residual, 
 }
 
 extern "C" int zb200_rope_split(const void* qkv, const float* inv_freq, void* q, void* k, void* v, int rows, int seq_len, int pos0,
-                                int n_heads, int n_kv_heads, void* stream) {
+                                const int* pos_ptr, int n_heads, int n_kv_heads, void* stream) {
   ZB_REQUIRE(qkv && inv_freq && q && k && v && rows > 0 && seq_len > 0 && rows % seq_len == 0 && pos0 >= 0 && n_heads > 0 &&
                  n_kv_heads > 0,
              "rope_split: bad arguments");
   ZB_CHECK_CUDA(launch_pdl(rope_split_kernel, dim3((unsigned)rows), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(),
-                           (const bf16*)qkv, inv_freq, (bf16*)q, (bf16*)k, (bf16*)v, seq_len, pos0, n_heads, n_kv_heads));
+                           (const bf16*)qkv, inv_freq, (bf16*)q, (bf16*)k, (bf16*)v, seq_len, pos0, pos_ptr, n_heads, n_kv_heads));
   return ZB200_OK;
 }
 

@@ -324,6 +324,16 @@ extern "C" int zb200_embed_sum(const int32_t* ids, int ids_stride_b, int ids_str
   return ZB200_OK;
 }
 
+extern "C" int zb200_embed_sum_at(const int32_t* ids, int ids_stride_b, int ids_stride_q, const int* col_ptr, int col_add,
+                                  const void* emb, void* out, int batch, int n_q, int vocab, int d, int dup_rows_offset,
+                                  void* stream) {
+  ZB_REQUIRE(ids && col_ptr && emb && out && n_q > 0 && n_q <= ZB200_MAX_CODEBOOKS && d % 8 == 0 && batch > 0,
+             "embed_sum_at: bad arguments");
+  ZB_CHECK_CUDA(launch_embed_sum(ids, ids_stride_b, ids_stride_q, col_ptr, col_add, 1, (const bf16*)emb, (bf16*)out, batch, n_q,
+                                 vocab, d, 1, 0, dup_rows_offset, (cudaStream_t)stream));
+  return ZB200_OK;
+}
+
 extern "C" int zb200_gemm_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo,
                                int splits, float* ws, int* tickets, void* stream) {
   ZB_REQUIRE(m > 0 && n > 0 && k > 0 && k % 64 == 0 && lda % 8 == 0, "gemm: bad shape m=%d n=%d k=%d lda=%d", m, n, k, lda);

@@ -55,11 +55,14 @@ class Mamba2StackB200:
                      ssm=torch.zeros(rows, s["n_heads"], s["head_dim"], s["d_state"], dtype=torch.bfloat16, device=self.device))
                 for _ in self.layers]
 
+    def _ensure_ws(self):
+        if self._ws is None:  # split-K fix-up slots of the weight-streaming GEMMs (<= 296 CTAs) and their self-resetting tickets
+            self._ws = torch.empty(296 * 2 * 32768, dtype=torch.float32, device=self.device)
+            self._tickets = torch.zeros(1024, dtype=torch.int32, device=self.device)
+
     def _gemm(self, a, w, n):
         if a.shape[0] <= 128:  # decode: weight-streaming stream-K kernel
-            if self._ws is None:
-                self._ws = torch.empty(296 * 2 * 32768, dtype=torch.float32, device=self.device)
-                self._tickets = torch.zeros(1024, dtype=torch.int32, device=self.device)
+            self._ensure_ws()
             return ops.gemm_skinny_bf16(a, w, n, 0, self._ws, self._tickets)  # grid planned like the engine's GEMMs
         return ops.gemm_bf16(a, w, n)
 
@@ -123,6 +126,7 @@ class HybridBackboneB200:
         self._ws = self._tickets = None
 
     _gemm = Mamba2StackB200._gemm
+    _ensure_ws = Mamba2StackB200._ensure_ws
 
     def allocate_inference_cache(self, n_seq, max_seqlen):
         s = self.s
@@ -137,13 +141,16 @@ class HybridBackboneB200:
                 states.append(None)
         return dict(kv=kv, layers=states, seqlen_offset=0, max_seqlen=max_seqlen)
 
-    def forward(self, x, cache, seq_len=1):
+    def forward(self, x, cache, seq_len=1, pos_ptr=None):
         """x bf16 [n_seq*seq_len, d_model] (sequence-major) at positions cache['seqlen_offset'].. -> norm_f output for every
-        row; the cache advances by seq_len (InferenceParams.seqlen_offset, zonos/config.py:8-25)."""
+        row; the cache advances by seq_len (InferenceParams.seqlen_offset, zonos/config.py:8-25).  pos_ptr: address of a
+        device int32 holding the position of a decode step (seq_len == 1) -- no host value enters the launches then, so the
+        step can be captured in a CUDA graph and replayed while the device advances the position."""
         s, pos0 = self.s, cache["seqlen_offset"]
         Di, G, N = s["d_inner"], s["n_groups"], s["d_state"]
         n_seq = x.shape[0] // seq_len
-        decode = seq_len == 1 and pos0 > 0
+        decode = seq_len == 1 and (pos0 > 0 or pos_ptr is not None)
+        assert pos_ptr is None or seq_len == 1
         if pos0 + seq_len > cache["max_seqlen"]:
             raise AssertionError(f"sequence length {pos0 + seq_len} exceeds the KV cache ({cache['max_seqlen']})")
         residual, hidden = None, x
@@ -161,7 +168,16 @@ class HybridBackboneB200:
                 mixed = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
             else:
                 qkv = self._gemm(hn, L["w_in"], (self.H + 2 * self.Hkv) * 128)
-                q, k, v = ops.rope_split(qkv, self.inv_freq, seq_len, pos0, self.H, self.Hkv)
+                q, k, v = ops.rope_split(qkv, self.inv_freq, seq_len, pos0, self.H, self.Hkv, pos_ptr=pos_ptr)
+                if pos_ptr is not None:
+                    ops.kv_write_at(cache["kv"], li, k, v, pos_ptr)
+                    mixed = ops.attn_decode_at(q, cache["kv"], li, pos_ptr, self.H)
+                    hidden = self._gemm(mixed, L["w_out"], s["d_model"])
+                    if "w_fc1" in L:
+                        hn2, residual = ops.add_norm(hidden, residual, L["n2w"], L["n2b"], self.eps, self.rms)
+                        h1 = ops.gated_mlp_act(self._gemm(hn2, L["w_fc1"], 2 * L["d_ff"]))
+                        hidden = self._gemm(h1, L["w_fc2"], s["d_model"])
+                    continue
                 ops.kv_write(cache["kv"], li, k.view(n_seq, seq_len, self.Hkv, 128), v.view(n_seq, seq_len, self.Hkv, 128), pos0)
                 if decode:
                     mixed = ops.attn_decode(q, cache["kv"], li, pos0 + 1, self.H)
@@ -173,15 +189,16 @@ class HybridBackboneB200:
                 h1 = ops.gated_mlp_act(self._gemm(hn2, L["w_fc1"], 2 * L["d_ff"]))
                 hidden = self._gemm(h1, L["w_fc2"], s["d_model"])
         out, _ = ops.add_norm(hidden, residual, self.fw, self.fb, self.eps, self.rms)
-        cache["seqlen_offset"] = pos0 + seq_len
+        if pos_ptr is None:  # (with a device-side position the caller advances the host copy: graph replays do not pass here)
+            cache["seqlen_offset"] = pos0 + seq_len
         return out
 
 
 class ZonosHybridB200:
     """`Zonos.generate` (zonos/model.py:224-457) on the hybrid backbone, host-driven: embedding sum, HybridBackboneB200,
-    heads + CFG GEMM, fused sampler + EOS state machine -- every operation a kernel of libzonos_b200.so, one frame per
-    loop iteration, positions kept on the host (eager launches: this is the functional path of the hybrid; the per-frame CUDA
-    graph of the transformer engine is not built for it yet).
+    heads + CFG GEMM, fused sampler + EOS state machine -- every operation a kernel of libzonos_b200.so.  The decode step
+    takes its column / position from the device-side loop state, so after the first frame it is replayed from a torch CUDA
+    graph (`_graph=False`: eager launches); the prefill and the first frame run eagerly.
 
     sd: `embeddings.{k}.weight` [1026, d] and `heads.{k}.weight` [1026, d] like the reference state dict (model.py:57-62)."""
 
@@ -200,7 +217,7 @@ class ZonosHybridB200:
 
     @torch.inference_mode()
     def generate(self, prefix_conditioning, audio_prefix_codes=None, max_new_tokens=86 * 30, cfg_scale=2.0, batch_size=1,
-                 sampling_params=None, seed=0, row_base=0, _tap=None, _poll_every=16):
+                 sampling_params=None, seed=0, row_base=0, _tap=None, _poll_every=16, _graph=True):
         from .sampler import UNKNOWN_ID, LoopState
 
         assert cfg_scale != 1, "TODO: add support for cfg_scale=1"
@@ -228,20 +245,51 @@ class ZonosHybridB200:
         if _tap is not None:
             torch.cuda.synchronize(dev)
             _tap(0, logits.clone(), delayed[..., loop.first_offset:loop.first_offset + 1].to(torch.int64))
-        steps = 0
-        while steps < loop.max_steps:
-            col = loop.first_offset + steps  # the frame sampled by the previous iteration (state[offset] - 1 on the device)
-            e = ops.embed_codes(delayed[..., col:col + 1].contiguous(), self.emb).view(B, d)
-            out = self.backbone.forward(torch.cat([e, e], 0), cache, 1)
-            logits = self._logits(out, B, cfg_scale)
-            loop.sample_step(logits)
-            steps += 1
-            if _tap is not None or steps % _poll_every == 0 or steps == loop.max_steps:
-                torch.cuda.synchronize(dev)
-                if _tap is not None:
-                    c = loop.first_offset + steps
-                    _tap(steps, logits.clone(), delayed[..., c:c + 1].to(torch.int64))
-                if int(loop.host_flags[0]):
-                    break
+        # decode loop (model.py:345-432): the frame's column and position live in the device-side loop state (the sampler's
+        # second pass advances them), so one step is a fixed launch sequence: first frame eagerly, then replays of a CUDA graph
+        from .sampler import ST_OFFSET, ST_POS
+
+        col_addr = loop.state.data_ptr() + 4 * ST_OFFSET
+        pos_addr = loop.state.data_ptr() + 4 * ST_POS
+        self.backbone._ensure_ws()
+        ws, tickets = self.backbone._ws, self.backbone._tickets
+
+        def one_step():
+            e = ops.embed_codes_at(delayed, col_addr, -1, self.emb)  # the frame sampled by the previous iteration, cond + uncond
+            h = self.backbone.forward(e, cache, 1, pos_ptr=pos_addr)
+            lg = ops.heads_cfg(h, self.w_heads, B, self.N_Q, self.VOCAB, cfg_scale, ws, tickets)
+            loop.sample_step(lg)
+            return lg
+
+        steps, graph, logits_g = 0, None, None
+
+        def after(lg):
+            nonlocal steps
+            torch.cuda.synchronize(dev)
+            ran = int(loop.host_flags[1]) - steps  # frames executed (launches past the end of the loop are no-ops)
+            steps += ran
+            cache["seqlen_offset"] += ran
+            if _tap is not None and ran > 0:
+                c = loop.first_offset + steps
+                _tap(steps, lg.clone(), delayed[..., c:c + 1].to(torch.int64))
+            return bool(loop.host_flags[0])
+
+        finished = False
+        if loop.max_steps > 0:
+            finished = after(one_step())
+        if not finished and steps < loop.max_steps and _graph:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                logits_g = one_step()
+            # (the capture does not execute the step)
+        chunk = 1 if _tap is not None else max(1, int(_poll_every))
+        while not finished and steps < loop.max_steps:
+            n = min(chunk, loop.max_steps - steps)
+            for _ in range(n):
+                if graph is not None:
+                    graph.replay()
+                else:
+                    logits_g = one_step()
+            finished = after(logits_g)
         self.last_generate_stats = dict(steps=steps)
         return loop.finish()

@@ -279,7 +279,7 @@ def add_norm(x: torch.Tensor, residual, w: torch.Tensor, b, eps: float, rms: boo
     return out, residual
 
 
-def rope_split(qkv: torch.Tensor, inv_freq: torch.Tensor, seq_len: int, pos0: int, n_heads: int, n_kv_heads: int):
+def rope_split(qkv: torch.Tensor, inv_freq: torch.Tensor, seq_len: int, pos0: int, n_heads: int, n_kv_heads: int, pos_ptr=None):
     """Hybrid attention layers: Wqkv output bf16 [rows, (H+2Hkv)*128] -> rotated q [rows, H*128], rotated k and v
     [rows, Hkv*128] (non-interleaved rotary at position pos0 + row % seq_len)."""
     qkv = _cuda(qkv, torch.bfloat16)
@@ -289,7 +289,7 @@ def rope_split(qkv: torch.Tensor, inv_freq: torch.Tensor, seq_len: int, pos0: in
     k = torch.empty(rows, n_kv_heads * 128, dtype=torch.bfloat16, device=qkv.device)
     v = torch.empty_like(k)
     check(lib().zb200_rope_split(ptr(qkv), ptr(_cuda(inv_freq, torch.float32)), ptr(q), ptr(k), ptr(v), rows, seq_len, pos0,
-                                 n_heads, n_kv_heads, stream_ptr()), "rope_split")
+                                 ctypes.c_void_p(0 if pos_ptr is None else pos_ptr), n_heads, n_kv_heads, stream_ptr()), "rope_split")
     return q, k, v
 
 
@@ -317,3 +317,28 @@ def heads_cfg(xn: torch.Tensor, w_heads_packed: torch.Tensor, batch: int, n_q: i
                                 ptr(logits), 148, ptr(ws), ctypes.c_int64(ws.numel()), ptr(tickets), tickets.numel(), stream_ptr()),
           "heads_cfg")
     return logits
+
+
+# ---- decode-step forms with device-side position / column (host-sequenced steps replayed from a CUDA graph) -----------------
+def kv_write_at(kv: PagedKV, layer: int, k: torch.Tensor, v: torch.Tensor, pos_ptr: int):
+    """k, v bf16 [n_seq, n_kv*128] -> the pool at position *pos_ptr (device int32 address)."""
+    check(lib().zb200_kv_write_at(ptr(k), ptr(v), ptr(kv.pool), ptr(kv.block_table), kv.pages_per_seq, kv.num_pages,
+                                  kv.n_kv_heads, layer, k.shape[0], ctypes.c_void_p(pos_ptr), stream_ptr()), "kv_write_at")
+
+
+def attn_decode_at(q: torch.Tensor, kv: PagedKV, layer: int, pos_ptr: int, n_heads: int) -> torch.Tensor:
+    out = torch.empty_like(q)
+    check(lib().zb200_attn_decode_at(ptr(q), ptr(kv.pool), ptr(kv.block_table), kv.pages_per_seq, kv.num_pages, n_heads,
+                                     kv.n_kv_heads, layer, q.shape[0], ctypes.c_void_p(pos_ptr), 1, ptr(None), ptr(None), ptr(out),
+                                     stream_ptr()), "attn_decode_at")
+    return out
+
+
+def embed_codes_at(delayed_i32: torch.Tensor, col_ptr: int, col_add: int, emb: torch.Tensor, dup: bool = True) -> torch.Tensor:
+    """Embedding sum of column *col_ptr + col_add of delayed int32 [B, Q, T] -> bf16 [2B or B, d] (rows duplicated for CFG)."""
+    B, Q, T = delayed_i32.shape
+    _, V, d = emb.shape
+    out = torch.empty((2 * B if dup else B), d, dtype=torch.bfloat16, device=delayed_i32.device)
+    check(lib().zb200_embed_sum_at(ptr(delayed_i32), Q * T, T, ctypes.c_void_p(col_ptr), col_add, ptr(emb), ptr(out), B, Q, V, d,
+                                   B if dup else 0, stream_ptr()), "embed_sum_at")
+    return out
