@@ -313,6 +313,30 @@ def mamba2_section(device, hbm_peak, rows=64, n_layers=40):
                                  "note": "host-sequenced kernels in a torch CUDA graph; attention layers and the C-side engine are not built yet"},
            "finite": bool(torch.isfinite(out).all())}
     del stack, states, graph
+    # (3) Zonos.generate on a random-init hybrid model of the recalled Zonos-v0.1-hybrid shape, batch 32 (C5-like), through
+    # zonos_b200.hybrid.ZonosHybridB200 (decode step replayed from a torch CUDA graph); marginal cost of a frame
+    from zonos_b200 import synth
+
+    model = synth.hybrid_model(device=device)
+    cond = synth.conditioning(32, 128, d, device=device, seed=1)
+
+    def gen(n_new):
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        out = model.generate(cond, None, max_new_tokens=n_new, batch_size=32, sampling_params=C3_SAMPLING, seed=1234)
+        torch.cuda.synchronize(device)
+        return time.perf_counter() - t0, out
+
+    gen(16)
+    t_a, _ = gen(128)
+    t_b, out = gen(512)
+    per_frame = (t_b - t_a) / (512 - 128)
+    res["generate_c5_like"] = {"workload": "hybrid Zonos.generate, recalled v0.1-hybrid shape (46 blocks, attention + GatedMLP every 9th), "
+                                           "random-init, batch 32, L_cond 128, min_p 0.1 + rep. penalty 3.0, cfg 2.0",
+                               "ms_per_frame": round(per_frame * 1e3, 3), "audio_s_per_s": round(32 / per_frame / FRAME_RATE, 1),
+                               "e2e_audio_s_per_s_512_frames": round(sum(o.shape[1] for o in out) / FRAME_RATE / t_b, 1),
+                               "note": "host-sequenced C-ABI kernels, decode step replayed from a torch CUDA graph; no C-side engine yet"}
+    del model
     return res
 
 

@@ -9,36 +9,15 @@ import time
 import torch
 
 sys.path.insert(0, ".")
-from oracle import mamba2 as om
-from zonos_b200.hybrid import HybridBackboneB200, ZonosHybridB200
+from zonos_b200 import synth
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
 N_new = int(sys.argv[2]) if len(sys.argv) > 2 else 256
-d, H, Hkv, F_, n_layers = 2048, 16, 4, 8192, 46
+n_layers, d = synth.HYBRID["n_layer"], synth.HYBRID["d_model"]
+model = synth.hybrid_model()
 g = torch.Generator().manual_seed(0)
 r = lambda *sh: torch.randn(*sh, generator=g)
 BF = torch.bfloat16
-base = om.synth_mixer_params(d_model=d, seed=0, dtype=BF)
-layers = []
-for l in range(n_layers):
-    if l % 9 == 8:
-        p = {"kind": "attn", "in_proj.weight": (r((H + 2 * Hkv) * 128, d) / d ** 0.5).to(BF),
-             "out_proj.weight": (r(d, H * 128) / (H * 128) ** 0.5).to(BF), "norm2.weight": torch.ones(d, dtype=BF),
-             "fc1.weight": (r(2 * F_, d) / d ** 0.5).to(BF), "fc2.weight": (r(d, F_) / F_ ** 0.5).to(BF)}
-    else:
-        p = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in base.items()}
-        p["mixer_norm.weight"] = p.pop("norm.weight")
-        p["kind"] = "mamba2"
-    p["norm.weight"] = torch.ones(d, dtype=BF)
-    layers.append(p)
-sd = {}
-for k in range(9):
-    sd[f"embeddings.{k}.weight"] = r(1026, d).to(BF)
-    hw = (4.0 * r(1026, d) / d ** 0.5).to(BF)
-    hw[1024:] = 0
-    sd[f"heads.{k}.weight"] = hw
-net = HybridBackboneB200(layers, dict(weight=torch.ones(d, dtype=BF)), base["shape"], "cuda", H, Hkv)
-model = ZonosHybridB200(sd, net)
 cond = torch.nn.functional.layer_norm(r(2 * B, 128, d), (d,)).to(BF).cuda()
 sp = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0, repetition_penalty_window=2, temperature=1.0)
 model.generate(cond, None, max_new_tokens=16, batch_size=B, sampling_params=sp, seed=1)
