@@ -254,6 +254,41 @@ typedef struct {
 int zb200_dac_decode(const zb200_dac_plan* plan, const int64_t* codes, int batch, int t, void* const* regions,
                      int64_t region_halves, float* wav, void* stream);
 
+/* ---- DACAutoencoder.codes_to_wavs post-processing (zonos/autoencoder.py:188-245) on a ragged batch of decoded
+ * waveforms: normalize_loudness (autoencoder.py:172-186 -> pyloudnorm 0.1.1 Meter.integrated_loudness: K-weighting
+ * high-shelf + high-pass biquads, 75 %-overlapped gating blocks, -70 LUFS absolute and -10 LU relative gates),
+ * trim_silence (autoencoder.py:49-90, including its quirks: the tail scan never tests the last frame and cuts the
+ * frame it detects), the 512-sample linear fade-in and the logarithmic fade-out (autoencoder.py:233-241).
+ * Everything the reference derives from the utterance LENGTH on the host (block size 0.4 / 0.1 s, the number of gating
+ * blocks and their integer sample bounds, computed with the reference's own float expressions) is passed in as
+ * tables; the fade curves are torch.linspace / torch.logspace evaluated once on the host so the device multiplies by
+ * the same fp32 values. */
+typedef struct {
+  double shelf_b[3], shelf_a[3]; /* K-weighting stage 1 (a[0] == 1) */
+  double hp_b[3], hp_a[3];       /* K-weighting stage 2 */
+  int32_t chunk;                 /* samples one thread filters sequentially (multiple of 4) */
+  int32_t max_blocks;            /* rows of blk_lo / blk_hi */
+  double chunk_transition[16];   /* row-major 4x4: zero-input transition of the cascaded filter state over `chunk` samples */
+  const int32_t* blk_lo[2];      /* device int32 [max_blocks]: first sample of gating block j for block size 0.4 s / 0.1 s */
+  const int32_t* blk_hi[2];      /* one past the last sample (not clipped to the utterance) */
+  double inv_norm[2];            /* 1 / (block_size * rate) */
+  const float* fade_in;          /* device fp32 [512] = torch.linspace(0, 1, 512) */
+  const float* fade_out;         /* device fp32: torch.logspace(0, -10, 512*k) for k = 1..20, concatenated */
+  double target_lufs;            /* -23.0 in codes_to_wavs */
+  float trim_threshold;          /* 1e-5 */
+  int32_t flags;                 /* bit 0: no fades (trim_silence / normalize_loudness called on their own) */
+} zb200_postproc_plan;
+/* wav fp32 [batch][pitch] (pitch % 4 == 0, 16-byte aligned), n_samples int32 [batch] valid samples per utterance,
+ * blk_sel int32 [batch]: 0 / 1 = index into the plan's block tables, -1 = loudness step skipped (the reference's
+ * "audio too short" path: gain 1), n_blocks int32 [batch]; all device pointers.  Writes out fp32 [batch][pitch]
+ * (utterance b occupies out[b][0 .. bounds[b][1]-bounds[b][0]), zero after), bounds int32 [batch][2] = the [start, end)
+ * trim_silence kept, lufs double [batch] (integrated loudness before the gain), gain fp32 [batch].
+ * ws: device scratch of at least zb200_postproc_ws_bytes(batch, max_n, chunk, max_blocks) bytes. */
+int64_t zb200_postproc_ws_bytes(int batch, int max_n, int chunk, int max_blocks);
+int zb200_codes_postprocess(const zb200_postproc_plan* plan, const float* wav, int64_t pitch, const int32_t* n_samples,
+                            const int32_t* blk_sel, const int32_t* n_blocks, int batch, int max_n, float* out,
+                            int32_t* bounds, double* lufs, float* gain, void* ws, int64_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -190,6 +190,27 @@ def gen_dac():
     torch.save(out, os.path.join(OUT, "dac.pt"))
 
 
+def gen_postproc():
+    """The reference's codes_to_wavs with decode patched to hand back the test waveform.  pyloudnorm is not installed
+    here, so its normalize_loudness takes its own except-branch (audio unchanged): these fixtures pin the trim and the
+    fades (see oracle/postproc.py's header)."""
+    import logging
+
+    import zonos.autoencoder as zae
+
+    zae.logger.setLevel(logging.ERROR)
+    ae = object.__new__(zae.DACAutoencoder)
+    ae.sampling_rate, ae.num_codebooks = 44100, 9
+    out = {}
+    for name in sc.POSTPROC_GOLDEN:
+        wav = sc.postproc_wav(name)
+        ae.decode = lambda c, w=wav: w.clone().unsqueeze(0)
+        (res,) = ae.codes_to_wavs(torch.zeros(1, 9, wav.shape[1] // 512, dtype=torch.long))
+        trimmed = ae.trim_silence(wav)
+        out[name] = dict(wav=res, trimmed_len=trimmed.shape[1], in_sum=float(wav.double().sum()))
+    torch.save(out, os.path.join(OUT, "postproc.pt"))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     import_reference()
@@ -200,6 +221,7 @@ def main():
     gen_eos(model)
     gen_model(model, "tiny")
     gen_dac()
+    gen_postproc()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

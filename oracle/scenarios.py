@@ -96,3 +96,39 @@ def sampler_inputs(seed: int = 21, B: int = 4):
     rp = torch.tensor([3.0, 1.0, 2.0, 1.5][:B])
     noise = torch.empty(B, N_CODEBOOKS, V_PAD).exponential_(1, generator=g)
     return logits, hist, rp, noise
+
+
+# codes_to_wavs post-processing cases: (frames of 512 samples, leading silent frames, trailing silent frames, amplitude)
+POSTPROC_CASES = {
+    "one_frame": (1, 0, 0, 0.3),
+    "three_frames": (3, 0, 0, 0.3),
+    "four_frames": (4, 0, 0, 0.2),
+    "short_block": (9, 1, 0, 0.25),  # 4608 samples: loudness on 0.1 s blocks
+    "lead_tail": (40, 3, 2, 0.1),
+    "tail_only": (100, 0, 5, 0.5),
+    "long_lead": (180, 20, 1, 0.05),  # > 2 s: 0.4 s blocks; the silence outlasts the 16 frames trim_silence looks at
+    "quiet_part": (240, 2, 3, 0.4),  # a passage below the relative gate
+    "silent": (64, 0, 0, 0.0),
+}
+POSTPROC_GOLDEN = ("one_frame", "three_frames", "four_frames", "short_block", "lead_tail", "tail_only")
+
+
+def postproc_wav(name: str) -> torch.Tensor:
+    """fp32 [1, 512 * frames]: a few partials under a slow envelope plus noise, near-silent head / tail."""
+    frames, lead, tail, amp = POSTPROC_CASES[name]
+    n = 512 * frames
+    g = torch.Generator().manual_seed(1000 + frames)
+    t = torch.arange(n, dtype=torch.float64) / 44100.0
+    x = torch.zeros(n, dtype=torch.float64)
+    for f0, a in ((140.0, 1.0), (420.0, 0.5), (1900.0, 0.3), (5200.0, 0.15)):
+        x += a * torch.sin(2 * torch.pi * f0 * t + float(torch.rand((), generator=g)) * 6.28)
+    x *= 0.6 + 0.4 * torch.sin(2 * torch.pi * 3.1 * t)
+    x = amp * (x / 2.0 + 0.05 * torch.randn(n, generator=g, dtype=torch.float64))
+    if name == "quiet_part":
+        x[n // 3 : n // 2] *= 0.01
+    x += 1e-5 * torch.randn(n, generator=g, dtype=torch.float64)
+    if lead:
+        x[: 512 * lead] *= 1e-4
+    if tail:
+        x[n - 512 * tail :] *= 1e-4
+    return x.to(torch.float32).unsqueeze(0)

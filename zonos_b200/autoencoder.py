@@ -1,5 +1,10 @@
-"""DACAutoencoder.decode on B200 (zonos/autoencoder.py:12-19,44-47) -- see zonos_b200/dac.py for the kernels' host side."""
+"""DACAutoencoder.decode / codes_to_wavs on B200 (zonos/autoencoder.py:12-19,44-47,172-267) -- see zonos_b200/dac.py
+and zonos_b200/postproc.py for the kernels' host side."""
+import logging
+
 import torch
+
+logger = logging.getLogger(__name__)
 
 
 class DACAutoencoder:
@@ -12,6 +17,7 @@ class DACAutoencoder:
         self.num_codebooks = 9
         self.sampling_rate = 44100
         self._decoder = None
+        self._postproc = {}
         self._device = torch.device("cpu")
 
     def to(self, device):
@@ -32,3 +38,89 @@ class DACAutoencoder:
         if self._decoder is None:
             raise RuntimeError("DAC weights not loaded: call autoencoder.load_dac_state_dict(state_dict) first")
         return self._decoder.decode(codes)
+
+    # ---- post-processing (autoencoder.py:49-90,172-267), batched on the device -----------------------------------
+    def _post(self, target_lufs: float):
+        from .postproc import WavPostprocessor
+
+        key = (str(self._device), float(target_lufs))
+        if key not in self._postproc:
+            self._postproc[key] = WavPostprocessor(self._device, self.sampling_rate, target_lufs)
+        return self._postproc[key]
+
+    def _padded(self, wav: torch.Tensor) -> torch.Tensor:
+        """[1, n] (any device) -> contiguous fp32 [1, round_up(n, 4)] on the device."""
+        n = wav.shape[1]
+        buf = torch.zeros(1, (n + 3) // 4 * 4, dtype=torch.float32, device=self._device)
+        buf[:, :n] = wav
+        return buf
+
+    def trim_silence(self, wav: torch.Tensor) -> torch.Tensor:
+        """autoencoder.py:49-90 with its default threshold / frame size: [1, n] -> [1, end - start]."""
+        assert wav.ndim == 2 and wav.shape[0] == 1, "Expected mono audio tensor"
+        out, bounds, _, _ = self._post(-23.0).run(self._padded(wav), [wav.shape[1]], loudness=False, fades=False)
+        start, end = bounds[0].tolist()
+        return out[:, : end - start].to(wav.device)
+
+    def normalize_loudness(self, audio: torch.Tensor, sr: int, target_lufs: float = -19.0) -> torch.Tensor:
+        """autoencoder.py:172-186: audio * 10 ** ((target - integrated loudness) / 20); unchanged when too short."""
+        assert sr == self.sampling_rate and audio.ndim == 2 and audio.shape[0] == 1
+        _, _, _, gain = self._post(target_lufs).run(self._padded(audio), [audio.shape[1]], fades=False)
+        return audio * gain.to(audio.device)
+
+    def codes_to_wavs(self, codes, device_output: bool = False) -> list:
+        """autoencoder.py:188-245: codes [B, 9, T] / [9, T] / a list of those -> list of fp32 [1, n_i] waveforms
+        (loudness-normalised to -23 LUFS, silence-trimmed, faded).  Utterances of equal length are decoded as one batch
+        (the decoder treats rows independently, so this equals the reference's one-by-one loop); the post-processing
+        runs once over the ragged batch.  Returns CPU tensors like the reference unless device_output."""
+        if isinstance(codes, (list, tuple)):
+            code_list = [c.unsqueeze(0) if c.dim() == 2 else c for c in codes]
+        elif codes.dim() == 2:
+            code_list = [codes.unsqueeze(0)]
+        elif codes.dim() == 3:
+            code_list = [codes[i : i + 1] for i in range(codes.shape[0])]
+        else:
+            raise ValueError(f"Invalid shape for codes: {codes.shape}. Expected [num_codebooks, num_codes] or "
+                             "[batch_size, num_codebooks, num_codes]")
+        kept = []
+        for c in code_list:
+            if c.shape[2] == 0:
+                logger.warning("Empty codebook detected, skipping decoding.")
+                continue
+            kept.extend(c[i : i + 1] for i in range(c.shape[0]))
+        if not kept:
+            return []
+        by_len = {}
+        for i, c in enumerate(kept):
+            by_len.setdefault(c.shape[2], []).append(i)
+        if len(by_len) == 1:
+            wav = self.decode(torch.cat(kept, 0).to(self._device)).squeeze(1)
+            n_samples = [wav.shape[1]] * len(kept)
+        else:
+            decoded = {}
+            for idx in by_len.values():
+                w = self.decode(torch.cat([kept[i] for i in idx], 0).to(self._device)).squeeze(1)
+                for k, i in enumerate(idx):
+                    decoded[i] = w[k]
+            n_samples = [decoded[i].shape[0] for i in range(len(kept))]
+            wav = torch.zeros(len(kept), (max(n_samples) + 3) // 4 * 4, dtype=torch.float32, device=self._device)
+            for i in range(len(kept)):
+                wav[i, : n_samples[i]] = decoded[i]
+        out, bounds, _, _ = self._post(-23.0).run(wav.contiguous(), n_samples)
+        if not device_output:
+            host = torch.empty(out.shape, dtype=out.dtype, pin_memory=True)
+            host.copy_(out, non_blocking=True)
+            out = host
+        b = bounds.tolist()  # synchronises
+        return [out[i : i + 1, : e - s] for i, (s, e) in enumerate(b)]
+
+    def save_codes(self, paths, codes) -> None:
+        """autoencoder.py:247-268."""
+        from .postproc import write_wav_f32
+
+        if isinstance(paths, str):
+            paths = [paths]
+        wavs = self.codes_to_wavs(codes)
+        assert len(paths) == len(wavs), f"Number of paths ({len(paths)}) must match number of codes ({len(wavs)})"
+        for p, w in zip(paths, wavs):
+            write_wav_f32(p, w, self.sampling_rate)

@@ -1,0 +1,369 @@
+// DACAutoencoder.codes_to_wavs post-processing on a ragged batch of decoded waveforms (zonos/autoencoder.py:188-245):
+// BS.1770 integrated loudness as pyloudnorm 0.1.1 computes it (normalize_loudness, autoencoder.py:172-186), the
+// energy trim (trim_silence, autoencoder.py:49-90) and the two fades (autoencoder.py:233-241).
+//
+// The only sequential part is the K-weighting IIR (two cascaded biquads).  It is split into chunks of `chunk` samples:
+//   1. kw_chunk<state>: every chunk filtered from a zero state -> its end state (one thread per chunk, fp64)
+//   2. kw_chunk_scan:   s_in[c+1] = M^chunk s_in[c] + s_end[c]            (one warp per utterance)
+//   3. kw_chunk<filter>: every chunk filtered again from its true start state, result stored as fp32 (as pyloudnorm
+//                       does: it filters in place in the float32 input array)
+//   4. kw_block_energy: mean square of every gating block (bounds from the host tables)
+//   5. loudness_trim:   gating, LUFS, gain, then the frame energies of the scaled signal and the trim bounds
+//   6. apply:           out = ((x * gain) * fade_in) * fade_out over the kept range
+// All of it is HBM-bound byte streaming: the signal is read three times (plus the overlapped block read) and written
+// twice (fp32).
+#include "../../include/zonos_b200.h"
+#include "common.cuh"
+
+#include <math.h>
+
+namespace zb {
+namespace {
+
+struct KwCoef {
+  double b0a, b1a, b2a, a1a, a2a;
+  double b0b, b1b, b2b, a1b, a2b;
+};
+struct KwMat {
+  double m[16];
+};
+
+// One sample through both transposed direct-form-II biquads (scipy.signal.lfilter's structure).  pyloudnorm writes the
+// first stage's output back into the float32 array before the second stage runs, hence the rounding in between.
+__device__ __forceinline__ double kw_step(const KwCoef& c, double x, double (&s)[4]) {
+  const double ya = fma(c.b0a, x, s[0]);
+  s[0] = fma(-c.a1a, ya, fma(c.b1a, x, s[1]));
+  s[1] = fma(-c.a2a, ya, c.b2a * x);
+  const double xb = (double)(float)ya;
+  const double yb = fma(c.b0b, xb, s[2]);
+  s[2] = fma(-c.a1b, yb, fma(c.b1b, xb, s[3]));
+  s[3] = fma(-c.a2b, yb, c.b2b * xb);
+  return yb;
+}
+
+constexpr int KW_THREADS = 128;
+
+template <bool WRITE>
+__global__ void __launch_bounds__(KW_THREADS)
+kw_chunk_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t* __restrict__ n_samples,
+                const int32_t* __restrict__ blk_sel, int chunk, int chunks_pitch, KwCoef coef,
+                double* __restrict__ s_end, const double* __restrict__ s_in, float* __restrict__ y) {
+  const int b = blockIdx.y;
+  const int c = blockIdx.x * KW_THREADS + threadIdx.x;
+  const int n = n_samples[b];
+  if (blk_sel[b] < 0) return;
+  const int64_t first = (int64_t)c * chunk;
+  if (first >= n) return;
+  const bool last = first + chunk >= n;
+  if (!WRITE && last) return;  // nobody consumes the end state of the last chunk
+  const int len = last ? (int)(n - first) : chunk;
+  double s[4] = {0.0, 0.0, 0.0, 0.0};
+  if (WRITE) {
+    const double* si = s_in + ((int64_t)b * chunks_pitch + c) * 4;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s[i] = si[i];
+  }
+  const float* x = wav + (int64_t)b * pitch + first;
+  float* yo = WRITE ? y + (int64_t)b * pitch + first : nullptr;
+  int i = 0;
+  for (; i + 4 <= len; i += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(x + i);
+    float4 o;
+    o.x = (float)kw_step(coef, (double)v.x, s);
+    o.y = (float)kw_step(coef, (double)v.y, s);
+    o.z = (float)kw_step(coef, (double)v.z, s);
+    o.w = (float)kw_step(coef, (double)v.w, s);
+    if (WRITE) *reinterpret_cast<float4*>(yo + i) = o;
+  }
+  for (; i < len; ++i) {
+    const float o = (float)kw_step(coef, (double)x[i], s);
+    if (WRITE) yo[i] = o;
+  }
+  if (!WRITE) {
+    double* se = s_end + ((int64_t)b * chunks_pitch + c) * 4;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) se[k] = s[k];
+  }
+}
+
+__device__ __forceinline__ double shfl_f64(double v, int src) {
+  int lo = __double2loint(v), hi = __double2hiint(v);
+  lo = __shfl_sync(0xffffffffu, lo, src);
+  hi = __shfl_sync(0xffffffffu, hi, src);
+  return __hiloint2double(hi, lo);
+}
+
+// One warp per utterance.  Each lane holds the zero-state end state of one chunk; the warp walks 32 chunks at a time,
+// every lane carrying the same running state, and lane k keeps the state that enters chunk base + k.
+__global__ void __launch_bounds__(32)
+kw_chunk_scan_kernel(const int32_t* __restrict__ n_samples, const int32_t* __restrict__ blk_sel, int chunk,
+                     int chunks_pitch, KwMat M, const double* __restrict__ s_end, double* __restrict__ s_in) {
+  const int b = blockIdx.x, lane = threadIdx.x;
+  if (blk_sel[b] < 0) return;
+  const int n = n_samples[b];
+  const int n_chunks = (n + chunk - 1) / chunk;
+  double s[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int base = 0; base < n_chunks; base += 32) {
+    const int c = base + lane;
+    double e[4] = {0.0, 0.0, 0.0, 0.0};
+    if (c < n_chunks - 1) {
+      const double* p = s_end + ((int64_t)b * chunks_pitch + c) * 4;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) e[i] = p[i];
+    }
+    double mine[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int k = 0; k < 32; ++k) {
+      if (lane == k) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) mine[i] = s[i];
+      }
+      double t[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        double acc = shfl_f64(e[i], k);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc = fma(M.m[i * 4 + j], s[j], acc);
+        t[i] = acc;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) s[i] = t[i];
+    }
+    if (c < n_chunks) {
+      double* p = s_in + ((int64_t)b * chunks_pitch + c) * 4;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) p[i] = mine[i];
+    }
+  }
+}
+
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += shfl_f64(v, (threadIdx.x & 31) ^ o);
+  return v;
+}
+
+constexpr int BE_THREADS = 256;
+
+// z[b][j] = (1 / (T_g * rate)) * sum(y[lo_j : hi_j]^2)  (pyloudnorm meter.py, eq. 1); squares in fp32 as np.square of
+// the float32 array gives, the sum carried in fp64.
+__global__ void __launch_bounds__(BE_THREADS)
+kw_block_energy_kernel(const float* __restrict__ y, int64_t pitch, const int32_t* __restrict__ n_samples,
+                       const int32_t* __restrict__ blk_sel, const int32_t* __restrict__ n_blocks,
+                       const int32_t* __restrict__ lo0, const int32_t* __restrict__ hi0,
+                       const int32_t* __restrict__ lo1, const int32_t* __restrict__ hi1, double inv0, double inv1,
+                       int max_blocks, double* __restrict__ z) {
+  const int b = blockIdx.y, j = blockIdx.x;
+  const int sel = blk_sel[b];
+  if (sel < 0 || j >= n_blocks[b]) return;
+  const int n = n_samples[b];
+  const int lo = min(sel ? lo1[j] : lo0[j], n);
+  const int hi = min(sel ? hi1[j] : hi0[j], n);
+  const float* p = y + (int64_t)b * pitch;
+  double acc = 0.0;
+  for (int i = lo + threadIdx.x; i < hi; i += BE_THREADS) {
+    const float v = p[i];
+    acc += (double)__fmul_rn(v, v);
+  }
+  acc = warp_sum_f64(acc);
+  __shared__ double part[BE_THREADS / 32];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < BE_THREADS / 32; ++w) t += part[w];
+    z[(int64_t)b * max_blocks + j] = (sel ? inv1 : inv0) * t;
+  }
+}
+
+constexpr int LT_THREADS = 1024;
+constexpr int TRIM_FRAME = 512;      // autoencoder.py:53
+constexpr int TRIM_MAX_FRAMES = 16;  // autoencoder.py:67
+
+__global__ void __launch_bounds__(LT_THREADS)
+loudness_trim_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t* __restrict__ n_samples,
+                     const int32_t* __restrict__ blk_sel, const int32_t* __restrict__ n_blocks, int max_blocks,
+                     const double* __restrict__ z, double target_lufs, float threshold, int32_t* __restrict__ bounds,
+                     double* __restrict__ lufs_out, float* __restrict__ gain_out) {
+  const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __shared__ float gain_s;
+  __shared__ int over[2 * TRIM_MAX_FRAMES];
+  const int n = n_samples[b];
+  if (warp == 0) {
+    double lufs = nan("");
+    float gain = 1.0f;
+    if (blk_sel[b] >= 0) {
+      const int nb = n_blocks[b];
+      const double* zb_ = z + (int64_t)b * max_blocks;
+      // absolute gate (Gamma_a = -70 LKFS), then the mean of the blocks that pass it
+      double sum1 = 0.0, cnt1 = 0.0;
+      for (int j = lane; j < nb; j += 32) {
+        const double l = -0.691 + 10.0 * log10(zb_[j]);
+        if (l >= -70.0) { sum1 += zb_[j]; cnt1 += 1.0; }
+      }
+      sum1 = warp_sum_f64(sum1);
+      cnt1 = warp_sum_f64(cnt1);
+      const double gamma_r = -0.691 + 10.0 * log10(sum1 / cnt1) - 10.0;  // 0/0 -> NaN -> every comparison false
+      double sum2 = 0.0, cnt2 = 0.0;
+      for (int j = lane; j < nb; j += 32) {
+        const double l = -0.691 + 10.0 * log10(zb_[j]);
+        if (l > gamma_r && l > -70.0) { sum2 += zb_[j]; cnt2 += 1.0; }
+      }
+      sum2 = warp_sum_f64(sum2);
+      cnt2 = warp_sum_f64(cnt2);
+      const double zavg = cnt2 > 0.0 ? sum2 / cnt2 : 0.0;  // np.nan_to_num(mean([]))
+      lufs = -0.691 + 10.0 * log10(zavg);
+      gain = (float)pow(10.0, (target_lufs - lufs) / 20.0);
+    }
+    if (lane == 0) {
+      gain_s = gain;
+      lufs_out[b] = lufs;
+      gain_out[b] = gain;
+    }
+  }
+  __syncthreads();
+  const float gain = gain_s;
+  const int nf = min((n / TRIM_FRAME) / 4, TRIM_MAX_FRAMES);
+  {
+    // warps 0..15: leading frame i; warps 16..31: trailing frame i (its slice is empty for i == 0: wav[:, -512:-0])
+    const bool tail = warp >= TRIM_MAX_FRAMES;
+    const int i = tail ? warp - TRIM_MAX_FRAMES : warp;
+    int flag = 0;
+    if (i < nf && !(tail && i == 0)) {
+      const int first = tail ? n - (i + 1) * TRIM_FRAME : i * TRIM_FRAME;
+      const float* p = wav + (int64_t)b * pitch + first;
+      float acc = 0.0f;
+#pragma unroll
+      for (int k = 0; k < TRIM_FRAME / 32; ++k) {
+        const float v = __fmul_rn(p[k * 32 + lane], gain);  // no fma contraction: torch squares, then sums
+        acc += __fmul_rn(v, v);
+      }
+      acc = warp_sum(acc);
+      flag = (acc / (float)TRIM_FRAME) > threshold;
+    }
+    if (lane == 0) over[warp] = flag;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int start = 0, end = n;
+    for (int i = 0; i < nf; ++i)
+      if (over[i]) { start = i * TRIM_FRAME; break; }
+    for (int i = 1; i < nf; ++i)
+      if (over[TRIM_MAX_FRAMES + i]) { end = n - (i + 1) * TRIM_FRAME; break; }  // cuts the detected frame too
+    if (end < start) end = start;
+    bounds[2 * b] = start;
+    bounds[2 * b + 1] = end;
+  }
+}
+
+constexpr int AP_THREADS = 256;
+constexpr int AP_PER_THREAD = 8;
+constexpr int FADE_BLOCK = 512;      // autoencoder.py:234
+constexpr int FADE_MAX_BLOCKS = 20;  // autoencoder.py:239
+
+__global__ void __launch_bounds__(AP_THREADS)
+postproc_apply_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t* __restrict__ bounds,
+                      const float* __restrict__ gain_in, const float* __restrict__ fade_in,
+                      const float* __restrict__ fade_out, int no_fades, float* __restrict__ out) {
+  const int b = blockIdx.y;
+  const int start = bounds[2 * b], n_out = bounds[2 * b + 1] - start;
+  const float gain = gain_in[b];
+  const int fo_blocks = no_fades ? 0 : min((n_out / FADE_BLOCK) / 4, FADE_MAX_BLOCKS);
+  const int fo_len = fo_blocks * FADE_BLOCK;
+  const int fo_first = n_out - fo_len;
+  const float* fo = fade_out + (int64_t)FADE_BLOCK * (fo_blocks * (fo_blocks - 1) / 2);  // tables of 512*k, k = 1..20
+  const float* x = wav + (int64_t)b * pitch + start;
+  float* o = out + (int64_t)b * pitch;
+  const int64_t base = (int64_t)blockIdx.x * (AP_THREADS * AP_PER_THREAD);
+#pragma unroll
+  for (int k = 0; k < AP_PER_THREAD; ++k) {
+    const int64_t i = base + k * AP_THREADS + threadIdx.x;
+    if (i >= pitch) break;
+    float v = 0.0f;
+    if (i < n_out) {
+      v = x[i] * gain;
+      if (i < FADE_BLOCK && !no_fades) v = v * fade_in[i];
+      if (fo_blocks > 0 && i >= fo_first) v = v * fo[i - fo_first];
+    }
+    o[i] = v;
+  }
+}
+
+struct WsLayout {
+  int chunks_pitch;
+  int64_t s_end, s_in, z, total;
+};
+WsLayout ws_layout(int batch, int max_n, int chunk, int max_blocks) {
+  WsLayout w;
+  w.chunks_pitch = (max_n + chunk - 1) / chunk + 1;
+  const int64_t states = (int64_t)batch * w.chunks_pitch * 4 * (int64_t)sizeof(double);
+  w.s_end = 0;
+  w.s_in = states;
+  w.z = 2 * states;
+  w.total = w.z + (int64_t)batch * (max_blocks > 0 ? max_blocks : 1) * (int64_t)sizeof(double);
+  return w;
+}
+
+}  // namespace
+}  // namespace zb
+
+using namespace zb;
+
+extern "C" int64_t zb200_postproc_ws_bytes(int batch, int max_n, int chunk, int max_blocks) {
+  if (batch <= 0 || max_n < 0 || chunk <= 0 || max_blocks < 0) return 0;
+  return ws_layout(batch, max_n, chunk, max_blocks).total;
+}
+
+extern "C" int zb200_codes_postprocess(const zb200_postproc_plan* plan, const float* wav, int64_t pitch,
+                                       const int32_t* n_samples, const int32_t* blk_sel, const int32_t* n_blocks,
+                                       int batch, int max_n, float* out, int32_t* bounds, double* lufs, float* gain,
+                                       void* ws, int64_t ws_bytes, void* stream) {
+  ZB_REQUIRE(plan && wav && n_samples && blk_sel && n_blocks && out && bounds && lufs && gain && ws,
+             "codes_postprocess: null pointer");
+  ZB_REQUIRE(batch > 0 && max_n > 0 && pitch >= max_n, "codes_postprocess: bad batch / max_n / pitch");
+  ZB_REQUIRE(pitch % 4 == 0 && (reinterpret_cast<uintptr_t>(wav) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+             "codes_postprocess: wav / out must be 16-byte aligned with a pitch that is a multiple of 4 samples");
+  ZB_REQUIRE(wav != out, "codes_postprocess: out must not alias wav (out is the filter's scratch)");
+  ZB_REQUIRE(plan->chunk >= 4 && plan->chunk % 4 == 0, "codes_postprocess: chunk must be a positive multiple of 4");
+  ZB_REQUIRE(plan->max_blocks > 0 && plan->blk_lo[0] && plan->blk_hi[0] && plan->blk_lo[1] && plan->blk_hi[1],
+             "codes_postprocess: gating-block tables missing");
+  ZB_REQUIRE(plan->fade_in && plan->fade_out, "codes_postprocess: fade tables missing");
+  const WsLayout w = ws_layout(batch, max_n, plan->chunk, plan->max_blocks);
+  ZB_REQUIRE(ws_bytes >= w.total, "codes_postprocess: workspace too small (%lld < %lld bytes)", (long long)ws_bytes,
+             (long long)w.total);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  KwCoef c;
+  c.b0a = plan->shelf_b[0]; c.b1a = plan->shelf_b[1]; c.b2a = plan->shelf_b[2];
+  c.a1a = plan->shelf_a[1]; c.a2a = plan->shelf_a[2];
+  c.b0b = plan->hp_b[0]; c.b1b = plan->hp_b[1]; c.b2b = plan->hp_b[2];
+  c.a1b = plan->hp_a[1]; c.a2b = plan->hp_a[2];
+  KwMat M;
+  for (int i = 0; i < 16; ++i) M.m[i] = plan->chunk_transition[i];
+  char* wsb = static_cast<char*>(ws);
+  double* s_end = reinterpret_cast<double*>(wsb + w.s_end);
+  double* s_in = reinterpret_cast<double*>(wsb + w.s_in);
+  double* z = reinterpret_cast<double*>(wsb + w.z);
+  const int n_chunks = ceil_div(max_n, plan->chunk);
+  const dim3 kw_grid(ceil_div(n_chunks, KW_THREADS), batch);
+  kw_chunk_kernel<false><<<kw_grid, KW_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, plan->chunk, w.chunks_pitch,
+                                                         c, s_end, nullptr, nullptr);
+  ZB_CHECK_LAUNCH("kw_chunk_kernel<state>");
+  kw_chunk_scan_kernel<<<batch, 32, 0, st>>>(n_samples, blk_sel, plan->chunk, w.chunks_pitch, M, s_end, s_in);
+  ZB_CHECK_LAUNCH("kw_chunk_scan_kernel");
+  kw_chunk_kernel<true><<<kw_grid, KW_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, plan->chunk, w.chunks_pitch, c,
+                                                        nullptr, s_in, out);
+  ZB_CHECK_LAUNCH("kw_chunk_kernel<filter>");
+  kw_block_energy_kernel<<<dim3(plan->max_blocks, batch), BE_THREADS, 0, st>>>(
+      out, pitch, n_samples, blk_sel, n_blocks, plan->blk_lo[0], plan->blk_hi[0], plan->blk_lo[1], plan->blk_hi[1],
+      plan->inv_norm[0], plan->inv_norm[1], plan->max_blocks, z);
+  ZB_CHECK_LAUNCH("kw_block_energy_kernel");
+  loudness_trim_kernel<<<batch, LT_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, n_blocks, plan->max_blocks, z,
+                                                     plan->target_lufs, plan->trim_threshold, bounds, lufs, gain);
+  ZB_CHECK_LAUNCH("loudness_trim_kernel");
+  const dim3 ap_grid((unsigned)((pitch + AP_THREADS * AP_PER_THREAD - 1) / (AP_THREADS * AP_PER_THREAD)), batch);
+  postproc_apply_kernel<<<ap_grid, AP_THREADS, 0, st>>>(wav, pitch, bounds, gain, plan->fade_in, plan->fade_out,
+                                                        (plan->flags & 1) != 0, out);
+  ZB_CHECK_LAUNCH("postproc_apply_kernel");
+  return ZB200_OK;
+}
