@@ -10,6 +10,7 @@ cfg 2.0, random-init Zonos-v0.1-transformer weights).  Prints ONE JSON line on r
 """
 import argparse
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -242,6 +243,52 @@ def dac_section(device, batch, frames):
             "tflops": round(flops / ms / 1e9, 1), "bound": "tensor",
             "frac_of_sustained_bf16_peak": None if tf_peak is None else round(flops / ms / 1e9 / tf_peak, 4),
             "launches": 31 * reps * 2, "finite": bool(torch.isfinite(wav_host).all())}
+
+
+def postproc_section(device, hbm_peak, batch, frames, cpu_utts=2):
+    """codes_to_wavs' post-processing (loudness normalisation, trim, fades) over a batch of decoded
+    waveforms already in HBM, against the reference's per-utterance CPU loop (oracle/postproc.py, bounded sample).
+    Algorithmic bytes: the signal has to be read once for the loudness, once more for the scaled output, and written
+    once = 12 B per sample; the kernels move ~6x4 B (chunked IIR in two passes + 75 %-overlapped gating blocks)."""
+    from zonos_b200.postproc import WavPostprocessor
+
+    n = 512 * frames
+    g = torch.Generator(device=device).manual_seed(3)
+    t = torch.arange(n, device=device, dtype=torch.float32) / 44100.0
+    wav = 0.2 * torch.sin(2 * math.pi * 180.0 * t).unsqueeze(0) * (0.6 + 0.4 * torch.sin(2 * math.pi * 2.3 * t))
+    wav = (wav + 0.03 * torch.randn(batch, n, device=device, generator=g)).contiguous()
+    wav[:, :1536] *= 1e-4
+    pp = WavPostprocessor(device)
+    lens = [n] * batch
+    for _ in range(2):
+        out, bounds, lufs, gain = pp.run(wav, lens)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        out, bounds, lufs, gain = pp.run(wav, lens)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    audio_s = batch * n / 44100.0
+    from oracle import postproc as opp  # CPU leg: the reference's loop restated
+
+    host = wav[:cpu_utts].cpu()
+    t0 = time.perf_counter()
+    refs = [opp.post(host[i : i + 1]) for i in range(cpu_utts)]
+    dt = time.perf_counter() - t0
+    b0 = bounds[0].tolist()
+    ok = b0 == [refs[0]["start"], refs[0]["end"]] and abs(float(lufs[0]) - refs[0]["lufs"]) < 1e-4
+    algo = 12 * batch * n
+    return {"workload": f"codes_to_wavs post-processing, batch {batch} x {n} samples ({n / 44100.0:.1f} s each)",
+            "ms": round(ms, 3), "audio_s_per_s": round(audio_s / (ms * 1e-3), 1), "launches": 6 * reps,
+            "algorithmic_bytes": algo, "bound": "hbm",
+            "hbm_frac": None if hbm_peak is None else round(algo / (ms * 1e-3) / 1e9 / hbm_peak, 4),
+            "lufs_in": round(float(lufs[0]), 3), "matches_cpu_leg": bool(ok),
+            "cpu_baseline": {"value": round(cpu_utts * n / 44100.0 / dt, 1), "unit": "audio-s/s", "cores": 1,
+                             "kind": "port", "sample": f"{cpu_utts} utterances of {n / 44100.0:.1f} s through "
+                                                       f"oracle/postproc.py ({dt:.2f} s)"}}
 
 
 def mamba2_section(device, hbm_peak, rows=64, n_layers=40):
@@ -517,6 +564,9 @@ def main_b200(args, world, rank, local):
         line["dac_decode"] = dac_section(device, B, args.max_new_tokens)
     if world == 1 and not args.no_mamba:
         line["hybrid_mamba2"] = mamba2_section(device, hbm_peak)
+        torch.cuda.empty_cache()
+    if world == 1 and not args.no_dac:
+        line["postprocess"] = postproc_section(device, hbm_peak, B, args.max_new_tokens)
         torch.cuda.empty_cache()
         # SURVEY 8(d) metric (i), second form: codes -> waveform included.  The two stages run back to back on the same
         # GPU, so the pipeline rate is the harmonic composition of the two end-to-end rates measured above.
