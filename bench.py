@@ -245,7 +245,7 @@ def dac_section(device, batch, frames):
             "launches": 31 * reps * 2, "finite": bool(torch.isfinite(wav_host).all())}
 
 
-def postproc_section(device, hbm_peak, batch, frames, cpu_utts=2):
+def postproc_section(device, hbm_peak, batch, frames, cpu_utts=2, chunk=None):
     """codes_to_wavs' post-processing (loudness normalisation, trim, fades) over a batch of decoded
     waveforms already in HBM, against the reference's per-utterance CPU loop (oracle/postproc.py, bounded sample).
     Algorithmic bytes: the signal has to be read once for the loudness, once more for the scaled output, and written
@@ -258,7 +258,7 @@ def postproc_section(device, hbm_peak, batch, frames, cpu_utts=2):
     wav = 0.2 * torch.sin(2 * math.pi * 180.0 * t).unsqueeze(0) * (0.6 + 0.4 * torch.sin(2 * math.pi * 2.3 * t))
     wav = (wav + 0.03 * torch.randn(batch, n, device=device, generator=g)).contiguous()
     wav[:, :1536] *= 1e-4
-    pp = WavPostprocessor(device)
+    pp = WavPostprocessor(device) if chunk is None else WavPostprocessor(device, chunk=chunk)
     lens = [n] * batch
     for _ in range(2):
         out, bounds, lufs, gain = pp.run(wav, lens)

@@ -257,10 +257,12 @@ loudness_trim_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t
 }
 
 constexpr int AP_THREADS = 256;
-constexpr int AP_PER_THREAD = 8;
+constexpr int AP_VEC_PER_THREAD = 4;   // float4 each
 constexpr int FADE_BLOCK = 512;      // autoencoder.py:234
 constexpr int FADE_MAX_BLOCKS = 20;  // autoencoder.py:239
 
+// out[b][i] = ((x[b][start + i] * gain) * fade_in[i]) * fade_out[i - (n_out - fade_len)], zero from n_out to the pitch.
+// start is a multiple of 512 and the pitch a multiple of 4, so the float4 path is always aligned.
 __global__ void __launch_bounds__(AP_THREADS)
 postproc_apply_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t* __restrict__ bounds,
                       const float* __restrict__ gain_in, const float* __restrict__ fade_in,
@@ -269,23 +271,36 @@ postproc_apply_kernel(const float* __restrict__ wav, int64_t pitch, const int32_
   const int start = bounds[2 * b], n_out = bounds[2 * b + 1] - start;
   const float gain = gain_in[b];
   const int fo_blocks = no_fades ? 0 : min((n_out / FADE_BLOCK) / 4, FADE_MAX_BLOCKS);
-  const int fo_len = fo_blocks * FADE_BLOCK;
-  const int fo_first = n_out - fo_len;
+  const int fo_first = n_out - fo_blocks * FADE_BLOCK;
   const float* fo = fade_out + (int64_t)FADE_BLOCK * (fo_blocks * (fo_blocks - 1) / 2);  // tables of 512*k, k = 1..20
+  const int fi_end = no_fades ? 0 : FADE_BLOCK;
   const float* x = wav + (int64_t)b * pitch + start;
   float* o = out + (int64_t)b * pitch;
-  const int64_t base = (int64_t)blockIdx.x * (AP_THREADS * AP_PER_THREAD);
+  const int64_t base = (int64_t)blockIdx.x * (AP_THREADS * AP_VEC_PER_THREAD * 4);
 #pragma unroll
-  for (int k = 0; k < AP_PER_THREAD; ++k) {
-    const int64_t i = base + k * AP_THREADS + threadIdx.x;
+  for (int k = 0; k < AP_VEC_PER_THREAD; ++k) {
+    const int64_t i = base + ((int64_t)k * AP_THREADS + threadIdx.x) * 4;
     if (i >= pitch) break;
-    float v = 0.0f;
-    if (i < n_out) {
-      v = x[i] * gain;
-      if (i < FADE_BLOCK && !no_fades) v = v * fade_in[i];
-      if (fo_blocks > 0 && i >= fo_first) v = v * fo[i - fo_first];
+    float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    if (i + 3 < n_out && start + i + 3 < pitch) {
+      const float4 t = *reinterpret_cast<const float4*>(x + i);
+      v[0] = t.x * gain; v[1] = t.y * gain; v[2] = t.z * gain; v[3] = t.w * gain;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (i + e < n_out) v[e] = x[i + e] * gain;
     }
-    o[i] = v;
+    if (i < fi_end || (fo_blocks > 0 && i + 3 >= fo_first)) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int64_t ie = i + e;
+        if (ie < n_out) {
+          if (ie < fi_end) v[e] = v[e] * fade_in[ie];
+          if (fo_blocks > 0 && ie >= fo_first) v[e] = v[e] * fo[ie - fo_first];
+        }
+      }
+    }
+    *reinterpret_cast<float4*>(o + i) = make_float4(v[0], v[1], v[2], v[3]);
   }
 }
 
@@ -361,7 +376,8 @@ extern "C" int zb200_codes_postprocess(const zb200_postproc_plan* plan, const fl
   loudness_trim_kernel<<<batch, LT_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, n_blocks, plan->max_blocks, z,
                                                      plan->target_lufs, plan->trim_threshold, bounds, lufs, gain);
   ZB_CHECK_LAUNCH("loudness_trim_kernel");
-  const dim3 ap_grid((unsigned)((pitch + AP_THREADS * AP_PER_THREAD - 1) / (AP_THREADS * AP_PER_THREAD)), batch);
+  const int ap_tile = AP_THREADS * AP_VEC_PER_THREAD * 4;
+  const dim3 ap_grid((unsigned)((pitch + ap_tile - 1) / ap_tile), batch);
   postproc_apply_kernel<<<ap_grid, AP_THREADS, 0, st>>>(wav, pitch, bounds, gain, plan->fade_in, plan->fade_out,
                                                         (plan->flags & 1) != 0, out);
   ZB_CHECK_LAUNCH("postproc_apply_kernel");
