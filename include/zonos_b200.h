@@ -261,7 +261,7 @@ int zb200_dac_decode(const zb200_dac_plan* plan, const int64_t* codes, int batch
  * frame it detects), the 512-sample linear fade-in and the logarithmic fade-out (autoencoder.py:233-241).
  * Everything the reference derives from the utterance LENGTH on the host (block size 0.4 / 0.1 s, the number of gating
  * blocks and their integer sample bounds, computed with the reference's own float expressions) is passed in as
- * tables; the fade curves are torch.linspace / torch.logspace evaluated once on the host so the device multiplies by
+ * tables (block bounds as indices into one sorted edge list, so that overlapping blocks share their partial sums); the fade curves are torch.linspace / torch.logspace evaluated once on the host so the device multiplies by
  * the same fp32 values. */
 typedef struct {
   double shelf_b[3], shelf_a[3]; /* K-weighting stage 1 (a[0] == 1) */
@@ -269,8 +269,12 @@ typedef struct {
   int32_t chunk;                 /* samples one thread filters sequentially (multiple of 4) */
   int32_t max_blocks;            /* rows of blk_lo / blk_hi */
   double chunk_transition[16];   /* row-major 4x4: zero-input transition of the cascaded filter state over `chunk` samples */
-  const int32_t* blk_lo[2];      /* device int32 [max_blocks]: first sample of gating block j for block size 0.4 s / 0.1 s */
-  const int32_t* blk_hi[2];      /* one past the last sample (not clipped to the utterance) */
+  const int32_t* edges[2];       /* device int32 [n_edges[k]], k = block size 0.4 s / 0.1 s: the sorted distinct first /
+                                    one-past-last samples of all gating blocks (edges[k][0] == 0); consecutive edges
+                                    bound a "segment"; a chunk may touch at most 8 segments */
+  int32_t n_edges[2];            /* <= 2 * max_blocks + 2 */
+  const int32_t* blk_lo[2];      /* device int32 [max_blocks]: gating block j = segments blk_lo[k][j] .. blk_hi[k][j] - 1 */
+  const int32_t* blk_hi[2];      /* (the block's samples are not clipped to the utterance in the table; the kernels clip) */
   double inv_norm[2];            /* 1 / (block_size * rate) */
   const float* fade_in;          /* device fp32 [512] = torch.linspace(0, 1, 512) */
   const float* fade_out;         /* device fp32: torch.logspace(0, -10, 512*k) for k = 1..20, concatenated */

@@ -114,3 +114,16 @@ def test_wav_writer_header(tmp_path):
     fmt, ch, rate, _, _, bits = struct.unpack("<HHIIHH", raw[20:36])
     assert (fmt, ch, rate, bits) == (3, 1, 44100, 32)
     assert np.array_equal(np.frombuffer(raw[44:], dtype="<f4"), w[0].numpy())
+
+
+def test_host_edge_tables_cover_every_block():
+    from zonos_b200 import postproc as hp
+
+    for bs in hp.WavPostprocessor.BLOCK_SIZES:
+        lo, hi = hp.block_bounds(bs, 44100, 700)
+        edges, e_lo, e_hi = hp.edge_tables(lo, hi)
+        assert edges == sorted(set(edges)) and edges[0] == 0
+        for j in (0, 1, 5, 333, 699):
+            assert edges[e_lo[j]] == lo[j] and edges[e_hi[j]] == hi[j] and e_lo[j] < e_hi[j]
+        for chunk in (512, 2048):
+            assert hp.max_pieces(edges, chunk) <= hp.MAX_PIECES

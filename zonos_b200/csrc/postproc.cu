@@ -5,13 +5,15 @@
 // The only sequential part is the K-weighting IIR (two cascaded biquads).  It is split into chunks of `chunk` samples:
 //   1. kw_chunk<state>: every chunk filtered from a zero state -> its end state (one thread per chunk, fp64)
 //   2. kw_chunk_scan:   s_in[c+1] = M^chunk s_in[c] + s_end[c]            (one warp per utterance)
-//   3. kw_chunk<filter>: every chunk filtered again from its true start state, result stored as fp32 (as pyloudnorm
-//                       does: it filters in place in the float32 input array)
-//   4. kw_block_energy: mean square of every gating block (bounds from the host tables)
-//   5. loudness_trim:   gating, LUFS, gain, then the frame energies of the scaled signal and the trim bounds
+//   3. kw_chunk<energy>: every chunk filtered again from its true start state; the K-weighted sample is rounded to
+//                       fp32 (pyloudnorm filters in place in the float32 input array), squared, and summed per
+//                       SEGMENT -- the pieces between consecutive gating-block edges that fall inside the chunk
+//   4. kw_segment_sum:  the pieces of every segment added up in chunk order (deterministic, no atomics)
+//   5. loudness_trim:   block energies (a block is a run of segments), gating, LUFS, gain, then the frame energies of
+//                       the scaled signal and the trim bounds
 //   6. apply:           out = ((x * gain) * fade_in) * fade_out over the kept range
-// All of it is HBM-bound byte streaming: the signal is read three times (plus the overlapped block read) and written
-// twice (fp32).
+// All of it is HBM-bound byte streaming: the signal is read three times and written once (fp32), 16 B per sample
+// against the 12 B a single-pass filter would need.
 #include "../../include/zonos_b200.h"
 #include "common.cuh"
 
@@ -43,47 +45,105 @@ __device__ __forceinline__ double kw_step(const KwCoef& c, double x, double (&s)
 
 constexpr int KW_THREADS = 128;
 
-template <bool WRITE>
+constexpr int KW_MAX_PIECES = 8;  // segments one chunk may touch (host checks the tables against it)
+
+// ENERGY == false: end state of the chunk from a zero start state.  ENERGY == true: the chunk from its true start state,
+// sum of squares per segment piece -> part[b][c][0..], index of the chunk's first segment -> seg0[b][c].
+template <bool ENERGY>
 __global__ void __launch_bounds__(KW_THREADS)
 kw_chunk_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t* __restrict__ n_samples,
                 const int32_t* __restrict__ blk_sel, int chunk, int chunks_pitch, KwCoef coef,
-                double* __restrict__ s_end, const double* __restrict__ s_in, float* __restrict__ y) {
+                double* __restrict__ s_end, const double* __restrict__ s_in, const int32_t* __restrict__ edges0,
+                const int32_t* __restrict__ edges1, int n_edges0, int n_edges1, double* __restrict__ part,
+                int32_t* __restrict__ seg0) {
   const int b = blockIdx.y;
   const int c = blockIdx.x * KW_THREADS + threadIdx.x;
   const int n = n_samples[b];
-  if (blk_sel[b] < 0) return;
+  const int sel = blk_sel[b];
+  if (sel < 0) return;
   const int64_t first = (int64_t)c * chunk;
   if (first >= n) return;
   const bool last = first + chunk >= n;
-  if (!WRITE && last) return;  // nobody consumes the end state of the last chunk
+  if (!ENERGY && last) return;  // nobody consumes the end state of the last chunk
   const int len = last ? (int)(n - first) : chunk;
   double s[4] = {0.0, 0.0, 0.0, 0.0};
-  if (WRITE) {
-    const double* si = s_in + ((int64_t)b * chunks_pitch + c) * 4;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) s[i] = si[i];
-  }
   const float* x = wav + (int64_t)b * pitch + first;
-  float* yo = WRITE ? y + (int64_t)b * pitch + first : nullptr;
-  int i = 0;
-  for (; i + 4 <= len; i += 4) {
-    const float4 v = *reinterpret_cast<const float4*>(x + i);
-    float4 o;
-    o.x = (float)kw_step(coef, (double)v.x, s);
-    o.y = (float)kw_step(coef, (double)v.y, s);
-    o.z = (float)kw_step(coef, (double)v.z, s);
-    o.w = (float)kw_step(coef, (double)v.w, s);
-    if (WRITE) *reinterpret_cast<float4*>(yo + i) = o;
-  }
-  for (; i < len; ++i) {
-    const float o = (float)kw_step(coef, (double)x[i], s);
-    if (WRITE) yo[i] = o;
-  }
-  if (!WRITE) {
+  if (!ENERGY) {
+    int i = 0;
+    for (; i + 4 <= len; i += 4) {
+      const float4 v = *reinterpret_cast<const float4*>(x + i);
+      kw_step(coef, (double)v.x, s);
+      kw_step(coef, (double)v.y, s);
+      kw_step(coef, (double)v.z, s);
+      kw_step(coef, (double)v.w, s);
+    }
+    for (; i < len; ++i) kw_step(coef, (double)x[i], s);
     double* se = s_end + ((int64_t)b * chunks_pitch + c) * 4;
 #pragma unroll
     for (int k = 0; k < 4; ++k) se[k] = s[k];
+    return;
   }
+  const double* si = s_in + ((int64_t)b * chunks_pitch + c) * 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) s[i] = si[i];
+  const int32_t* E = sel ? edges1 : edges0;
+  const int ne = sel ? n_edges1 : n_edges0;
+  int seg = 0;  // largest index with E[seg] <= first (E[0] == 0)
+  for (int lo = 0, hi = ne; hi - lo > 1;) {
+    const int mid = (lo + hi) >> 1;
+    if ((int64_t)E[mid] <= first) lo = mid; else hi = mid;
+    seg = lo;
+  }
+  seg0[(int64_t)b * chunks_pitch + c] = seg;
+  double* pc = part + ((int64_t)b * chunks_pitch + c) * KW_MAX_PIECES;
+  int piece = 0;
+  int64_t next_edge = seg + 1 < ne ? (int64_t)E[seg + 1] : INT64_MAX;
+  double acc = 0.0;
+  auto sample = [&](float xv, int64_t idx) {
+    while (idx >= next_edge) {
+      if (piece < KW_MAX_PIECES) pc[piece] = acc;
+      acc = 0.0;
+      ++piece;
+      ++seg;
+      next_edge = seg + 1 < ne ? (int64_t)E[seg + 1] : INT64_MAX;
+    }
+    const float yf = (float)kw_step(coef, (double)xv, s);
+    acc += (double)__fmul_rn(yf, yf);  // np.square of the float32 array, summed in fp64
+  };
+  int i = 0;
+  for (; i + 4 <= len; i += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(x + i);
+    sample(v.x, first + i);
+    sample(v.y, first + i + 1);
+    sample(v.z, first + i + 2);
+    sample(v.w, first + i + 3);
+  }
+  for (; i < len; ++i) sample(x[i], first + i);
+  if (piece < KW_MAX_PIECES) pc[piece] = acc;
+}
+
+// seg_sum[b][s] = sum of the pieces of segment s = [E[s], E[s+1]) (clipped to the utterance), chunk by chunk.
+__global__ void __launch_bounds__(128)
+kw_segment_sum_kernel(const int32_t* __restrict__ n_samples, const int32_t* __restrict__ blk_sel, int chunk,
+                      int chunks_pitch, const int32_t* __restrict__ edges0, const int32_t* __restrict__ edges1,
+                      int n_edges0, int n_edges1, const double* __restrict__ part, const int32_t* __restrict__ seg0,
+                      int seg_pitch, double* __restrict__ seg_sum) {
+  const int b = blockIdx.y, sg = blockIdx.x * 128 + threadIdx.x;
+  const int sel = blk_sel[b];
+  if (sel < 0) return;
+  const int32_t* E = sel ? edges1 : edges0;
+  const int ne = sel ? n_edges1 : n_edges0;
+  if (sg + 1 >= ne) return;
+  const int n = n_samples[b];
+  const int lo = min(E[sg], n), hi = min(E[sg + 1], n);
+  double t = 0.0;
+  if (lo < hi) {
+    for (int c = lo / chunk; c <= (hi - 1) / chunk; ++c) {
+      const int p = sg - seg0[(int64_t)b * chunks_pitch + c];
+      if (p >= 0 && p < KW_MAX_PIECES) t += part[((int64_t)b * chunks_pitch + c) * KW_MAX_PIECES + p];
+    }
+  }
+  seg_sum[(int64_t)b * seg_pitch + sg] = t;
 }
 
 __device__ __forceinline__ double shfl_f64(double v, int src) {
@@ -142,40 +202,6 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
   return v;
 }
 
-constexpr int BE_THREADS = 256;
-
-// z[b][j] = (1 / (T_g * rate)) * sum(y[lo_j : hi_j]^2)  (pyloudnorm meter.py, eq. 1); squares in fp32 as np.square of
-// the float32 array gives, the sum carried in fp64.
-__global__ void __launch_bounds__(BE_THREADS)
-kw_block_energy_kernel(const float* __restrict__ y, int64_t pitch, const int32_t* __restrict__ n_samples,
-                       const int32_t* __restrict__ blk_sel, const int32_t* __restrict__ n_blocks,
-                       const int32_t* __restrict__ lo0, const int32_t* __restrict__ hi0,
-                       const int32_t* __restrict__ lo1, const int32_t* __restrict__ hi1, double inv0, double inv1,
-                       int max_blocks, double* __restrict__ z) {
-  const int b = blockIdx.y, j = blockIdx.x;
-  const int sel = blk_sel[b];
-  if (sel < 0 || j >= n_blocks[b]) return;
-  const int n = n_samples[b];
-  const int lo = min(sel ? lo1[j] : lo0[j], n);
-  const int hi = min(sel ? hi1[j] : hi0[j], n);
-  const float* p = y + (int64_t)b * pitch;
-  double acc = 0.0;
-  for (int i = lo + threadIdx.x; i < hi; i += BE_THREADS) {
-    const float v = p[i];
-    acc += (double)__fmul_rn(v, v);
-  }
-  acc = warp_sum_f64(acc);
-  __shared__ double part[BE_THREADS / 32];
-  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double t = 0.0;
-#pragma unroll
-    for (int w = 0; w < BE_THREADS / 32; ++w) t += part[w];
-    z[(int64_t)b * max_blocks + j] = (sel ? inv1 : inv0) * t;
-  }
-}
-
 constexpr int LT_THREADS = 1024;
 constexpr int TRIM_FRAME = 512;      // autoencoder.py:53
 constexpr int TRIM_MAX_FRAMES = 16;  // autoencoder.py:67
@@ -183,7 +209,10 @@ constexpr int TRIM_MAX_FRAMES = 16;  // autoencoder.py:67
 __global__ void __launch_bounds__(LT_THREADS)
 loudness_trim_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t* __restrict__ n_samples,
                      const int32_t* __restrict__ blk_sel, const int32_t* __restrict__ n_blocks, int max_blocks,
-                     const double* __restrict__ z, double target_lufs, float threshold, int32_t* __restrict__ bounds,
+                     const int32_t* __restrict__ e_lo0, const int32_t* __restrict__ e_hi0,
+                     const int32_t* __restrict__ e_lo1, const int32_t* __restrict__ e_hi1, double inv0, double inv1,
+                     const double* __restrict__ seg_sum, int seg_pitch, double* __restrict__ z, double target_lufs,
+                     float threshold, int32_t* __restrict__ bounds,
                      double* __restrict__ lufs_out, float* __restrict__ gain_out) {
   const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   __shared__ float gain_s;
@@ -194,7 +223,21 @@ loudness_trim_kernel(const float* __restrict__ wav, int64_t pitch, const int32_t
     float gain = 1.0f;
     if (blk_sel[b] >= 0) {
       const int nb = n_blocks[b];
-      const double* zb_ = z + (int64_t)b * max_blocks;
+      double* zb_ = z + (int64_t)b * max_blocks;
+      {
+        // z_j = (1 / (T_g * rate)) * sum(y[lo_j : hi_j]^2)  (pyloudnorm meter.py, eq. 1): block j is the run of
+        // segments e_lo[j] .. e_hi[j] - 1
+        const int sel = blk_sel[b];
+        const int32_t* e_lo = sel ? e_lo1 : e_lo0;
+        const int32_t* e_hi = sel ? e_hi1 : e_hi0;
+        const double inv = sel ? inv1 : inv0;
+        const double* ss = seg_sum + (int64_t)b * seg_pitch;
+        for (int j = lane; j < nb; j += 32) {
+          double t = 0.0;
+          for (int sg = e_lo[j]; sg < e_hi[j]; ++sg) t += ss[sg];
+          zb_[j] = inv * t;  // read back below by the same lane
+        }
+      }
       // absolute gate (Gamma_a = -70 LKFS), then the mean of the blocks that pass it
       double sum1 = 0.0, cnt1 = 0.0;
       for (int j = lane; j < nb; j += 32) {
@@ -305,17 +348,21 @@ postproc_apply_kernel(const float* __restrict__ wav, int64_t pitch, const int32_
 }
 
 struct WsLayout {
-  int chunks_pitch;
-  int64_t s_end, s_in, z, total;
+  int chunks_pitch, seg_pitch;
+  int64_t s_end, s_in, part, seg_sum, z, seg0, total;
 };
 WsLayout ws_layout(int batch, int max_n, int chunk, int max_blocks) {
   WsLayout w;
   w.chunks_pitch = (max_n + chunk - 1) / chunk + 1;
-  const int64_t states = (int64_t)batch * w.chunks_pitch * 4 * (int64_t)sizeof(double);
+  w.seg_pitch = 2 * max_blocks + 2;  // at most one lower and one upper edge per block
+  const int64_t chunks = (int64_t)batch * w.chunks_pitch, d = (int64_t)sizeof(double);
   w.s_end = 0;
-  w.s_in = states;
-  w.z = 2 * states;
-  w.total = w.z + (int64_t)batch * (max_blocks > 0 ? max_blocks : 1) * (int64_t)sizeof(double);
+  w.s_in = w.s_end + chunks * 4 * d;
+  w.part = w.s_in + chunks * 4 * d;
+  w.seg_sum = w.part + chunks * KW_MAX_PIECES * d;
+  w.z = w.seg_sum + (int64_t)batch * w.seg_pitch * d;
+  w.seg0 = w.z + (int64_t)batch * (max_blocks > 0 ? max_blocks : 1) * d;
+  w.total = w.seg0 + chunks * (int64_t)sizeof(int32_t);
   return w;
 }
 
@@ -339,10 +386,14 @@ extern "C" int zb200_codes_postprocess(const zb200_postproc_plan* plan, const fl
   ZB_REQUIRE(pitch % 4 == 0 && (reinterpret_cast<uintptr_t>(wav) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(out) & 15) == 0,
              "codes_postprocess: wav / out must be 16-byte aligned with a pitch that is a multiple of 4 samples");
-  ZB_REQUIRE(wav != out, "codes_postprocess: out must not alias wav (out is the filter's scratch)");
+  ZB_REQUIRE(wav != out, "codes_postprocess: out must not alias wav");
   ZB_REQUIRE(plan->chunk >= 4 && plan->chunk % 4 == 0, "codes_postprocess: chunk must be a positive multiple of 4");
-  ZB_REQUIRE(plan->max_blocks > 0 && plan->blk_lo[0] && plan->blk_hi[0] && plan->blk_lo[1] && plan->blk_hi[1],
+  ZB_REQUIRE(plan->max_blocks > 0 && plan->blk_lo[0] && plan->blk_hi[0] && plan->blk_lo[1] && plan->blk_hi[1] &&
+                 plan->edges[0] && plan->edges[1],
              "codes_postprocess: gating-block tables missing");
+  for (int k = 0; k < 2; ++k)
+    ZB_REQUIRE(plan->n_edges[k] >= 2 && plan->n_edges[k] <= 2 * plan->max_blocks + 2,
+               "codes_postprocess: n_edges[%d] = %d out of range", k, plan->n_edges[k]);
   ZB_REQUIRE(plan->fade_in && plan->fade_out, "codes_postprocess: fade tables missing");
   const WsLayout w = ws_layout(batch, max_n, plan->chunk, plan->max_blocks);
   ZB_REQUIRE(ws_bytes >= w.total, "codes_postprocess: workspace too small (%lld < %lld bytes)", (long long)ws_bytes,
@@ -358,23 +409,30 @@ extern "C" int zb200_codes_postprocess(const zb200_postproc_plan* plan, const fl
   char* wsb = static_cast<char*>(ws);
   double* s_end = reinterpret_cast<double*>(wsb + w.s_end);
   double* s_in = reinterpret_cast<double*>(wsb + w.s_in);
+  double* part = reinterpret_cast<double*>(wsb + w.part);
+  double* seg_sum = reinterpret_cast<double*>(wsb + w.seg_sum);
   double* z = reinterpret_cast<double*>(wsb + w.z);
+  int32_t* seg0 = reinterpret_cast<int32_t*>(wsb + w.seg0);
   const int n_chunks = ceil_div(max_n, plan->chunk);
   const dim3 kw_grid(ceil_div(n_chunks, KW_THREADS), batch);
   kw_chunk_kernel<false><<<kw_grid, KW_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, plan->chunk, w.chunks_pitch,
-                                                         c, s_end, nullptr, nullptr);
+                                                         c, s_end, nullptr, nullptr, nullptr, 0, 0, nullptr, nullptr);
   ZB_CHECK_LAUNCH("kw_chunk_kernel<state>");
   kw_chunk_scan_kernel<<<batch, 32, 0, st>>>(n_samples, blk_sel, plan->chunk, w.chunks_pitch, M, s_end, s_in);
   ZB_CHECK_LAUNCH("kw_chunk_scan_kernel");
   kw_chunk_kernel<true><<<kw_grid, KW_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, plan->chunk, w.chunks_pitch, c,
-                                                        nullptr, s_in, out);
-  ZB_CHECK_LAUNCH("kw_chunk_kernel<filter>");
-  kw_block_energy_kernel<<<dim3(plan->max_blocks, batch), BE_THREADS, 0, st>>>(
-      out, pitch, n_samples, blk_sel, n_blocks, plan->blk_lo[0], plan->blk_hi[0], plan->blk_lo[1], plan->blk_hi[1],
-      plan->inv_norm[0], plan->inv_norm[1], plan->max_blocks, z);
-  ZB_CHECK_LAUNCH("kw_block_energy_kernel");
-  loudness_trim_kernel<<<batch, LT_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, n_blocks, plan->max_blocks, z,
-                                                     plan->target_lufs, plan->trim_threshold, bounds, lufs, gain);
+                                                        nullptr, s_in, plan->edges[0], plan->edges[1],
+                                                        plan->n_edges[0], plan->n_edges[1], part, seg0);
+  ZB_CHECK_LAUNCH("kw_chunk_kernel<energy>");
+  const int max_edges = plan->n_edges[0] > plan->n_edges[1] ? plan->n_edges[0] : plan->n_edges[1];
+  kw_segment_sum_kernel<<<dim3(ceil_div(max_edges, 128), batch), 128, 0, st>>>(
+      n_samples, blk_sel, plan->chunk, w.chunks_pitch, plan->edges[0], plan->edges[1], plan->n_edges[0],
+      plan->n_edges[1], part, seg0, w.seg_pitch, seg_sum);
+  ZB_CHECK_LAUNCH("kw_segment_sum_kernel");
+  loudness_trim_kernel<<<batch, LT_THREADS, 0, st>>>(
+      wav, pitch, n_samples, blk_sel, n_blocks, plan->max_blocks, plan->blk_lo[0], plan->blk_hi[0], plan->blk_lo[1],
+      plan->blk_hi[1], plan->inv_norm[0], plan->inv_norm[1], seg_sum, w.seg_pitch, z, plan->target_lufs,
+      plan->trim_threshold, bounds, lufs, gain);
   ZB_CHECK_LAUNCH("loudness_trim_kernel");
   const int ap_tile = AP_THREADS * AP_VEC_PER_THREAD * 4;
   const dim3 ap_grid((unsigned)((pitch + ap_tile - 1) / ap_tile), batch);

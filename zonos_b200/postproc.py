@@ -17,6 +17,7 @@ from . import _lib
 TRIM_FRAME = 512
 FADE_BLOCK = 512
 FADE_MAX_BLOCKS = 20
+MAX_PIECES = 8  # KW_MAX_PIECES in csrc/postproc.cu: segments one chunk may touch
 
 
 class PostprocPlan(ctypes.Structure):
@@ -28,6 +29,8 @@ class PostprocPlan(ctypes.Structure):
         ("chunk", ctypes.c_int32),
         ("max_blocks", ctypes.c_int32),
         ("chunk_transition", ctypes.c_double * 16),
+        ("edges", ctypes.c_void_p * 2),
+        ("n_edges", ctypes.c_int32 * 2),
         ("blk_lo", ctypes.c_void_p * 2),
         ("blk_hi", ctypes.c_void_p * 2),
         ("inv_norm", ctypes.c_double * 2),
@@ -89,6 +92,23 @@ def block_bounds(block_size: float, rate: int, count: int):
     return lo, hi
 
 
+def edge_tables(lo, hi):
+    """Sorted distinct block edges and, per block, its [first, last) segment indices (segment s = [edges[s], edges[s+1])).
+    Overlapping blocks then share the per-segment sums of squares."""
+    edges = sorted(set(lo) | set(hi))
+    index = {e: i for i, e in enumerate(edges)}
+    return edges, [index[v] for v in lo], [index[v] for v in hi]
+
+
+def max_pieces(edges, chunk: int) -> int:
+    """Largest number of segments any aligned chunk of `chunk` samples touches."""
+    e = np.asarray(edges)
+    starts = np.arange(0, e[-1] + chunk, chunk)
+    first = np.searchsorted(e, starts, side="right")
+    last = np.searchsorted(e, starts + chunk - 1, side="right")
+    return int((last - first).max()) + 1
+
+
 class WavPostprocessor:
     """Batched normalize_loudness + trim_silence + fades.  `run` takes a padded fp32 [B, pitch] device buffer and the
     valid sample count of each row."""
@@ -115,9 +135,12 @@ class WavPostprocessor:
         count = max(128, 1 << (need - 1).bit_length())
         tabs = []
         for bs in self.BLOCK_SIZES:
-            lo, hi = block_bounds(bs, self.rate, count)
-            tabs.append((torch.tensor(lo, dtype=torch.int32, device=self.device),
-                         torch.tensor(hi, dtype=torch.int32, device=self.device)))
+            edges, e_lo, e_hi = edge_tables(*block_bounds(bs, self.rate, count))
+            assert edges[0] == 0 and len(edges) <= 2 * count + 2
+            if max_pieces(edges, self.chunk) > MAX_PIECES:
+                raise ValueError(f"chunk {self.chunk} spans more than {MAX_PIECES} gating-block segments at "
+                                 f"{self.rate} Hz / {bs} s blocks; use a smaller chunk")
+            tabs.append(tuple(torch.tensor(v, dtype=torch.int32, device=self.device) for v in (edges, e_lo, e_hi)))
         self._tables, self._max_blocks = tabs, count
 
     def _plan(self, no_fades: bool) -> PostprocPlan:
@@ -127,8 +150,9 @@ class WavPostprocessor:
         p.chunk, p.max_blocks = self.chunk, self._max_blocks
         p.chunk_transition[:] = list(self._transition.reshape(-1))
         for k in range(2):
-            p.blk_lo[k] = self._tables[k][0].data_ptr()
-            p.blk_hi[k] = self._tables[k][1].data_ptr()
+            p.edges[k], p.n_edges[k] = self._tables[k][0].data_ptr(), self._tables[k][0].numel()
+            p.blk_lo[k] = self._tables[k][1].data_ptr()
+            p.blk_hi[k] = self._tables[k][2].data_ptr()
             p.inv_norm[k] = 1.0 / (self.BLOCK_SIZES[k] * self.rate)
         p.fade_in, p.fade_out = self.fade_in.data_ptr(), self.fade_out.data_ptr()
         p.target_lufs, p.trim_threshold, p.flags = self.target_lufs, 1e-5, int(no_fades)
