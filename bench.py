@@ -237,12 +237,23 @@ def dac_section(device, batch, frames):
     ms, ms_e2e = e0.elapsed_time(e1) / reps, e1.elapsed_time(e2) / reps
     flops = 1608302592 * batch * frames  # conv MACs x 2 per code frame (DAC layer table)
     audio_s = batch * frames / FRAME_RATE
-    del ae
+    # the public call one level up: host codes -> decode -> loudness / trim / fades -> list of host waveforms
+    ae.codes_to_wavs(codes_host)
+    t0 = time.perf_counter()
+    wavs = ae.codes_to_wavs(codes_host)
+    torch.cuda.synchronize()
+    c2w_s = time.perf_counter() - t0
+    c2w_len = sum(w.shape[1] for w in wavs)
+    del ae, wavs
     return {"workload": f"DAC 44.1 kHz decode, batch {batch} x {frames} frames", "ms": round(ms, 1),
             "audio_s_per_s": round(audio_s / (ms * 1e-3), 1), "e2e_audio_s_per_s": round(audio_s / (ms_e2e * 1e-3), 1),
             "tflops": round(flops / ms / 1e9, 1), "bound": "tensor",
             "frac_of_sustained_bf16_peak": None if tf_peak is None else round(flops / ms / 1e9 / tf_peak, 4),
-            "launches": 31 * reps * 2, "finite": bool(torch.isfinite(wav_host).all())}
+            "launches": 31 * reps * 2, "finite": bool(torch.isfinite(wav_host).all()),
+            "codes_to_wavs": {"ms": round(c2w_s * 1e3, 1), "audio_s_per_s": round(audio_s / c2w_s, 1),
+                              "kept_samples": int(c2w_len),
+                              "note": "DACAutoencoder.codes_to_wavs(host codes): decode + post-processing, "
+                                      "waveforms copied to pinned host memory"}}
 
 
 def postproc_section(device, hbm_peak, batch, frames, cpu_utts=2, chunk=None):

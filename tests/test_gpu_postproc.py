@@ -11,7 +11,7 @@ from oracle import shapes
 pytestmark = pytest.mark.gpu
 
 # Loudness is a floating-point path: the oracle sums float32 squares pairwise (numpy), the kernel in fp64, and the
-# K-weighted signal is stitched from 2048-sample chunks; both effects are ~1e-7 relative on the block energies.
+# K-weighted signal is stitched from 1024-sample chunks; both effects are ~1e-7 relative on the block energies.
 LUFS_TOL_DB = 1e-4
 # The gain enters every output sample once: 1e-4 dB is 1.2e-5 relative; measured deviations are a few fp32 ulps.
 WAV_RTOL = 2e-5
@@ -80,7 +80,7 @@ def test_silent_utterance_follows_the_reference_into_infinity():
 
 
 def test_long_utterance_many_chunks():
-    """12 s of audio: 259 chunks of 2048 per utterance, > 100 gating blocks; loudness within 1e-4 dB of the oracle."""
+    """12 s of audio: 517 chunks of 1024 per utterance, > 100 gating blocks; loudness within 1e-4 dB of the oracle."""
     g = torch.Generator().manual_seed(5)
     n = [44100 * 12 + 123, 44100 * 7]
     t = torch.arange(n[0], dtype=torch.float64) / 44100

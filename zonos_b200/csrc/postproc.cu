@@ -4,7 +4,8 @@
 //
 // The only sequential part is the K-weighting IIR (two cascaded biquads).  It is split into chunks of `chunk` samples:
 //   1. kw_chunk<state>: every chunk filtered from a zero state -> its end state (one thread per chunk, fp64)
-//   2. kw_chunk_scan:   s_in[c+1] = M^chunk s_in[c] + s_end[c]            (one warp per utterance)
+//   2. kw_chunk_scan:   s_in[c+1] = M^chunk s_in[c] + s_end[c]            (one warp per utterance, 32 chunks per
+//                       5-step warp scan)
 //   3. kw_chunk<energy>: every chunk filtered again from its true start state; the K-weighted sample is rounded to
 //                       fp32 (pyloudnorm filters in place in the float32 input array), squared, and summed per
 //                       SEGMENT -- the pieces between consecutive gating-block edges that fall inside the chunk
@@ -25,9 +26,6 @@ namespace {
 struct KwCoef {
   double b0a, b1a, b2a, a1a, a2a;
   double b0b, b1b, b2b, a1b, a2b;
-};
-struct KwMat {
-  double m[16];
 };
 
 // One sample through both transposed direct-form-II biquads (scipy.signal.lfilter's structure).  pyloudnorm writes the
@@ -153,16 +151,31 @@ __device__ __forceinline__ double shfl_f64(double v, int src) {
   return __hiloint2double(hi, lo);
 }
 
-// One warp per utterance.  Each lane holds the zero-state end state of one chunk; the warp walks 32 chunks at a time,
-// every lane carrying the same running state, and lane k keeps the state that enters chunk base + k.
+struct KwPow {
+  double m[6][16];  // M^1, M^2, M^4, M^8, M^16, M^32 with M the transition over one chunk (row-major 4x4)
+};
+
+__device__ __forceinline__ void kw_matvec_acc(const double* __restrict__ m, const double (&v)[4], double (&acc)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    double t = acc[i];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) t = fma(m[i * 4 + j], v[j], t);
+    acc[i] = t;
+  }
+}
+
+// One warp per utterance: s_in[c + 1] = M s_in[c] + s_end[c].  32 chunks at a time, one per lane, as an inclusive
+// Hillis-Steele scan of the affine recurrence (step k adds M^(2^k) times the value 2^k lanes below); the state entering
+// the group rides in lane 0's element, the last lane's result enters the next group.
 __global__ void __launch_bounds__(32)
 kw_chunk_scan_kernel(const int32_t* __restrict__ n_samples, const int32_t* __restrict__ blk_sel, int chunk,
-                     int chunks_pitch, KwMat M, const double* __restrict__ s_end, double* __restrict__ s_in) {
+                     int chunks_pitch, KwPow P, const double* __restrict__ s_end, double* __restrict__ s_in) {
   const int b = blockIdx.x, lane = threadIdx.x;
   if (blk_sel[b] < 0) return;
   const int n = n_samples[b];
   const int n_chunks = (n + chunk - 1) / chunk;
-  double s[4] = {0.0, 0.0, 0.0, 0.0};
+  double sb[4] = {0.0, 0.0, 0.0, 0.0};  // state entering chunk `base`
   for (int base = 0; base < n_chunks; base += 32) {
     const int c = base + lane;
     double e[4] = {0.0, 0.0, 0.0, 0.0};
@@ -171,28 +184,28 @@ kw_chunk_scan_kernel(const int32_t* __restrict__ n_samples, const int32_t* __res
 #pragma unroll
       for (int i = 0; i < 4; ++i) e[i] = p[i];
     }
-    double mine[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int k = 0; k < 32; ++k) {
-      if (lane == k) {
+    if (lane == 0) {
+      double* q = s_in + ((int64_t)b * chunks_pitch + base) * 4;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) mine[i] = s[i];
-      }
+      for (int i = 0; i < 4; ++i) q[i] = sb[i];
+      kw_matvec_acc(P.m[0], sb, e);
+    }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const int d = 1 << k;
       double t[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        double acc = shfl_f64(e[i], k);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc = fma(M.m[i * 4 + j], s[j], acc);
-        t[i] = acc;
-      }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) s[i] = t[i];
+      for (int i = 0; i < 4; ++i) t[i] = shfl_f64(e[i], lane >= d ? lane - d : lane);
+      if (lane >= d) kw_matvec_acc(P.m[k], t, e);
     }
-    if (c < n_chunks) {
-      double* p = s_in + ((int64_t)b * chunks_pitch + c) * 4;
+    // e = state after chunk c = state entering chunk c + 1
+    if (lane < 31 && c + 1 < n_chunks) {
+      double* q = s_in + ((int64_t)b * chunks_pitch + c + 1) * 4;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) p[i] = mine[i];
+      for (int i = 0; i < 4; ++i) q[i] = e[i];
     }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) sb[i] = shfl_f64(e[i], 31);
   }
 }
 
@@ -404,8 +417,15 @@ extern "C" int zb200_codes_postprocess(const zb200_postproc_plan* plan, const fl
   c.a1a = plan->shelf_a[1]; c.a2a = plan->shelf_a[2];
   c.b0b = plan->hp_b[0]; c.b1b = plan->hp_b[1]; c.b2b = plan->hp_b[2];
   c.a1b = plan->hp_a[1]; c.a2b = plan->hp_a[2];
-  KwMat M;
-  for (int i = 0; i < 16; ++i) M.m[i] = plan->chunk_transition[i];
+  KwPow P;
+  for (int i = 0; i < 16; ++i) P.m[0][i] = plan->chunk_transition[i];
+  for (int k = 1; k < 6; ++k)  // squares: M^(2^k)
+    for (int i = 0; i < 4; ++i)
+      for (int j = 0; j < 4; ++j) {
+        double t = 0.0;
+        for (int l = 0; l < 4; ++l) t += P.m[k - 1][i * 4 + l] * P.m[k - 1][l * 4 + j];
+        P.m[k][i * 4 + j] = t;
+      }
   char* wsb = static_cast<char*>(ws);
   double* s_end = reinterpret_cast<double*>(wsb + w.s_end);
   double* s_in = reinterpret_cast<double*>(wsb + w.s_in);
@@ -418,7 +438,7 @@ extern "C" int zb200_codes_postprocess(const zb200_postproc_plan* plan, const fl
   kw_chunk_kernel<false><<<kw_grid, KW_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, plan->chunk, w.chunks_pitch,
                                                          c, s_end, nullptr, nullptr, nullptr, 0, 0, nullptr, nullptr);
   ZB_CHECK_LAUNCH("kw_chunk_kernel<state>");
-  kw_chunk_scan_kernel<<<batch, 32, 0, st>>>(n_samples, blk_sel, plan->chunk, w.chunks_pitch, M, s_end, s_in);
+  kw_chunk_scan_kernel<<<batch, 32, 0, st>>>(n_samples, blk_sel, plan->chunk, w.chunks_pitch, P, s_end, s_in);
   ZB_CHECK_LAUNCH("kw_chunk_scan_kernel");
   kw_chunk_kernel<true><<<kw_grid, KW_THREADS, 0, st>>>(wav, pitch, n_samples, blk_sel, plan->chunk, w.chunks_pitch, c,
                                                         nullptr, s_in, plan->edges[0], plan->edges[1],

@@ -115,7 +115,7 @@ class WavPostprocessor:
 
     BLOCK_SIZES = (0.400, 0.100)
 
-    def __init__(self, device, rate: int = 44100, target_lufs: float = -23.0, chunk: int = 2048):
+    def __init__(self, device, rate: int = 44100, target_lufs: float = -23.0, chunk: int = 1024):
         self.device = torch.device(device)
         self.rate = rate
         self.chunk = chunk
