@@ -204,9 +204,10 @@ def attn_roofline(shape, batch, ctx, device, hbm_peak):
             "bytes_per_launch": algo, "ms_per_launch": round(ms, 5), "ctx": ctx, "nsplit": nsplit}
 
 
-def dac_section(device, batch, frames):
+def dac_section(device, batch, frames, world=1):
     """BASELINE configs[3] (C4): DACAutoencoder.decode of `batch` x `frames` synthetic codes -> fp32 waveforms, device
-    resident and end to end (codes from pinned host memory, waveform back to the host)."""
+    resident and end to end (codes from pinned host memory, waveform back to the host).  world > 1: every rank decodes
+    its own batch (utterances are independent: no collective), times are the max over ranks, audio is the sum."""
     from oracle import shapes as oshapes  # synthetic weights only (the decoder under test is the CUDA one)
     from zonos_b200.autoencoder import DACAutoencoder
 
@@ -225,6 +226,7 @@ def dac_section(device, batch, frames):
     torch.cuda.synchronize()
     e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
     reps = 3
+    barrier(world)
     e0.record()
     for _ in range(reps):
         wav = ae.decode(codes)
@@ -234,9 +236,19 @@ def dac_section(device, batch, frames):
         wav_host.copy_(wav, non_blocking=True)
     e2.record()
     torch.cuda.synchronize()
-    ms, ms_e2e = e0.elapsed_time(e1) / reps, e1.elapsed_time(e2) / reps
-    flops = 1608302592 * batch * frames  # conv MACs x 2 per code frame (DAC layer table)
-    audio_s = batch * frames / FRAME_RATE
+    ms = max_over_ranks(e0.elapsed_time(e1) / reps, world, device)
+    ms_e2e = max_over_ranks(e1.elapsed_time(e2) / reps, world, device)
+    flops = 1608302592 * batch * frames * world  # conv MACs x 2 per code frame (DAC layer table)
+    audio_s = world * batch * frames / FRAME_RATE
+    if world > 1:
+        finite = bool(torch.isfinite(wav_host).all())
+        del ae
+        return {"workload": f"DAC 44.1 kHz decode, batch {batch} x {frames} frames per GPU, {world} GPUs", "ms": round(ms, 1),
+                "audio_s_per_s": round(audio_s / (ms * 1e-3), 1),
+                "e2e_audio_s_per_s": round(audio_s / (ms_e2e * 1e-3), 1), "tflops": round(flops / ms / 1e9, 1),
+                "bound": "tensor", "frac_of_sustained_bf16_peak":
+                    None if tf_peak is None else round(flops / ms / 1e9 / tf_peak / world, 4),
+                "launches": 31 * reps * 2, "finite": finite}
     # the public call one level up: host codes -> decode -> loudness / trim / fades -> list of host waveforms
     ae.codes_to_wavs(codes_host)
     t0 = time.perf_counter()
@@ -539,6 +551,7 @@ def main_b200(args, world, rank, local):
     ms_e2e = max_over_ranks(e0.elapsed_time(e1), world, device)
     total_frames_e2e = sum_over_ranks(frames_e2e, world, device)
     clk = clocks.stop() if rank == 0 else None
+    dac_multi = dac_section(device, B, args.max_new_tokens, world) if world > 1 and not args.no_dac else None
 
     if rank != 0:
         return
@@ -573,6 +586,8 @@ def main_b200(args, world, rank, local):
     torch.cuda.empty_cache()
     if world == 1 and not args.no_dac:
         line["dac_decode"] = dac_section(device, B, args.max_new_tokens)
+    elif dac_multi is not None:
+        line["dac_decode"] = dac_multi
     if world == 1 and not args.no_mamba:
         line["hybrid_mamba2"] = mamba2_section(device, hbm_peak)
         torch.cuda.empty_cache()
