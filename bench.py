@@ -551,9 +551,12 @@ def main_b200(args, world, rank, local):
     ms_e2e = max_over_ranks(e0.elapsed_time(e1), world, device)
     total_frames_e2e = sum_over_ranks(frames_e2e, world, device)
     clk = clocks.stop() if rank == 0 else None
-    dac_multi = dac_section(device, B, args.max_new_tokens, world) if world > 1 and not args.no_dac else None
 
     if rank != 0:
+        if not args.no_dac:  # C4 sharded: every rank decodes its own batch once the model's memory is released
+            del model
+            torch.cuda.empty_cache()
+            dac_section(device, B, args.max_new_tokens, world)
         return
     value = total_frames / FRAME_RATE / (ms_dev * 1e-3)
     e2e = total_frames_e2e / FRAME_RATE / (ms_e2e * 1e-3)
@@ -586,8 +589,8 @@ def main_b200(args, world, rank, local):
     torch.cuda.empty_cache()
     if world == 1 and not args.no_dac:
         line["dac_decode"] = dac_section(device, B, args.max_new_tokens)
-    elif dac_multi is not None:
-        line["dac_decode"] = dac_multi
+    elif not args.no_dac:
+        line["dac_decode"] = dac_section(device, B, args.max_new_tokens, world)
     if world == 1 and not args.no_mamba:
         line["hybrid_mamba2"] = mamba2_section(device, hbm_peak)
         torch.cuda.empty_cache()

@@ -176,14 +176,23 @@ kw_chunk_scan_kernel(const int32_t* __restrict__ n_samples, const int32_t* __res
   const int n = n_samples[b];
   const int n_chunks = (n + chunk - 1) / chunk;
   double sb[4] = {0.0, 0.0, 0.0, 0.0};  // state entering chunk `base`
+  auto load_end = [&](int c, double (&v)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = 0.0;
+    if (c < n_chunks - 1) {
+      const double2* p = reinterpret_cast<const double2*>(s_end + ((int64_t)b * chunks_pitch + c) * 4);
+      const double2 lo = p[0], hi = p[1];
+      v[0] = lo.x; v[1] = lo.y; v[2] = hi.x; v[3] = hi.y;
+    }
+  };
+  double nxt[4];
+  load_end(lane, nxt);
   for (int base = 0; base < n_chunks; base += 32) {
     const int c = base + lane;
-    double e[4] = {0.0, 0.0, 0.0, 0.0};
-    if (c < n_chunks - 1) {
-      const double* p = s_end + ((int64_t)b * chunks_pitch + c) * 4;
+    double e[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) e[i] = p[i];
-    }
+    for (int i = 0; i < 4; ++i) e[i] = nxt[i];
+    load_end(c + 32, nxt);  // the next group's end states travel while this group is scanned
     if (lane == 0) {
       double* q = s_in + ((int64_t)b * chunks_pitch + base) * 4;
 #pragma unroll
