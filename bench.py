@@ -383,31 +383,39 @@ def mamba2_section(device, hbm_peak, rows=64, n_layers=40):
                                  "note": "host-sequenced kernels in a torch CUDA graph; attention layers and the C-side engine are not built yet"},
            "finite": bool(torch.isfinite(out).all())}
     del stack, states, graph
-    # (3) Zonos.generate on a random-init hybrid model of the recalled Zonos-v0.1-hybrid shape, batch 32 (C5-like), through
-    # zonos_b200.hybrid.ZonosHybridB200 (decode step replayed from a torch CUDA graph); marginal cost of a frame
+    res["generate_c5_like"] = hybrid_generate_section(device)
+    return res
+
+
+def hybrid_generate_section(device, world=1):
+    """BASELINE configs[4]-like: Zonos.generate on a random-init hybrid model of the recalled Zonos-v0.1-hybrid shape,
+    batch 32 per GPU, through zonos_b200.hybrid.ZonosHybridB200 (decode step replayed from a torch CUDA graph); the
+    marginal cost of a frame.  world > 1: every rank generates its own batch (no collective), times are the max over
+    ranks, audio is the sum."""
     from zonos_b200 import synth
 
     model = synth.hybrid_model(device=device)
-    cond = synth.conditioning(32, 128, d, device=device, seed=1)
+    cond = synth.conditioning(32, 128, 2048, device=device, seed=1)
 
     def gen(n_new):
         torch.cuda.synchronize(device)
+        barrier(world)
         t0 = time.perf_counter()
         out = model.generate(cond, None, max_new_tokens=n_new, batch_size=32, sampling_params=C3_SAMPLING, seed=1234)
         torch.cuda.synchronize(device)
-        return time.perf_counter() - t0, out
+        return max_over_ranks(time.perf_counter() - t0, world, device), out
 
     gen(16)
     t_a, _ = gen(128)
     t_b, out = gen(512)
     per_frame = (t_b - t_a) / (512 - 128)
-    res["generate_c5_like"] = {"workload": "hybrid Zonos.generate, recalled v0.1-hybrid shape (46 blocks, attention + GatedMLP every 9th), "
-                                           "random-init, batch 32, L_cond 128, min_p 0.1 + rep. penalty 3.0, cfg 2.0",
-                               "ms_per_frame": round(per_frame * 1e3, 3), "audio_s_per_s": round(32 / per_frame / FRAME_RATE, 1),
-                               "e2e_audio_s_per_s_512_frames": round(sum(o.shape[1] for o in out) / FRAME_RATE / t_b, 1),
-                               "note": "host-sequenced C-ABI kernels, decode step replayed from a torch CUDA graph; no C-side engine yet"}
+    frames = sum_over_ranks(float(sum(o.shape[1] for o in out)), world, device)
     del model
-    return res
+    return {"workload": "hybrid Zonos.generate, recalled v0.1-hybrid shape (46 blocks, attention + GatedMLP every 9th), "
+                        f"random-init, batch 32 per GPU, {world} GPU(s), L_cond 128, min_p 0.1 + rep. penalty 3.0, cfg 2.0",
+            "ms_per_frame": round(per_frame * 1e3, 3), "audio_s_per_s": round(world * 32 / per_frame / FRAME_RATE, 1),
+            "e2e_audio_s_per_s_512_frames": round(frames / FRAME_RATE / t_b, 1),
+            "note": "host-sequenced C-ABI kernels, decode step replayed from a torch CUDA graph; no C-side engine yet"}
 
 
 def latency_batch1(model, shape, args, device, hbm_peak):
@@ -557,6 +565,9 @@ def main_b200(args, world, rank, local):
             del model
             torch.cuda.empty_cache()
             dac_section(device, B, args.max_new_tokens, world)
+        if not args.no_mamba:  # C5-like sharded the same way
+            torch.cuda.empty_cache()
+            hybrid_generate_section(device, world)
         return
     value = total_frames / FRAME_RATE / (ms_dev * 1e-3)
     e2e = total_frames_e2e / FRAME_RATE / (ms_e2e * 1e-3)
@@ -594,6 +605,9 @@ def main_b200(args, world, rank, local):
     if world == 1 and not args.no_mamba:
         line["hybrid_mamba2"] = mamba2_section(device, hbm_peak)
         torch.cuda.empty_cache()
+    elif not args.no_mamba:
+        torch.cuda.empty_cache()
+        line["hybrid_mamba2"] = {"generate_c5_like": hybrid_generate_section(device, world)}
     if world == 1 and not args.no_dac:
         line["postprocess"] = postproc_section(device, hbm_peak, B, args.max_new_tokens)
         torch.cuda.empty_cache()
