@@ -145,3 +145,28 @@ def test_rejects_bad_arguments():
     with pytest.raises(ValueError):
         _lib.check(_lib.lib().zb200_codes_postprocess(ctypes.byref(plan), z, ctypes.c_int64(1024), z, z, z, 1, 1024, z,
                                                       z, z, z, z, ctypes.c_int64(0), z), "codes_postprocess")
+
+
+def test_save_codes_and_batched_tensor_form(tmp_path):
+    """codes as one [B, 9, T] tensor (one batched decode), waveforms kept on the device, and save_codes' files."""
+    from zonos_b200.autoencoder import DACAutoencoder
+
+    ae = DACAutoencoder().to("cuda")
+    ae.load_dac_state_dict(shapes.synth_dac_weights(seed=7, arch=shapes.DAC_TINY))
+    codes = torch.randint(0, 1024, (3, 9, 25), generator=torch.Generator().manual_seed(2))
+    on_dev = ae.codes_to_wavs(codes.cuda(), device_output=True)
+    on_host = ae.codes_to_wavs(codes)
+    assert len(on_dev) == 3 and all(w.is_cuda for w in on_dev)
+    for d, h, c in zip(on_dev, on_host, codes):
+        assert torch.equal(d.cpu(), h)
+        ref = opp.post(ae.decode(c[None].cuda()).cpu().squeeze(0))
+        torch.testing.assert_close(h, ref["wav"], rtol=WAV_RTOL, atol=1e-9)
+    paths = [str(tmp_path / f"u{i}.wav") for i in range(3)]
+    ae.save_codes(paths, codes)
+    for p, h in zip(paths, on_host):
+        raw = open(p, "rb").read()
+        assert raw[:4] == b"RIFF" and np.array_equal(np.frombuffer(raw[44:], dtype="<f4"), h[0].numpy())
+    with pytest.raises(AssertionError):
+        ae.save_codes(paths[:2], codes)
+    with pytest.raises(ValueError):
+        ae.codes_to_wavs(torch.zeros(2, 2, 9, 4, dtype=torch.long))
