@@ -616,6 +616,11 @@ def main_b200(args, world, rank, local):
         gen, dac = line["e2e"]["value"], line["dac_decode"]["e2e_audio_s_per_s"]
         line["e2e_waveform"] = {"value": round(1.0 / (1.0 / gen + 1.0 / dac), 2), "unit": "audio-s/s",
                                 "note": "generate (host conditioning in) + DAC decode (waveform to host), sequential"}
+        c2w = line["dac_decode"].get("codes_to_wavs", {}).get("audio_s_per_s")
+        if c2w:
+            line["e2e_wavs"] = {"value": round(1.0 / (1.0 / gen + 1.0 / c2w), 2), "unit": "audio-s/s",
+                                "note": "generate + codes_to_wavs (decode, loudness normalisation, trim, fades; "
+                                        "waveforms to host), sequential"}
     if world == 1 and not args.no_cpu_baseline:
         frames = args.cpu_frames
         v, dt, cores = cpu_reference_sample(frames, args.shape)
