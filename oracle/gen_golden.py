@@ -130,7 +130,14 @@ MODEL_CASES = {
 }
 
 
-def gen_model(model, shape):
+# The real (Zonos-v0.1-transformer) shape: one short case, so that the 26-layer d=2048 engine is pinned to the reference
+# itself and not only to the oracle port (the port is then checked against this file on CPU, the engine on the GPU).
+MODEL_CASES_REAL = {
+    "real_b2_greedy_prefix": (2, 9, 3, 6, sc.GREEDY, 2.0),
+}
+
+
+def gen_model(model, shape, cases=None):
     """G2-G4 + G7: embed, prefill logits, teacher-forced decode logits, free-running generate."""
     W = shapes.synth_transformer_weights(shape, seed=0)
     d = shapes.SHAPES[shape]["d_model"]
@@ -139,7 +146,7 @@ def gen_model(model, shape):
     ids = torch.randint(0, 1026, (2, 9, 6), generator=g)
     out["embed"] = dict(ids=ids, out=model.embed_codes(ids))
 
-    for name, (B, Lc, P, N, sp, cfg) in MODEL_CASES.items():
+    for name, (B, Lc, P, N, sp, cfg) in (MODEL_CASES if cases is None else cases).items():
         cond = shapes.synth_conditioning(B, Lc, d, seed=1)
         pre = None if P == 0 else torch.randint(0, 1024, (B, 9, P), generator=torch.Generator().manual_seed(2))
         logit_log = []
@@ -211,10 +218,34 @@ def gen_postproc():
     torch.save(out, os.path.join(OUT, "postproc.pt"))
 
 
+def gen_model_real():
+    """Real-shape model file: the reference's bf16 logits, plus the same prefill in fp32 (oracle port, which the CPU test
+    pins bit-exactly to the reference at this shape): |bf16 reference - fp32| is the reference's own rounding noise, the
+    yardstick for the 26-layer gates."""
+    from . import delay as odelay
+    from . import generate as ogen
+
+    gen_model(build_reference_model("real"), "real", MODEL_CASES_REAL)
+    path = os.path.join(OUT, "model_real.pt")
+    g = torch.load(path, weights_only=False)
+    for name, (B, Lc, P, N, sp, cfg) in MODEL_CASES_REAL.items():
+        W32 = {k: v.float() for k, v in shapes.synth_transformer_weights("real", seed=0).items()}
+        cond = shapes.synth_conditioning(B, Lc, 2048, seed=1).float()
+        codes = torch.full((B, 9, P + N), -1, dtype=torch.int64)
+        codes[..., :P] = torch.randint(0, 1024, (B, 9, P), generator=torch.Generator().manual_seed(2))
+        src = ogen.ModelLogits(W32, "real", cond, Lc + P + N + 9, cfg)
+        g["cases"][name]["logits_fp32_prefill"] = src.prefill(odelay.apply_delay_pattern(codes, 1025)[..., :P + 1])
+    torch.save(g, path)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     import_reference()
     torch.set_grad_enabled(False)
+    if "--real" in sys.argv:  # only the real-shape model file (builds the 1.6 B-parameter reference model on the CPU)
+        gen_model_real()
+        print("model_real.pt", os.path.getsize(os.path.join(OUT, "model_real.pt")))
+        return
     gen_delay()
     gen_sampler()
     model = build_reference_model("tiny")

@@ -101,6 +101,30 @@ def test_embed_and_logits_tiny(golden):
         ids = case["frames"][..., s - 1:s]
 
 
+def test_logits_real_shape_vs_reference(golden):
+    """The oracle port at the REAL shape (26 layers, d = 2048, 16/4 heads) against logits the unmodified reference
+    produced on the same seeded weights (tests/golden/model_real.pt, `python -m oracle.gen_golden --real`): prefill +
+    5 teacher-forced decode frames, bit-exact like the tiny cases."""
+    from oracle.gen_golden import MODEL_CASES_REAL
+
+    g = golden("model_real.pt")
+    W = shapes.synth_transformer_weights("real", seed=0)
+    assert weights_checksum(W) == pytest.approx(g["weights_checksum"], rel=1e-9)
+    (name, (B, Lc, P, N, sp, cfg)), = MODEL_CASES_REAL.items()
+    case = g["cases"][name]
+    cond = shapes.synth_conditioning(B, Lc, 2048, seed=1)
+    pre = torch.randint(0, 1024, (B, 9, P), generator=torch.Generator().manual_seed(2))
+    codes = torch.full((B, 9, P + N), -1, dtype=torch.int64)
+    codes[..., :P] = pre
+    delayed = odelay.apply_delay_pattern(codes, 1025)
+    src = ogen.ModelLogits(W, "real", cond, Lc + P + N + 9, cfg)
+    assert torch.equal(src.prefill(delayed[..., :P + 1]), case["logits"][0])
+    ids = torch.where(delayed[..., P + 1:P + 2] == -1, case["logits"][0].argmax(-1, keepdim=True), delayed[..., P + 1:P + 2])
+    for s in range(1, 6):
+        assert torch.equal(src.step(ids), case["logits"][s])
+        ids = case["frames"][..., s - 1:s]
+
+
 def test_dac_decode(golden):
     g = golden("dac.pt")
     for arch_name, arch in (("tiny", shapes.DAC_TINY), ("real", shapes.DAC)):

@@ -181,6 +181,30 @@ class Zonos(nn.Module):
         finally:
             eng.close()
 
+    def _debug_forced_decode_logits(self, prefix_conditioning, audio_prefix_codes, cfg_scale, first_frame, frames,
+                                    max_new_tokens):
+        """Test hook: teacher forcing.  After the prefill, `first_frame` [B, 9, 1] and then the columns of `frames`
+        [B, 9, n] are written into the delayed-code matrix (only where it is still unknown, like model.py:307-314 /
+        :417-418) instead of sampled tokens, and the decode step's CFG logits are returned for each of the n + 1 steps."""
+        B = prefix_conditioning.shape[0] // 2
+        loop, eng, delayed = self._open_session(prefix_conditioning, audio_prefix_codes, max_new_tokens, cfg_scale, B,
+                                                None, 0, 0, None)
+        out = []
+        try:
+            forced = torch.cat([first_frame, frames], dim=-1).to(device=self.device, dtype=torch.int32)
+            col = loop.first_offset
+            for s in range(forced.shape[-1]):
+                cell = delayed[..., col + s]
+                delayed[..., col + s] = torch.where(cell == UNKNOWN_ID, forced[..., s], cell)
+                eng.decode_logits()  # embeds column state[ST_OFFSET] - 1 at position state[ST_POS]
+                out.append(eng.logits.clone())
+                loop.state[ST_OFFSET] += 1
+                loop.state[1] += 1  # ST_POS
+            torch.cuda.synchronize()
+            return out
+        finally:
+            eng.close()
+
     # ------------------------------------------------------------------------------------------------ generate
     @torch.inference_mode()
     def generate(
