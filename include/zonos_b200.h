@@ -96,6 +96,20 @@ int zb200_kv_write(const void* k, const void* v, void* pool, const int* block_ta
 int zb200_attn_decode(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,
                       int n_heads, int n_kv_heads, int layer, int n_seq, int n_keys, int nsplit, float* ws, int* tickets,
                       void* out, void* stream);
+/* Allocation-free variant of zb200_attn_decode.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same computation and arguments as zb200_attn_decode, minus ws / tickets: the split-KV scratch lives in a
+ * file-scope `static __device__` array of the library (csrc/attention.cu), 8.14 MiB that every GPU loading the library
+ * holds until exit.  The call performs no cudaMalloc / cudaFree / allocating library routine (one cudaMemsetAsync of the
+ * merge tickets on `stream`, and on the first call per device one cudaGetSymbolAddress).
+ * Limit: n_seq * n_kv_heads * nsplit <= ZB200_ATTN_NOALLOC_MAX_UNITS, otherwise ZB200_ERR_INVALID with a message that
+ * names the limit (use zb200_attn_decode with your own scratch then).
+ * All calls on a device share the one array, which keeps the last call's contents: calls that OVERLAP on the GPU
+ * (different streams, or graph branches without a dependency) race on it -- serialise them. */
+#define ZB200_ATTN_NOALLOC_MAX_UNITS 4096
+int zb200_attn_decode_noalloc(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,
+                              int n_heads, int n_kv_heads, int layer, int n_seq, int n_keys, int nsplit, void* out,
+                              void* stream);
 /* Causal prefill attention (_torch.py:136 with S > 1): query s of a sequence sees keys 0..pos0+s.
  * q/out bf16 [n_seq, seq_len, H*128]. */
 int zb200_attn_prefill(const void* q, const void* pool, const int* block_table, int pages_per_seq, int num_pages,

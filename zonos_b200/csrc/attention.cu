@@ -544,3 +544,78 @@ extern "C" int zb200_attn_prefill(const void* q, const void* pool, const int* bl
   ZB_CHECK_CUDA(launch_attn_prefill(a, n_seq, (cudaStream_t)stream));
   return ZB200_OK;
 }
+
+// ---------------------------------------------------------------------------------------------- allocation-free variant
+// zb200_attn_decode_noalloc: the split-KV decode attention with its scratch (split partials + merge tickets) in a
+// file-scope device array instead of caller-allocated buffers, for callers that cannot allocate (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the array (8.14 MiB) until exit.
+//
+// In HOST code the array's name is a host-side stand-in, not a device address (a kernel handed it faults or, where the
+// GPU can reach host memory, silently uses the wrong memory): the device address is resolved once per device, with that
+// device current, by cudaGetSymbolAddress below, and that pointer is what the kernel receives.
+namespace zb {
+constexpr int NOALLOC_MAX_UNITS = ZB200_ATTN_NOALLOC_MAX_UNITS;  // n_seq * n_kv_heads * nsplit
+constexpr int NOALLOC_UNIT_FLOATS = 520;                         // 4 heads x (128 + 2) floats per split partial
+constexpr int NOALLOC_MAX_DEVICES = 64;
+struct AttnNoallocScratch {
+  float partial[(size_t)NOALLOC_MAX_UNITS * NOALLOC_UNIT_FLOATS];
+  int tickets[NOALLOC_MAX_UNITS];
+};
+static __device__ __align__(256) AttnNoallocScratch g_attn_noalloc_scratch;
+
+}  // namespace zb
+
+#include <mutex>
+
+namespace {
+std::mutex g_noalloc_mu;
+zb::AttnNoallocScratch* g_noalloc_ptr[zb::NOALLOC_MAX_DEVICES] = {};  // device address per device ordinal
+
+// Device address of the scratch array on the CURRENT device (resolved on first use on that device).
+int noalloc_scratch(zb::AttnNoallocScratch** out) {
+  int dev = -1;
+  ZB_CHECK_CUDA(cudaGetDevice(&dev));
+  ZB_REQUIRE(dev >= 0 && dev < zb::NOALLOC_MAX_DEVICES, "attn_decode_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    zb::AttnNoallocScratch* p = nullptr;
+    ZB_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, zb::g_attn_noalloc_scratch));
+    ZB_REQUIRE(p != nullptr, "attn_decode_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return ZB200_OK;
+}
+}  // namespace
+
+extern "C" int zb200_attn_decode_noalloc(const void* q, const void* pool, const int* block_table, int pages_per_seq,
+                                         int num_pages, int n_heads, int n_kv_heads, int layer, int n_seq, int n_keys,
+                                         int nsplit, void* out, void* stream) {
+  using namespace zb;
+  ZB_REQUIRE(q && pool && block_table && out, "attn_decode_noalloc: null buffer");
+  ZB_REQUIRE(n_seq > 0 && n_keys > 0 && nsplit >= 1 && n_kv_heads > 0 && n_heads % n_kv_heads == 0 && n_heads / n_kv_heads <= 4,
+             "attn_decode_noalloc: bad shape (GQA group must be <= 4)");
+  ZB_REQUIRE(n_keys <= pages_per_seq * ZB200_PAGE, "attn_decode_noalloc: n_keys exceeds the block table");
+  const long long units = (long long)n_seq * n_kv_heads * nsplit;
+  ZB_REQUIRE(units <= NOALLOC_MAX_UNITS,
+             "attn_decode_noalloc: n_seq*n_kv_heads*nsplit = %lld exceeds the built-in scratch (ZB200_ATTN_NOALLOC_MAX_UNITS = %d); "
+             "use zb200_attn_decode with caller-allocated scratch",
+             units, NOALLOC_MAX_UNITS);
+  AttnNoallocScratch* s = nullptr;
+  const int rc = noalloc_scratch(&s);
+  if (rc != ZB200_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // The array is shared by every call and keeps the last call's contents.  The partials are fully overwritten before
+  // they are read; the merge tickets must start at zero (they reset themselves, but a call that was aborted half-way
+  // would leave them dirty), so they are cleared on the caller's stream -- a memset, not an allocation.
+  if (nsplit > 1) ZB_CHECK_CUDA(cudaMemsetAsync(s->tickets, 0, sizeof(int) * (size_t)n_seq * n_kv_heads, st));
+  AttnDecodeArgs a;
+  a.q = (const bf16*)q, a.out = (bf16*)out;
+  a.kv = make_kv((void*)pool, block_table, pages_per_seq, num_pages, n_kv_heads, layer);
+  a.pos_ptr = nullptr, a.pos_add = n_keys - 1, a.n_heads = n_heads, a.n_kv_heads = n_kv_heads;
+  a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
+  a.partial_ws = s->partial, a.tickets = s->tickets;
+  ZB_CHECK_CUDA(launch_attn_decode(a, n_seq, nsplit, st));
+  return ZB200_OK;
+}

@@ -190,6 +190,19 @@ def attn_decode(q: torch.Tensor, kv: PagedKV, layer: int, n_keys: int, n_heads: 
     return out
 
 
+ATTN_NOALLOC_MAX_UNITS = 4096  # ZB200_ATTN_NOALLOC_MAX_UNITS (include/zonos_b200.h)
+
+
+def attn_decode_noalloc(q: torch.Tensor, kv: PagedKV, layer: int, n_keys: int, n_heads: int, nsplit: int, out: torch.Tensor):
+    """zb200_attn_decode_noalloc: split-KV scratch in the library's built-in device array; this wrapper allocates nothing
+    either (q and out are the caller's CUDA bf16 tensors).  Calls that overlap on the GPU race on the shared scratch."""
+    assert q.is_cuda and out.is_cuda and q.dtype == out.dtype == torch.bfloat16 and q.is_contiguous() and out.is_contiguous()
+    check(lib().zb200_attn_decode_noalloc(ptr(q), ptr(kv.pool), ptr(kv.block_table), kv.pages_per_seq, kv.num_pages, n_heads,
+                                          kv.n_kv_heads, layer, q.shape[0], n_keys, nsplit, ptr(out), stream_ptr()),
+          "attn_decode_noalloc")
+    return out
+
+
 def attn_prefill(q: torch.Tensor, kv: PagedKV, layer: int, pos0: int, n_heads: int) -> torch.Tensor:
     q = _cuda(q, torch.bfloat16)
     n_seq, S = q.shape[:2]
