@@ -3,6 +3,7 @@
 // :181-202 (_prefill); zonos/backbone/_torch.py:73-80,99-102 (backbone / block forward).
 #include "../../include/zonos_b200.h"
 #include "attention.cuh"
+#include "chain.cuh"
 #include "common.cuh"
 #include "epilogues.cuh"
 #include "epilogues_t.cuh"
@@ -34,6 +35,7 @@ struct zb200_engine {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool forked = false;
+  unsigned long long* chain_trace = nullptr;  // debug timeline of the chain kernel (zb200_engine_set_chain_trace)
 };
 
 namespace {
@@ -325,6 +327,104 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
   return join_side(e, st);
 }
 
+// Decode step with rows = 2B <= 128 on the fused chain kernel (chain.cuh): one launch for everything between two
+// attention kernels.  Per frame: embedding sum, LayerNorm, [in_proj 0], then per layer attention + one chain launch
+// (out_proj, residual + norm2, fc1 + SwiGLU, fc2, residual + next norm, next in_proj -- heads + CFG after the last layer).
+// The chain launches' grid-barrier counters live in the upper half of gemm_tickets (zero-initialised by the shim): launch
+// j uses slot j and clears slot j - 1 (mod the launches of a frame), whose launch has completed by then.
+constexpr int CHAIN_SYNC_BASE = 512;  // ints: [0, 512) of gemm_tickets stay the ticketed phases' tile-pair tickets
+int run_decode_chain(zb200_engine* e, cudaStream_t st) {
+  const zb200_engine_desc& d = e->d;
+  const int dm = d.d_model, hd = d.n_heads * ZB200_HEAD_DIM, kvd = d.n_kv_heads * ZB200_HEAD_DIM;
+  const int rows = 2 * d.batch, sms = e->sk_sms, L = d.n_layer;
+  const int n_launches = L + 1;
+  const int* pos_ptr = d.state + ST_POS;
+  bf16 *x = (bf16*)d.x, *xn = (bf16*)d.xn, *q = (bf16*)d.q, *att = (bf16*)d.att, *h = (bf16*)d.h;
+
+  ChainArgs base{};
+  base.rows = rows, base.ws = d.gemm_ws, base.tickets = d.gemm_tickets, base.err = d.state + ST_ERROR;
+  base.x = x, base.xn = xn, base.q = q, base.d_model = dm, base.ln_eps = d.ln_eps;
+  base.kv = kv_of(d, 0), base.rope = d.rope, base.pos_ptr = pos_ptr, base.n_heads = d.n_heads;
+  base.logits = d.logits, base.batch = d.batch, base.n_q = d.n_q, base.vocab = d.vocab;
+  base.tiles_per_head = d.head_rows_padded / NT, base.cfg_scale = d.cfg_scale, base.trace = e->chain_trace;
+
+  auto sync_slot = [&](int j) { return d.gemm_tickets + CHAIN_SYNC_BASE + ((j + n_launches) % n_launches) * CH_SYNC_INTS; };
+  auto ph_qkv = [&](int l) {
+    ChainPhase p{};
+    p.W = (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, p.n_tiles = (hd + 2 * kvd) / NT, p.k_blocks = dm / 64;
+    p.epi = CH_EPI_PARTIAL, p.fin = CH_FIN_QKV, p.A = (const uint8_t*)xn, p.a_row_bytes = dm * 2, p.ldn = hd + 2 * kvd;
+    p.kv_layer = l;
+    chain_plan_partial(p, sms, rows, d.gemm_ws_floats);
+    return p;
+  };
+  auto ph_resid = [&](const void* w, int64_t stride, int l, const bf16* a_ptr, int k, const bf16* lnw, const bf16* lnb) {
+    ChainPhase p{};
+    p.W = (const uint8_t*)w + (size_t)l * stride, p.n_tiles = dm / NT, p.k_blocks = k / 64;
+    p.epi = CH_EPI_PARTIAL, p.fin = CH_FIN_RESID_LN, p.A = (const uint8_t*)a_ptr, p.a_row_bytes = k * 2, p.ldn = dm;
+    p.ln_w = lnw, p.ln_b = lnb;
+    chain_plan_partial(p, sms, rows, d.gemm_ws_floats);
+    return p;
+  };
+  auto ph_fc1 = [&](int l) {
+    ChainPhase p{};
+    p.W = (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, p.n_tiles = d.d_ff / (NT / 2), p.k_blocks = dm / 64;
+    p.epi = CH_EPI_SWIGLU, p.fin = CH_FIN_NONE, p.A = (const uint8_t*)xn, p.a_row_bytes = dm * 2, p.h = h, p.ldh = d.d_ff;
+    chain_plan_ticketed(p, sms);
+    return p;
+  };
+  auto ph_heads = [&]() {
+    ChainPhase p{};
+    p.W = (const uint8_t*)d.w_heads, p.n_tiles = d.n_q * (d.head_rows_padded / NT), p.k_blocks = dm / 64;
+    p.epi = CH_EPI_HEADS, p.fin = CH_FIN_NONE, p.a_pairs = 1, p.A = (const uint8_t*)xn, p.a_row_bytes = dm * 2;
+    chain_plan_ticketed(p, sms);
+    return p;
+  };
+
+  ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w, (const bf16*)d.ln1_b, xn, rows, dm, d.ln_eps, 1, 0, st));
+  {
+    ChainArgs a = base;
+    a.n_phases = 1, a.ph[0] = ph_qkv(0);
+    a.sync_mine = sync_slot(0), a.sync_prev = sync_slot(-1);
+    ZB_TRY(launch_chain(a, sms, st));
+  }
+  for (int l = 0; l < L; ++l) {
+    {
+      AttnDecodeArgs at;
+      at.q = q, at.out = att, at.kv = kv_of(d, l), at.pos_ptr = pos_ptr, at.pos_add = 0;
+      at.n_heads = d.n_heads, at.n_kv_heads = d.n_kv_heads, at.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
+      at.partial_ws = d.attn_ws, at.tickets = d.attn_tickets;
+      ZB_TRY(launch_attn_decode(at, rows, d.attn_nsplit, st));
+    }
+    const bool last = (l + 1 == L);
+    ChainArgs a = base;
+    a.n_phases = 4;
+    a.ph[0] = ph_resid(d.w_out, d.out_stride, l, att, hd, (const bf16*)d.ln2_w + (size_t)l * dm, (const bf16*)d.ln2_b + (size_t)l * dm);
+    a.ph[1] = ph_fc1(l);
+    a.ph[2] = ph_resid(d.w_fc2, d.fc2_stride, l, h, d.d_ff, last ? (const bf16*)d.lnf_w : (const bf16*)d.ln1_w + (size_t)(l + 1) * dm,
+                       last ? (const bf16*)d.lnf_b : (const bf16*)d.ln1_b + (size_t)(l + 1) * dm);
+    a.ph[3] = last ? ph_heads() : ph_qkv(l + 1);
+    a.sync_mine = sync_slot(l + 1), a.sync_prev = sync_slot(l);
+    ZB_TRY(launch_chain(a, sms, st));
+  }
+  return ZB200_OK;
+}
+
+// Shapes the chain kernel takes: even tile counts for the deferred phases, counters and tickets inside gemm_tickets,
+// at least one split of every deferred phase inside the workspace.
+bool chain_supported(const zb200_engine* e) {
+  const zb200_engine_desc& d = e->d;
+  const int dm = d.d_model, hd = d.n_heads * ZB200_HEAD_DIM, kvd = d.n_kv_heads * ZB200_HEAD_DIM, rows = 2 * d.batch;
+  if (d.flags & ZB200_ENGINE_NO_CHAIN) return false;
+  if (rows > GEMM_BM || e->sk_sms < 8) return false;
+  if ((dm / NT) % 2 || ((hd + 2 * kvd) / NT) % 2 || dm > 4096) return false;
+  if (d.n_gemm_tickets < CHAIN_SYNC_BASE + (d.n_layer + 1) * CH_SYNC_INTS) return false;
+  const int max_pairs = std::max(d.d_ff / (NT / 2), d.n_q * (d.head_rows_padded / NT)) / 2 + 1;
+  if (max_pairs > CHAIN_SYNC_BASE) return false;
+  if ((int64_t)rows * std::max(dm, hd + 2 * kvd) > d.gemm_ws_floats) return false;
+  if ((int64_t)e->sk_sms * 4 * SK_PARTIAL_F4 * 4 > d.gemm_ws_floats) return false;  // fix-up slots: 2 x 2 sub-tiles per CTA
+  return true;
+}
+
 // Decode step with rows = 2B <= 8 (gemm_swap.cuh): the weights are the 128-row UMMA operand, thread == output feature.
 // Each group of two n_tiles is shared by at most 8 CTAs whose 4 KB partials the last one to arrive sums in one batch of
 // loads, so RoPE / residual / SwiGLU / CFG epilogues run in the GEMM itself and no partial-sum pass exists.
@@ -519,6 +619,7 @@ static int decode_logits(zb200_engine* e, cudaStream_t st) {
   static const bool all_swap = getenv("ZB200_ALL_SWAP") != nullptr;
   if (2 * d.batch <= 8 && e->sk_sms > 0 && all_swap && d.d_model % 128 == 0 && d.d_ff % 128 == 0)
     return run_decode_small(e, st);
+  if (chain_supported(e)) return run_decode_chain(e, st);
   if (2 * d.batch <= GEMM_BM && e->sk_sms > 0) return run_decode_skinny(e, st);
   return run_backbone(e, 2 * d.batch, 1, true, st);
 }
@@ -589,3 +690,11 @@ extern "C" int zb200_engine_run(zb200_engine* e, int n_steps, void* stream) {
 }
 
 extern "C" int zb200_engine_launches_per_step(const zb200_engine* e) { return e ? e->launches : 0; }
+
+/* debug: device buffer [SMs][4][8] uint64 receiving the chain kernel's in-kernel globaltimer stamps (the last launch of a
+ * step overwrites the earlier ones unless the caller steps through the layers); nullptr switches it off. */
+extern "C" int zb200_engine_set_chain_trace(zb200_engine* e, unsigned long long* device_buf) {
+  ZB_REQUIRE(e, "engine_set_chain_trace: null engine");
+  e->chain_trace = device_buf;
+  return ZB200_OK;
+}

@@ -34,7 +34,11 @@ class EngineDesc(ctypes.Structure):
         ("n_gemm_tickets", ctypes.c_int32),
         ("attn_ws", ctypes.c_void_p), ("attn_tickets", ctypes.c_void_p),
         ("state", ctypes.c_void_p), ("delayed", ctypes.c_void_p),
+        ("flags", ctypes.c_int32),
     ]
+
+
+ENGINE_NO_CHAIN = 1  # ZB200_ENGINE_NO_CHAIN (include/zonos_b200.h)
 
 
 def rope_table(n_pos: int, head_dim: int, base: float = 10000.0, device="cuda") -> torch.Tensor:
@@ -79,7 +83,7 @@ class Engine:
     """One generate() call's device session: KV pages, activation workspaces, the C engine handle."""
 
     def __init__(self, pw: PackedWeights, cfg, batch: int, prefill_len: int, max_seq: int, t_delayed: int, delayed,
-                 state, cfg_scale: float, kv=None, attn_nsplit=None):
+                 state, cfg_scale: float, kv=None, attn_nsplit=None, flags=None):
         dev = pw.emb.device
         H, Hkv, L = cfg.attn_cfg["num_heads"], cfg.attn_cfg["num_heads_kv"], cfg.n_layer
         B2 = 2 * batch
@@ -122,6 +126,9 @@ class Engine:
         for name in ("x", "xn", "q", "att", "h", "logits", "gemm_ws", "gemm_tickets", "attn_ws", "attn_tickets", "state", "delayed"):
             setattr(d, name, getattr(self, name).data_ptr())
         d.gemm_ws_floats, d.n_gemm_tickets = self.gemm_ws.numel(), self.gemm_tickets.numel()
+        if flags is None:  # host-side switch for A/B measurements (the library itself reads no environment for this)
+            flags = ENGINE_NO_CHAIN if os.environ.get("ZB200_NO_CHAIN") else 0
+        d.flags = flags
         self.desc = d
         self.handle = ctypes.c_void_p()
         check(lib().zb200_engine_create(ctypes.byref(d), ctypes.byref(self.handle)), "engine_create")
@@ -153,6 +160,11 @@ class Engine:
 
     def run(self, n_steps: int):
         check(lib().zb200_engine_run(self.handle, n_steps, stream_ptr()), "engine_run")
+
+    def set_chain_trace(self, buf):
+        """Debug: uint64 CUDA tensor [SMs * 4 * 8] receiving the chain kernel's globaltimer stamps (None: off)."""
+        check(lib().zb200_engine_set_chain_trace(self.handle, ctypes.c_void_p(0 if buf is None else buf.data_ptr())),
+              "engine_set_chain_trace")
 
     def launches_per_step(self) -> int:
         return lib().zb200_engine_launches_per_step(self.handle)
