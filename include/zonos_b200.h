@@ -169,9 +169,10 @@ typedef struct {
   int32_t* delayed;              /* int32 [B][n_q][t_delayed] */
   int32_t flags;                 /* ZB200_ENGINE_* bits; 0 = defaults */
 } zb200_engine_desc;
-/* flags: decode step as one launch per GEMM (+ reduction kernels) instead of the fused per-layer chain kernel
- * (csrc/chain.cuh); both give the same rounding points, the split-K summation order differs. */
-#define ZB200_ENGINE_NO_CHAIN 1
+/* flags: run the decode step on the fused per-layer chain kernel (csrc/chain.cuh: one persistent launch for everything
+ * between two attention kernels, software grid barriers) instead of one launch per GEMM + reduction kernel.  Same
+ * rounding points, different split-K summation order.  Measured SLOWER than the default on B200: opt-in. */
+#define ZB200_ENGINE_CHAIN 1
 typedef struct zb200_engine zb200_engine;
 int zb200_engine_create(const zb200_engine_desc* desc, zb200_engine** out);
 void zb200_engine_destroy(zb200_engine* e);
@@ -187,8 +188,8 @@ int zb200_engine_capture(zb200_engine* e, const zb200_sampler_args* smp, void* s
 int zb200_engine_run(zb200_engine* e, int n_steps, void* stream);
 /* number of kernel launches in one step (for the bench's gpu_launches claim) */
 int zb200_engine_launches_per_step(const zb200_engine* e);
-/* debug hook (no reference counterpart): globaltimer stamps of the fused chain kernel, uint64 [SMs][4 phases][8 events]
- * in device memory; pass NULL to switch it off.  Takes effect for launches issued afterwards (not for a captured graph). */
+/* debug hook (no reference counterpart): globaltimer stamps of the fused chain kernel, uint64
+ * [n_layer + 1 launches][SMs][4 phases][8 events] in device memory; pass NULL to switch it off.  Takes effect for launches issued afterwards (not for a captured graph). */
 int zb200_engine_set_chain_trace(zb200_engine* e, unsigned long long* device_buf);
 
 /* ---- Hybrid backbone, Mamba2 mixer decode step (zonos/backbone/_mamba_ssm.py:18-31 builds the layers

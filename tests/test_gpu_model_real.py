@@ -90,9 +90,12 @@ def test_real_shape_logits_vs_reference_golden(real_model, golden):
         _compare(f"{name} decode frame {s + 1} vs reference", lg.cpu(), case["logits"][s + 1], cfg)
 
 
-@pytest.mark.parametrize("B,Lc,N", [(1, 23, 8), (16, 16, 6), (64, 16, 6)])
-def test_real_shape_teacher_forced_vs_oracle(real_model, real_weights, B, Lc, N):
-    """Free-running greedy generate on the GPU; every frame's CFG logits vs the CPU oracle on the same token history."""
+@pytest.mark.parametrize("B,Lc,N,chain", [(1, 23, 8, False), (16, 16, 6, False), (64, 16, 6, False), (64, 16, 6, True), (2, 16, 6, True)])
+def test_real_shape_teacher_forced_vs_oracle(real_model, real_weights, B, Lc, N, chain, monkeypatch):
+    """Free-running greedy generate on the GPU; every frame's CFG logits vs the CPU oracle on the same token history.
+    chain: the opt-in fused chain kernel (csrc/chain.cuh) instead of the default per-GEMM launches."""
+    if chain:
+        monkeypatch.setenv("ZB200_CHAIN", "1")
     cond = shapes.synth_conditioning(B, Lc, 2048, seed=21 + B)
     taps = []
     out = real_model.generate(cond.cuda(), None, max_new_tokens=N, batch_size=B, progress_bar=False,

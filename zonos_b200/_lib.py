@@ -7,7 +7,8 @@ import os
 import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libzonos_b200.so")
+# ZB200_LIB_SUFFIX selects an experiment build made with the same variable (zonos_b200/build.py); default: the product library
+LIB_PATH = os.path.join(_HERE, "lib", f"libzonos_b200{os.environ.get('ZB200_LIB_SUFFIX', '')}.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "zonos_b200.h")
 
 ZB200_OK, ZB200_ERR_INVALID, ZB200_ERR_CUDA, ZB200_ERR_STATE = 0, -1, -2, -3

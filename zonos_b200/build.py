@@ -27,6 +27,11 @@ for _k in ("SK_SA128", "SK_SW128_KB"):  # ring-depth experiments
         NVCC_FLAGS.append(f"-D{_k}={os.environ[_k]}")
 if os.environ.get("ZB200_TRACE"):
     NVCC_FLAGS.append("-DSK_TRACE")
+if os.environ.get("ZB200_EXTRA_DEFS"):  # experiment builds: extra -D flags, written to lib/libzonos_b200<ZB200_LIB_SUFFIX>.so
+    NVCC_FLAGS += os.environ["ZB200_EXTRA_DEFS"].split()
+if os.environ.get("ZB200_LIB_SUFFIX"):
+    LIB = os.path.join(LIBDIR, f"libzonos_b200{os.environ['ZB200_LIB_SUFFIX']}.so")
+    OBJ = OBJ + os.environ["ZB200_LIB_SUFFIX"]
 NVCC_FLAGS.remove("--use_fast_math=false")  # precise math on purpose: the sampler/Snake must match the reference
 
 
@@ -53,7 +58,7 @@ def _digest():
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     os.makedirs(LIBDIR, exist_ok=True)
-    stamp = os.path.join(LIBDIR, "build.sha256")
+    stamp = LIB + ".sha256" if os.environ.get("ZB200_LIB_SUFFIX") else os.path.join(LIBDIR, "build.sha256")
     dig = _digest()
     if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read().strip() == dig:
         return LIB

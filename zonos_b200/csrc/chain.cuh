@@ -66,20 +66,35 @@ struct ChainArgs {
   unsigned long long* trace;  // optional [gridDim.x][CH_MAX_PHASES][CH_TRACE_EVENTS] globaltimer stamps
 };
 
+#ifndef CH_POLL_SLEEP
+#define CH_POLL_SLEEP 0  // ns between polls of the fast path (experiment knob)
+#endif
+#ifndef CH_HELP
+#define CH_HELP 1        // P warps take the second tile of a phase's last fragment (experiment knob)
+#endif
+#ifndef CH_SW128
+#define CH_SW128 6       // weight-ring stages at 128 rows (experiment knob)
+#endif
+#ifndef CH_SA128
+#define CH_SA128 4       // activation-ring stages at 128 rows (experiment knob)
+#endif
 template <int A_ROWS>
 struct ChainCfg {
-  static constexpr int PROD_WARPS = (A_ROWS >= 128) ? 4 : 1;
+  // warps 0-3: epilogue group E; warps 4-7: A producers, then helper group P (tile 1 of a phase's last fragment, half of
+  // every reduction); warp 8: weight producer; warp 9: MMA issuer.  Every variant has the four P warps: at few rows they
+  // have little to gather, but the epilogues and reductions are the same size.
+  static constexpr int PROD_WARPS = 4;
   static constexpr int PROD_THREADS = PROD_WARPS * 32;
   static constexpr int THREADS = (4 + PROD_WARPS + 2) * 32;
   static constexpr int A_STAGE_BYTES = A_ROWS * 128;
   static constexpr int W_STAGE_BYTES = 2 * SK_TILE_BYTES;  // one k-block of two adjacent n_tiles (UMMA N = 128)
-  static constexpr int SA = (A_ROWS >= 128) ? 4 : 8;
-  static constexpr int SW = (A_ROWS >= 128) ? 7 : 10;
+  static constexpr int SA = (A_ROWS >= 128) ? CH_SA128 : 8;
+  static constexpr int SW = (A_ROWS >= 128) ? CH_SW128 : 8;
   static constexpr int A_BYTES = SA * A_STAGE_BYTES;
   static constexpr int W_BYTES = SW * W_STAGE_BYTES;
-  static constexpr int XPOSE_BYTES = (A_ROWS >= 128) ? 4 * 8192 : 0;  // per-epilogue-warp transpose for partial stores
+  static constexpr int XPOSE_BYTES = (CH_HELP ? 8 : 4) * 8192;  // per-warp transpose buffers for coalesced partial stores (E and P warps)
   static constexpr int BAR_OFFSET = A_BYTES + W_BYTES + XPOSE_BYTES;
-  static constexpr int N_BARS = 2 * SA + 2 * SW + 4;
+  static constexpr int N_BARS = 2 * SA + 2 * SW + 6;
   static constexpr int DYN_BYTES = BAR_OFFSET + N_BARS * 8 + 16 + 1024;
   static constexpr uint32_t TMEM_COLS = 256;  // two accumulator sets of 128 columns
   static_assert(A_BYTES % 1024 == 0 && W_BYTES >= GEMM_BM * 128, "operand tiles must be 1024-byte aligned / in bounds");
@@ -92,15 +107,25 @@ __device__ __forceinline__ int ch_ld_acquire(const int* p) {
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// Bounded wait for a monotonic counter.  Sticky: once any wait of the launch timed out, the rest fall through.
+// Bounded wait for a monotonic counter (one thread per CTA polls).  Sticky: once any wait of the launch timed out, the
+// rest fall through.
 __device__ __forceinline__ void ch_wait(const int* cnt, int target, int* err) {
-  if (ch_ld_acquire(cnt) >= target) return;
+  for (int it = 0; it < (1 << 22); ++it) {
+    if (ch_ld_acquire(cnt) >= target) return;
+    if (CH_POLL_SLEEP > 0) __nanosleep(CH_POLL_SLEEP);
+  }
   if (*reinterpret_cast<volatile int*>(err) & 2) return;
-  for (int it = 0; it < (1 << 23); ++it) {
-    __nanosleep(40);
+  for (int it = 0; it < (1 << 22); ++it) {
+    __nanosleep(100);
     if (ch_ld_acquire(cnt) >= target) return;
   }
   atomicOr(err, 2);
+}
+// Arrive after a CTA-wide (named) barrier: the barrier orders the group's writes before this thread's fence, the fence is
+// cumulative at gpu scope (the cooperative-groups grid.sync pattern): one fence per CTA instead of one per thread.
+__device__ __forceinline__ void ch_arrive(int* cnt) {
+  __threadfence();
+  atomicAdd(cnt, 1);
 }
 __device__ __forceinline__ void ch_stamp(const ChainArgs& a, int p, int ev) {
   if (a.trace) {
@@ -130,36 +155,58 @@ __device__ __forceinline__ ChainRange ch_range(const ChainPhase& ph, int cta) {
 }
 
 // ------------------------------------------------------------------------------------------------ reductions
+// Both run on the 256 threads of the E and P groups of one CTA (named barrier 3) and issue ALL their global loads before
+// the first use, so a row costs one L2 round trip, not one per column chunk and operand.
+//
 // Row `row` of:  o = bf16(sum_s ws[s][row][:]); x = bf16(x + o); xn = LayerNorm(x) * w + b     (resid_ln_kernel, ops.cu)
-// run by the 128 epilogue threads of one CTA (named barrier 1).  d <= 4096, d % 256 == 0.
-__device__ __forceinline__ void ch_resid_ln_row(const ChainArgs& a, const ChainPhase& ph, int row, int tid, float* red) {
-  constexpr int MAXV = 4, BATCH = 12;
-  const int d = a.d_model, splits = ph.n_splits, rows = a.rows, lane = tid & 31, warp = tid >> 5;
+// d <= 4096, d % 256 == 0; thread t owns columns [8t, 8t + 8) (+ 2048 for d > 2048).
+template <int MAXV>
+__device__ __forceinline__ void ch_resid_ln_row_t(const ChainArgs& a, const ChainPhase& ph, int row, int t, float* red) {
+  constexpr int BATCH = (MAXV == 1) ? 9 : 5;
+  const int d = a.d_model, splits = ph.n_splits, rows = a.rows, lane = t & 31, warp = t >> 5;
+  float o[MAXV][8];
+  uint4 xu[MAXV], wu[MAXV], bu[MAXV];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int col = (i * 256 + t) * 8;
+    if (col < d) {
+      xu[i] = __ldcg(reinterpret_cast<const uint4*>(a.x + (size_t)row * d + col));
+      wu[i] = __ldg(reinterpret_cast<const uint4*>(ph.ln_w + col)), bu[i] = __ldg(reinterpret_cast<const uint4*>(ph.ln_b + col));
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[i][j] = 0.f;
+  }
+  for (int s0 = 0; s0 < splits; s0 += BATCH) {  // one round of independent loads for <= BATCH splits, added in split order
+    float4 p0[MAXV][BATCH], p1[MAXV][BATCH];
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int col = (i * 256 + t) * 8;
+#pragma unroll
+      for (int s = 0; s < BATCH; ++s)
+        if (col < d && s0 + s < splits) ldg256_cg(a.ws + ((size_t)(s0 + s) * rows + row) * d + col, p0[i][s], p1[i][s]);
+    }
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int col = (i * 256 + t) * 8;
+#pragma unroll
+      for (int s = 0; s < BATCH; ++s)
+        if (col < d && s0 + s < splits) {
+          o[i][0] += p0[i][s].x, o[i][1] += p0[i][s].y, o[i][2] += p0[i][s].z, o[i][3] += p0[i][s].w;
+          o[i][4] += p1[i][s].x, o[i][5] += p1[i][s].y, o[i][6] += p1[i][s].z, o[i][7] += p1[i][s].w;
+        }
+    }
+  }
   float v[MAXV][8];
   float sum = 0.f;
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
-    const int col = (i * 128 + tid) * 8;
+    const int col = (i * 256 + t) * 8;
     if (col < d) {
-      float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int s0 = 0; s0 < splits; s0 += BATCH) {  // independent loads in flight, added in split order
-        float4 p0[BATCH], p1[BATCH];
-#pragma unroll
-        for (int s = 0; s < BATCH; ++s)
-          if (s0 + s < splits) ldg256_cg(a.ws + ((size_t)(s0 + s) * rows + row) * d + col, p0[s], p1[s]);
-#pragma unroll
-        for (int s = 0; s < BATCH; ++s)
-          if (s0 + s < splits) {
-            o[0] += p0[s].x, o[1] += p0[s].y, o[2] += p0[s].z, o[3] += p0[s].w;
-            o[4] += p1[s].x, o[5] += p1[s].y, o[6] += p1[s].z, o[7] += p1[s].w;
-          }
-      }
-      const uint4 xu = __ldcg(reinterpret_cast<const uint4*>(a.x + (size_t)row * d + col));
-      const float2 x0 = unpack_bf16x2(xu.x), x1 = unpack_bf16x2(xu.y), x2 = unpack_bf16x2(xu.z), x3 = unpack_bf16x2(xu.w);
+      const float2 x0 = unpack_bf16x2(xu[i].x), x1 = unpack_bf16x2(xu[i].y), x2 = unpack_bf16x2(xu[i].z), x3 = unpack_bf16x2(xu[i].w);
       const float xin[8] = {x0.x, x0.y, x1.x, x1.y, x2.x, x2.y, x3.x, x3.y};
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        v[i][j] = bf16_round(xin[j] + bf16_round(o[j]));
+        v[i][j] = bf16_round(xin[j] + bf16_round(o[i][j]));
         sum += v[i][j];
       }
       *reinterpret_cast<uint4*>(a.x + (size_t)row * d + col) =
@@ -167,50 +214,60 @@ __device__ __forceinline__ void ch_resid_ln_row(const ChainArgs& a, const ChainP
                      pack_bf16x2(v[i][6], v[i][7]));
     }
   }
-  auto block_sum = [&](float t) {
-    t = warp_sum(t);
-    ch_named_sync(1, 128);
-    if (lane == 0) red[warp] = t;
-    ch_named_sync(1, 128);
-    return (red[0] + red[1]) + (red[2] + red[3]);
+  auto block_sum = [&](float x) {
+    x = warp_sum(x);
+    ch_named_sync(3, 256);
+    if (lane == 0) red[warp] = x;
+    ch_named_sync(3, 256);
+    return ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
   };
   const float mean = block_sum(sum) / (float)d;
   float sq = 0.f;
 #pragma unroll
   for (int i = 0; i < MAXV; ++i)
-    if ((i * 128 + tid) * 8 < d)
+    if ((i * 256 + t) * 8 < d)
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float t = v[i][j] - mean;
-        sq += t * t;
+        const float c = v[i][j] - mean;
+        sq += c * c;
       }
   const float rstd = 1.0f / sqrtf(block_sum(sq) / (float)d + a.ln_eps);
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
-    const int col = (i * 128 + tid) * 8;
+    const int col = (i * 256 + t) * 8;
     if (col < d) {
-      const uint4 wu = __ldg(reinterpret_cast<const uint4*>(ph.ln_w + col)), bu = __ldg(reinterpret_cast<const uint4*>(ph.ln_b + col));
-      const uint32_t wv[4] = {wu.x, wu.y, wu.z, wu.w}, bv[4] = {bu.x, bu.y, bu.z, bu.w};
-      uint32_t o[4];
+      const uint32_t wv[4] = {wu[i].x, wu[i].y, wu[i].z, wu[i].w}, bv[4] = {bu[i].x, bu[i].y, bu[i].z, bu[i].w};
+      uint32_t r[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const float2 ww = unpack_bf16x2(wv[j]), bb = unpack_bf16x2(bv[j]);
-        o[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * ww.x + bb.x, (v[i][2 * j + 1] - mean) * rstd * ww.y + bb.y);
+        r[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * ww.x + bb.x, (v[i][2 * j + 1] - mean) * rstd * ww.y + bb.y);
       }
-      *reinterpret_cast<uint4*>(a.xn + (size_t)row * d + col) = make_uint4(o[0], o[1], o[2], o[3]);
+      *reinterpret_cast<uint4*>(a.xn + (size_t)row * d + col) = make_uint4(r[0], r[1], r[2], r[3]);
     }
   }
 }
+__device__ __forceinline__ void ch_resid_ln_row(const ChainArgs& a, const ChainPhase& ph, int row, int t, float* red) {
+  if (a.d_model <= 2048) ch_resid_ln_row_t<1>(a, ph, row, t, red);
+  else ch_resid_ln_row_t<2>(a, ph, row, t, red);
+}
 
 // Row `row` of the in_proj finish (qkv_finish_kernel, ops.cu): split sum -> bf16 -> interleaved RoPE on q and k -> q
-// buffer / KV page rows.
-__device__ __forceinline__ void ch_qkv_row(const ChainArgs& a, const ChainPhase& ph, int row, int tid) {
+// buffer / KV page rows.  Thread t owns columns [8t, 8t + 8), + 2048 per further round.
+__device__ __forceinline__ void ch_qkv_row(const ChainArgs& a, const ChainPhase& ph, int row, int t) {
   const int n_cols = ph.ldn, splits = ph.n_splits, rows = a.rows, n_heads = a.n_heads;
   KvLayout kv = a.kv;
   kv.layer = ph.kv_layer;
   const int kv_heads = kv.n_kv_heads;
   const int pos = *a.pos_ptr;
-  for (int col0 = tid * 8; col0 < n_cols; col0 += 128 * 8) {
+  for (int col0 = t * 8; col0 < n_cols; col0 += 256 * 8) {
+    const int head_all = col0 >> 7, within = col0 & 127;
+    const bool rot = head_all < n_heads + kv_heads;
+    float4 t01 = make_float4(0.f, 0.f, 0.f, 0.f), t23 = t01;
+    if (rot) {
+      const float4* cs = reinterpret_cast<const float4*>(a.rope + ((size_t)pos * 64 + (within >> 1)) * 2);
+      t01 = __ldg(cs), t23 = __ldg(cs + 1);
+    }
     float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int s0 = 0; s0 < splits; s0 += 8) {
       float4 p0[8], p1[8];
@@ -224,11 +281,8 @@ __device__ __forceinline__ void ch_qkv_row(const ChainArgs& a, const ChainPhase&
           o[4] += p1[s].x, o[5] += p1[s].y, o[6] += p1[s].z, o[7] += p1[s].w;
         }
     }
-    const int head_all = col0 >> 7, within = col0 & 127;
     float r[8];
-    if (head_all < n_heads + kv_heads) {
-      const float4* cs = reinterpret_cast<const float4*>(a.rope + ((size_t)pos * 64 + (within >> 1)) * 2);
-      const float4 t01 = __ldg(cs), t23 = __ldg(cs + 1);
+    if (rot) {
       const float co[4] = {t01.x, t01.z, t23.x, t23.z}, si[4] = {t01.y, t01.w, t23.y, t23.w};
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -252,6 +306,28 @@ __device__ __forceinline__ void ch_qkv_row(const ChainArgs& a, const ChainPhase&
 }
 
 // ------------------------------------------------------------------------------------------------ the kernel
+// Fused epilogue of one 64-column tile held by a warp (lane == TMEM lane == row within the warp's 32-row quarter).
+__device__ __forceinline__ void ch_tile_epilogue(const ChainArgs& a, const ChainPhase& ph, int quarter, int lane, int n_tile,
+                                                 int split, float* acc, float* xpose_w) {
+  const int row = quarter * 32 + lane;
+  const bool row_valid = row < a.rows;
+  if (ph.epi == CH_EPI_PARTIAL) {
+    const EpiPartial epi{a.ws, a.rows, ph.ldn};
+    epi.partial_warp(xpose_w, lane, quarter * 32, n_tile, split, acc);
+  } else if (ph.epi == CH_EPI_SWIGLU) {
+    const EpiSwiGLU<SK_NT> epi{ph.h, ph.ldh};
+    epi(row, row_valid, 0, n_tile, acc);
+  } else {
+    const EpiHeadsCfg<SK_NT> epi{a.logits, a.batch, a.n_q, a.vocab, a.tiles_per_head, a.cfg_scale};
+    epi(row, row_valid, 0, n_tile, acc);
+  }
+}
+// A fragment [ku_begin, ku_end) of tile pair `pair` that ends the CTA's range of a phase is "helped": the P warps take its
+// second tile.  Only fragments whose epilogue runs straight from TMEM qualify (deferred partials, or a complete K).
+__device__ __forceinline__ bool ch_helped(const ChainPhase& ph, int tiles, bool is_last, bool complete) {
+  return CH_HELP && tiles == 2 && is_last && (ph.epi == CH_EPI_PARTIAL || complete);
+}
+
 template <int A_ROWS>
 __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(const __grid_constant__ ChainArgs a) {
   using C = ChainCfg<A_ROWS>;
@@ -268,15 +344,17 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
   uint64_t* full_w = empty_a + SA;
   uint64_t* empty_w = full_w + SW;
   uint64_t* tmem_full = empty_w + SW;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* tmem_empty = tmem_full + 2;    // E group has read the accumulator set
+  uint64_t* tmem_empty_h = tmem_empty + 2;  // P group has read its tile of a helped fragment
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_h + 2);
   __shared__ int s_is_last;
-  __shared__ float s_red[4];
+  __shared__ float s_red[8];
 
   pdl_launch_dependents();
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, cta = blockIdx.x;
   if (tid == 0) {
+    ch_stamp(a, 0, 7);
     for (int s = 0; s < SA; ++s) {
       mbar_init(&full_a[s], C::PROD_THREADS);
       mbar_init(&empty_a[s], 1);
@@ -288,6 +366,7 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full[b], 1);
       mbar_init(&tmem_empty[b], 128);
+      mbar_init(&tmem_empty_h[b], 128);
     }
     fence_barrier_init();
   }
@@ -308,16 +387,17 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
       for (int p = 0; p < a.n_phases; ++p) {
         const ChainPhase& ph = a.ph[p];
         const ChainRange r = ch_range(ph, cta);
-        const int KB = ph.k_blocks;
+        const int KB = ph.k_blocks, n_tiles = ph.n_tiles;
+        const uint8_t* wbase = ph.W;
         for (int u = r.u0; u < r.u1; ++u, ++gi) {
           if (gi % SK_WLANES != lane) continue;
           const int s = gi % SW;
           const int pair = u / r.kbu, ku = u - pair * r.kbu;
-          const int tiles = min(2, ph.n_tiles - 2 * pair);
+          const int tiles = min(2, n_tiles - 2 * pair);
           mbar_wait(&empty_w[s], ((gi / SW) & 1) ^ 1);
           mbar_arrive_expect_tx(&full_w[s], (uint32_t)(tiles * SK_TILE_BYTES));
           uint8_t* dst = w_ring + s * C::W_STAGE_BYTES;
-          const uint8_t* src = ph.W + ((size_t)(2 * pair) * KB + ku) * SK_TILE_BYTES;
+          const uint8_t* src = wbase + ((size_t)(2 * pair) * KB + ku) * SK_TILE_BYTES;
           bulk_g2s_hint(dst, src, SK_TILE_BYTES, &full_w[s], pol);
           if (tiles == 2) bulk_g2s_hint(dst + SK_TILE_BYTES, src + (size_t)KB * SK_TILE_BYTES, SK_TILE_BYTES, &full_w[s], pol);
         }
@@ -327,6 +407,7 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
     // ---------------------------------------------------------------- MMA issuer
     if (lane == 0) {
       int gi = 0, f = 0;
+      uint32_t hpend = 0, hpar = 0;  // bit b: set b's previous fragment was helped (await the P group's read too) / its parity
       for (int p = 0; p < a.n_phases; ++p) {
         const ChainPhase& ph = a.ph[p];
         const ChainRange r = ch_range(ph, cta);
@@ -338,6 +419,10 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
           const uint32_t idesc = umma_idesc(GEMM_BM, tiles * SK_NT, 1);
           const int b = f & 1;
           mbar_wait(&tmem_empty[b], ((f >> 1) & 1) ^ 1);
+          if ((hpend >> b) & 1) {
+            mbar_wait(&tmem_empty_h[b], (hpar >> b) & 1);
+            hpar ^= 1u << b, hpend &= ~(1u << b);
+          }
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + (uint32_t)(b * 2 * SK_NT);
           for (int ku = ku_begin; ku < ku_end; ++ku, ++gi) {
@@ -356,82 +441,118 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
             umma_commit(&empty_w[sw]);
           }
           umma_commit(&tmem_full[b]);
+          if (ch_helped(ph, tiles, u + (ku_end - ku_begin) == r.u1, ku_begin == 0 && ku_end == r.kbu)) hpend |= 1u << b;
           u += ku_end - ku_begin;
           ++f;
         }
       }
     }
   } else if (warp >= 4) {
-    // ---------------------------------------------------------------- A producers (cp.async gather -> SW128 tiles)
+    // ---------------------------------------------------------------- P group: A producers, then helpers
     pdl_wait_prior();  // the first phase's activations come from the previous kernel
-    const int ptid = tid - 128;
+    const int ptid = tid - 128, quarter = warp - 4;
     const int rows = min(a.rows, A_ROWS);
     constexpr int CHUNKS = A_ROWS * 8;  // 16-byte chunks per stage
     constexpr int PER_THREAD = (CHUNKS + C::PROD_THREADS - 1) / C::PROD_THREADS;
     constexpr int MAXPEND = (SA < 8) ? SA : 8;
-    int a_base = 0;
+    int a_base = 0, f_base = 0;
     for (int p = 0; p < a.n_phases; ++p) {
       const ChainPhase& ph = a.ph[p];
       const ChainRange r = ch_range(ph, cta);
       const int n_units = r.u1 - r.u0;
-      if (n_units == 0) continue;
-      if (p > 0) {  // this phase's A is produced inside the launch: wait for the reduction (or the epilogues) before it
-        if (ptid == 0) {
-          const ChainPhase& pv = a.ph[p - 1];
-          if (pv.fin != CH_FIN_NONE) ch_wait(&a.sync_mine[2 * (p - 1) + 1], a.rows, a.err);
-          else ch_wait(&a.sync_mine[2 * (p - 1)], pv.grid, a.err);
-          __threadfence();
+      if (n_units > 0) {
+        if (p > 0) {  // this phase's A is produced inside the launch: wait for the reduction (or the epilogues) before it
+          if (ptid == 0) {
+            const ChainPhase& pv = a.ph[p - 1];
+            if (pv.fin != CH_FIN_NONE) ch_wait(&a.sync_mine[2 * (p - 1) + 1], a.rows, a.err);
+            else ch_wait(&a.sync_mine[2 * (p - 1)], pv.grid, a.err);
+          }
+          ch_named_sync(2, C::PROD_THREADS);
         }
-        if (C::PROD_WARPS > 1) ch_named_sync(2, C::PROD_THREADS); else __syncwarp();
-      }
-      if (ptid == 0) ch_stamp(a, p, 1);
-      const uint8_t* abase = ph.A;
-      const size_t arb = (size_t)ph.a_row_bytes;
-      int issued = 0, arrived = 0;
-      int ku = r.u0 % r.kbu;
-      while (arrived < n_units) {
-        bool can_issue = issued < n_units && (issued - arrived) < MAXPEND;
-        if (can_issue) {
-          const int gi = a_base + issued;
-          uint64_t* eb = &empty_a[gi % SA];
-          const uint32_t par = ((gi / SA) & 1) ^ 1;
-          if (issued == arrived) mbar_wait(eb, par);
-          else can_issue = mbar_test_wait(eb, par);
+        if (ptid == 0) ch_stamp(a, p, 1);
+        // Per-phase invariants of this thread's chunks.  Chunk j of the stage is row 16 j + r0, 16-byte column c: its
+        // swizzled destination is dst0 + 2048 j (the XOR term only sees r0 & 7) and its source src0 + j * step, so three
+        // registers describe all of them.  They are pinned with empty asm statements: left alone the compiler re-derives
+        // them per chunk from dynamically indexed kernel parameters, and the gather becomes the bottleneck of the phase.
+        uint64_t abase = reinterpret_cast<uint64_t>(ph.A);
+        uint32_t src0, dst0, step;
+        {
+          const uint32_t arb = (uint32_t)ph.a_row_bytes, r0 = (uint32_t)ptid >> 3, c = (uint32_t)ptid & 7u;
+          const bool pairs = ph.a_pairs != 0;
+          const uint32_t g0 = pairs ? ((r0 & 1u) ? (uint32_t)a.batch + (r0 >> 1) : (r0 >> 1)) : r0;
+          src0 = g0 * arb + c * 16u;
+          step = (pairs ? 8u : 16u) * arb;
+          dst0 = sw128_offset(r0, c);
         }
-        if (can_issue) {
-          uint8_t* a_tile = a_ring + ((a_base + issued) % SA) * C::A_STAGE_BYTES;
+        asm volatile("" : "+l"(abase), "+r"(src0), "+r"(dst0), "+r"(step));
+        const int r0i = ptid >> 3;
+        int issued = 0, arrived = 0;
+        int ku = r.u0 % r.kbu;
+        while (arrived < n_units) {
+          bool can_issue = issued < n_units && (issued - arrived) < MAXPEND;
+          if (can_issue) {
+            const int gi = a_base + issued;
+            uint64_t* eb = &empty_a[gi % SA];
+            const uint32_t par = ((gi / SA) & 1) ^ 1;
+            if (issued == arrived) mbar_wait(eb, par);
+            else can_issue = mbar_test_wait(eb, par);
+          }
+          if (can_issue) {
+            uint8_t* a_tile = a_ring + ((a_base + issued) % SA) * C::A_STAGE_BYTES;
+            const uint8_t* src_k = reinterpret_cast<const uint8_t*>(abase) + (size_t)ku * 128 + src0;
+            uint8_t* dst_k = a_tile + dst0;
 #pragma unroll
-          for (int j = 0; j < PER_THREAD; ++j) {
-            const int idx = j * C::PROD_THREADS + ptid;
-            const int rr = idx >> 3, c = idx & 7;
-            if (idx < CHUNKS && rr < rows) {
-              const int grow = ph.a_pairs ? ((rr & 1) ? a.batch + (rr >> 1) : (rr >> 1)) : rr;
-              cp_async16(a_tile + sw128_offset(rr, c), abase + (size_t)grow * arb + (size_t)ku * 128 + c * 16, 16u);
+            for (int j = 0; j < PER_THREAD; ++j)
+              if (j * C::PROD_THREADS + ptid < CHUNKS && j * 16 + r0i < rows) cp_async16(dst_k + j * 2048, src_k + (size_t)j * step, 16u);
+            cp_async_commit();
+            ++issued;
+            if (++ku == r.kbu) ku = 0;
+          } else {
+            switch (issued - arrived) {  // wait for the OLDEST pending group only
+              case 1: cp_async_wait<0>(); break;
+              case 2: cp_async_wait<1>(); break;
+              case 3: cp_async_wait<2>(); break;
+              case 4: cp_async_wait<3>(); break;
+              case 5: cp_async_wait<4>(); break;
+              case 6: cp_async_wait<5>(); break;
+              case 7: cp_async_wait<6>(); break;
+              default: cp_async_wait<7>(); break;
             }
+            fence_proxy_async();
+            mbar_arrive(&full_a[(a_base + arrived) % SA]);
+            ++arrived;
           }
-          cp_async_commit();
-          ++issued;
-          if (++ku == r.kbu) ku = 0;
-        } else {
-          switch (issued - arrived) {  // wait for the OLDEST pending group only
-            case 1: cp_async_wait<0>(); break;
-            case 2: cp_async_wait<1>(); break;
-            case 3: cp_async_wait<2>(); break;
-            case 4: cp_async_wait<3>(); break;
-            case 5: cp_async_wait<4>(); break;
-            case 6: cp_async_wait<5>(); break;
-            case 7: cp_async_wait<6>(); break;
-            default: cp_async_wait<7>(); break;
-          }
-          fence_proxy_async();
-          mbar_arrive(&full_a[(a_base + arrived) % SA]);
-          ++arrived;
         }
+        // ---- every A stage of the phase has landed: take the second tile of the CTA's last fragment off the E group
+        const int pair_last = (r.u1 - 1) / r.kbu, u_frag = max(r.u0, pair_last * r.kbu);
+        const int kb_ = u_frag - pair_last * r.kbu, ke_ = r.u1 - pair_last * r.kbu;
+        const int tiles = min(2, ph.n_tiles - 2 * pair_last);
+        const int n_frag = pair_last - r.u0 / r.kbu + 1;
+        if (ch_helped(ph, tiles, true, kb_ == 0 && ke_ == r.kbu)) {
+          const int f = f_base + n_frag - 1, b = f & 1;
+          mbar_wait(&tmem_full[b], (f >> 1) & 1);
+          tc_fence_after();
+          const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(b * 2 * SK_NT) + SK_NT;
+          float acc[SK_NT];
+          tmem_ld32(taddr, acc);
+          tmem_ld32(taddr + 32, acc + 32);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(&tmem_empty_h[b]);
+          ch_tile_epilogue(a, ph, quarter, lane, pair_last * 2 + 1, cta % ph.n_splits, acc, xpose + warp * 2048);
+          ch_named_sync(3, 256);  // with the E group: all outputs of the CTA are written, E's thread 0 arrives for both
+        }
+        a_base += n_units, f_base += n_frag;
       }
-      a_base += n_units;
+      if (ph.fin != CH_FIN_NONE && cta < a.rows) {  // half of row `cta`'s reduction
+        ch_named_sync(3, 256);  // E's thread 0 has seen every CTA's arrival
+        if (ph.fin == CH_FIN_RESID_LN) ch_resid_ln_row(a, ph, cta, tid, s_red);
+        else ch_qkv_row(a, ph, cta, tid);
+        ch_named_sync(3, 256);
+      }
     }
   } else {
-    // ---------------------------------------------------------------- epilogue warps (row == TMEM lane) + reductions
+    // ---------------------------------------------------------------- E group: epilogues (row == TMEM lane) + reductions
     pdl_wait_prior();  // residual stream, workspace, tickets and counters belong to the previous kernels until they are done
     if (cta == 0 && tid < CH_SYNC_INTS && a.sync_prev) a.sync_prev[tid] = 0;
     const int row = tid;
@@ -442,6 +563,7 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
       const ChainPhase& ph = a.ph[p];
       const ChainRange r = ch_range(ph, cta);
       const int KBU = r.kbu, units = r.units, G = ph.grid;
+      bool phase_helped = false;
       int u = r.u0;
       while (u < r.u1) {
         const int pair = u / KBU, ku_begin = u - pair * KBU;
@@ -449,41 +571,35 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
         const int tiles = min(2, ph.n_tiles - 2 * pair);
         const int b = f & 1;
         const bool complete = (ku_begin == 0 && ku_end == KBU);
+        const bool is_last = (u + (ku_end - ku_begin) == r.u1);
+        const bool helped = ch_helped(ph, tiles, is_last, complete);
+        const bool direct = (ph.epi == CH_EPI_PARTIAL) || complete;
+        const int n_mine = helped ? 1 : tiles;
+        phase_helped = helped;
         const int slot = (u == r.u0) ? 0 : 1;  // a CTA has at most two partial fragments per phase: its first and its last
         float4* mine = ws4 + ((size_t)cta * 2 + slot) * 2 * SK_PARTIAL_F4;
         mbar_wait(&tmem_full[b], (f >> 1) & 1);
-        if (tid == 0 && u + (ku_end - ku_begin) == r.u1) ch_stamp(a, p, 3);
+        if (tid == 0 && is_last) ch_stamp(a, p, 3);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * 2 * SK_NT);
         float acc[SK_NT];
-        for (int j = 0; j < tiles; ++j) {
+        for (int j = 0; j < n_mine; ++j) {
           tmem_ld32(taddr + j * SK_NT, acc);
           tmem_ld32(taddr + j * SK_NT + 32, acc + 32);
           tmem_ld_wait();
-          if (j == tiles - 1) {
+          if (j == n_mine - 1) {
             tc_fence_before();
             mbar_arrive(&tmem_empty[b]);  // the issuer may start the next-but-one fragment into this accumulator set
           }
-          const int n_tile = pair * 2 + j;
-          if (ph.epi == CH_EPI_PARTIAL) {
-            const EpiPartial epi{a.ws, a.rows, ph.ldn};
-            if constexpr (A_ROWS >= 128) epi.partial_warp(xpose + warp * 2048, lane, warp * 32, n_tile, cta % ph.n_splits, acc);
-            else epi.partial(row, row_valid, n_tile, cta % ph.n_splits, acc);
-          } else if (complete) {
-            if (ph.epi == CH_EPI_SWIGLU) {
-              const EpiSwiGLU<SK_NT> epi{ph.h, ph.ldh};
-              epi(row, row_valid, 0, n_tile, acc);
-            } else {
-              const EpiHeadsCfg<SK_NT> epi{a.logits, a.batch, a.n_q, a.vocab, a.tiles_per_head, a.cfg_scale};
-              epi(row, row_valid, 0, n_tile, acc);
-            }
+          if (direct) {
+            ch_tile_epilogue(a, ph, warp, lane, pair * 2 + j, cta % ph.n_splits, acc, xpose + warp * 2048);
           } else if (row_valid) {
 #pragma unroll
             for (int c = 0; c < SK_NT / 4; ++c)
               mine[(j * (SK_NT / 4) + c) * 128 + row] = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
           }
         }
-        if (ph.epi != CH_EPI_PARTIAL && !complete) {  // ticketed fix-up: the last contributor sums in CTA order
+        if (!direct) {  // ticketed fix-up: the last contributor sums in CTA order
           __threadfence();
           ch_named_sync(1, 128);
           const int c_first = sk_owner(pair * KBU, units, G), c_last = sk_owner(pair * KBU + KBU - 1, units, G);
@@ -509,14 +625,7 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
                   }
                 }
               }
-              const int n_tile = pair * 2 + j;
-              if (ph.epi == CH_EPI_SWIGLU) {
-                const EpiSwiGLU<SK_NT> epi{ph.h, ph.ldh};
-                epi(row, row_valid, 0, n_tile, acc);
-              } else {
-                const EpiHeadsCfg<SK_NT> epi{a.logits, a.batch, a.n_q, a.vocab, a.tiles_per_head, a.cfg_scale};
-                epi(row, row_valid, 0, n_tile, acc);
-              }
+              ch_tile_epilogue(a, ph, warp, lane, pair * 2 + j, 0, acc, xpose + warp * 2048);
             }
           }
           ch_named_sync(1, 128);  // s_is_last is rewritten by the next fragment
@@ -525,26 +634,24 @@ __global__ void __launch_bounds__(ChainCfg<A_ROWS>::THREADS, 1) chain_kernel(con
         ++f;
       }
       if (r.u1 > r.u0) {  // every output of this CTA for the phase is written: arrive on the phase's `done` counter
-        __threadfence();
-        ch_named_sync(1, 128);
+        if (phase_helped) ch_named_sync(3, 256);
+        else ch_named_sync(1, 128);
         if (tid == 0) {
-          atomicAdd(&a.sync_mine[2 * p], 1);
+          ch_arrive(&a.sync_mine[2 * p]);
           ch_stamp(a, p, 4);
         }
       }
       if (ph.fin != CH_FIN_NONE && cta < a.rows) {  // CTA r reduces row r once all CTAs of the phase have arrived
         if (tid == 0) {
           ch_wait(&a.sync_mine[2 * p], ph.grid, a.err);
-          __threadfence();
           ch_stamp(a, p, 5);
         }
-        ch_named_sync(1, 128);
+        ch_named_sync(3, 256);
         if (ph.fin == CH_FIN_RESID_LN) ch_resid_ln_row(a, ph, cta, tid, s_red);
         else ch_qkv_row(a, ph, cta, tid);
-        __threadfence();
-        ch_named_sync(1, 128);
+        ch_named_sync(3, 256);
         if (tid == 0) {
-          atomicAdd(&a.sync_mine[2 * p + 1], 1);
+          ch_arrive(&a.sync_mine[2 * p + 1]);
           ch_stamp(a, p, 6);
         }
       }

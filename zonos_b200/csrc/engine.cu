@@ -387,6 +387,9 @@ int run_decode_chain(zb200_engine* e, cudaStream_t st) {
     a.sync_mine = sync_slot(0), a.sync_prev = sync_slot(-1);
     ZB_TRY(launch_chain(a, sms, st));
   }
+  auto trace_slot = [&](int j) { return e->chain_trace ? e->chain_trace + (size_t)j * sms * CH_MAX_PHASES * CH_TRACE_EVENTS : nullptr; };
+  {
+  }
   for (int l = 0; l < L; ++l) {
     {
       AttnDecodeArgs at;
@@ -404,6 +407,7 @@ int run_decode_chain(zb200_engine* e, cudaStream_t st) {
                        last ? (const bf16*)d.lnf_b : (const bf16*)d.ln1_b + (size_t)(l + 1) * dm);
     a.ph[3] = last ? ph_heads() : ph_qkv(l + 1);
     a.sync_mine = sync_slot(l + 1), a.sync_prev = sync_slot(l);
+    a.trace = trace_slot(l + 1);
     ZB_TRY(launch_chain(a, sms, st));
   }
   return ZB200_OK;
@@ -414,7 +418,7 @@ int run_decode_chain(zb200_engine* e, cudaStream_t st) {
 bool chain_supported(const zb200_engine* e) {
   const zb200_engine_desc& d = e->d;
   const int dm = d.d_model, hd = d.n_heads * ZB200_HEAD_DIM, kvd = d.n_kv_heads * ZB200_HEAD_DIM, rows = 2 * d.batch;
-  if (d.flags & ZB200_ENGINE_NO_CHAIN) return false;
+  if (!(d.flags & ZB200_ENGINE_CHAIN)) return false;
   if (rows > GEMM_BM || e->sk_sms < 8) return false;
   if ((dm / NT) % 2 || ((hd + 2 * kvd) / NT) % 2 || dm > 4096) return false;
   if (d.n_gemm_tickets < CHAIN_SYNC_BASE + (d.n_layer + 1) * CH_SYNC_INTS) return false;
@@ -691,8 +695,8 @@ extern "C" int zb200_engine_run(zb200_engine* e, int n_steps, void* stream) {
 
 extern "C" int zb200_engine_launches_per_step(const zb200_engine* e) { return e ? e->launches : 0; }
 
-/* debug: device buffer [SMs][4][8] uint64 receiving the chain kernel's in-kernel globaltimer stamps (the last launch of a
- * step overwrites the earlier ones unless the caller steps through the layers); nullptr switches it off. */
+/* debug: device buffer [n_layer + 1 launches][SMs][4 phases][8 events] uint64 receiving the chain kernel's in-kernel
+ * globaltimer stamps; nullptr switches it off. */
 extern "C" int zb200_engine_set_chain_trace(zb200_engine* e, unsigned long long* device_buf) {
   ZB_REQUIRE(e, "engine_set_chain_trace: null engine");
   e->chain_trace = device_buf;

@@ -38,7 +38,7 @@ class EngineDesc(ctypes.Structure):
     ]
 
 
-ENGINE_NO_CHAIN = 1  # ZB200_ENGINE_NO_CHAIN (include/zonos_b200.h)
+ENGINE_CHAIN = 1  # ZB200_ENGINE_CHAIN (include/zonos_b200.h)
 
 
 def rope_table(n_pos: int, head_dim: int, base: float = 10000.0, device="cuda") -> torch.Tensor:
@@ -127,7 +127,7 @@ class Engine:
             setattr(d, name, getattr(self, name).data_ptr())
         d.gemm_ws_floats, d.n_gemm_tickets = self.gemm_ws.numel(), self.gemm_tickets.numel()
         if flags is None:  # host-side switch for A/B measurements (the library itself reads no environment for this)
-            flags = ENGINE_NO_CHAIN if os.environ.get("ZB200_NO_CHAIN") else 0
+            flags = ENGINE_CHAIN if os.environ.get("ZB200_CHAIN") else 0
         d.flags = flags
         self.desc = d
         self.handle = ctypes.c_void_p()
