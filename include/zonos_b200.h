@@ -173,9 +173,18 @@ typedef struct {
  * between two attention kernels, software grid barriers) instead of one launch per GEMM + reduction kernel.  Same
  * rounding points, different split-K summation order.  Measured SLOWER than the default on B200: opt-in. */
 #define ZB200_ENGINE_CHAIN 1
+/* flags: the engine only serves zb200_engine_forward (the backbone plugin contract); emb / w_heads / logits / state /
+ * delayed may be NULL and n_q / vocab are ignored. */
+#define ZB200_ENGINE_BACKBONE_ONLY 2
 typedef struct zb200_engine zb200_engine;
 int zb200_engine_create(const zb200_engine_desc* desc, zb200_engine** out);
 void zb200_engine_destroy(zb200_engine* e);
+/* The backbone plugin contract on its own -- TorchZonosBackbone.forward(hidden_states, inference_params)
+ * (zonos/backbone/_torch.py:73-80): x holds hidden [2B*seq_len, d_model]; positions are pos0 .. pos0+seq_len-1
+ * (inference_params.seqlen_offset), causal attention over the cache for seq_len > 1, all cached keys for seq_len == 1;
+ * writes the KV cache and norm_f of EVERY row to out (bf16 [2B*seq_len, d_model]).  ZB200_ERR_STATE on cache overflow
+ * (the reference's assert, _torch.py:44-45). */
+int zb200_engine_forward(zb200_engine* e, int seq_len, int pos0, void* out, void* stream);
 /* x holds the hidden states [2B*seq_len, d_model] (prefix conditioning ++ embedded prefix codes); writes the KV cache
  * for positions [0, seq_len) and the CFG logits of the last position. */
 int zb200_engine_prefill(zb200_engine* e, int seq_len, void* stream);

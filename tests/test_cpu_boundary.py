@@ -151,3 +151,45 @@ def test_gather_codes_gloo_world2():
     got = q.get(timeout=120)
     [p.join(60) for p in procs]
     assert got == [((9, 3 + i), 100 * i + 7) for i in range(5)]
+
+
+def test_patch_reference_on_the_imported_reference_class():
+    """INTEGRATION.md patch 2, applied to the UNMODIFIED reference class (when /root/reference is present): the signature
+    survives, generate() only needs config / state_dict() / device of the reference object, the reference's exceptions
+    keep their types, and on a CPU model the call ends in the 'no CPU fallback' error instead of the reference's loop."""
+    from oracle import ref_import, shapes
+
+    if not ref_import.available():
+        pytest.skip("reference checkout not present (GPU box)")
+    import zonos_b200
+
+    ref_import.import_reference()
+    import zonos.config as zc
+    import zonos.model as zm
+    from zonos.backbone import BACKBONES as REF_BACKBONES
+
+    before = inspect.signature(zm.Zonos.generate)
+    cls = zonos_b200.patch_reference(zm.Zonos)
+    try:
+        assert cls is zm.Zonos and inspect.signature(zm.Zonos.generate) == before and hasattr(zm.Zonos, "generate_reference")
+        cfg = zc.ZonosConfig.from_dict(shapes.reference_config_dict("tiny"))
+        m = zm.Zonos(cfg, REF_BACKBONES["torch"]).to("cpu", torch.bfloat16)
+        sd = m.state_dict()
+        sd.update(shapes.synth_transformer_weights("tiny", seed=0, padded_heads=False))
+        m.load_state_dict(sd)
+        x = torch.zeros(2, 4, 512, dtype=torch.bfloat16)
+        with pytest.raises(AssertionError):
+            m.generate(x, cfg_scale=1.0, batch_size=1)
+        with pytest.raises(ValueError):
+            m.generate(x, batch_size=2)
+        with pytest.raises(RuntimeError, match="CUDA"):
+            m.generate(x, batch_size=1, max_new_tokens=4, progress_bar=False)
+        stamp, mine = m._zb200  # built from the reference object's config + state dict, cached on it
+        assert mine.heads[0].weight.shape[0] == 1026 and mine.config.backbone.n_layer == cfg.backbone.n_layer
+        assert torch.equal(mine.state_dict()["backbone.layers.1.mlp.fc2.weight"], sd["backbone.layers.1.mlp.fc2.weight"])
+        with pytest.raises(RuntimeError, match="CUDA"):
+            m.generate(x, batch_size=1, max_new_tokens=4, progress_bar=False)
+        assert m._zb200[1] is mine  # cached, not rebuilt
+    finally:
+        zm.Zonos.generate = zm.Zonos.generate_reference
+        del zm.Zonos.generate_reference

@@ -271,3 +271,65 @@ def test_chain_and_per_gemm_decode_paths_agree(tiny_model, B, monkeypatch):
     d = (chain[:2][fin[:2]] - plain[:2][fin[:2]]).abs().max()
     print(f"B={B}: launches per frame {n_chain} (chain) vs {n_plain}; max|dlogit| over the first two frames {float(d):.4f}")
     assert float(d) <= logit_max_abs(2.0, plain[:2]) + 1e-6
+
+
+def test_backbone_plugin_contract_forward(tiny_model):
+    """BACKBONES["b200"].forward(hidden_states, inference_params) honours the plugin contract of
+    zonos/backbone/_torch.py:73-80, so the reference's own building blocks (_prefill -> _compute_logits, then
+    _decode_one_token with seqlen_offset advanced by the caller, zonos/model.py:103-142,181-202,317-319,420-421) run on it:
+    prefill of 7 + 3 positions and two decode steps against the CPU oracle."""
+    from oracle import backbone as ob
+    from oracle import generate as og
+
+    B, Lc, P = 2, 7, 2
+    W = shapes.synth_transformer_weights("tiny", seed=0)
+    cond = shapes.synth_conditioning(B, Lc, 512, seed=4)
+    ids = torch.randint(0, 1024, (B, 9, P + 1), generator=torch.Generator().manual_seed(6))
+    src = og.ModelLogits(W, "tiny", cond, 64, 2.0)
+    want = [src.prefill(ids)]
+    m = tiny_model
+    params = m.setup_cache(2 * B, 60)
+    got = [m._prefill(cond.cuda(), ids.cuda(), params, 2.0)]
+    params.seqlen_offset += Lc + P + 1
+    params.lengths_per_sample[:] += Lc + P + 1
+    for step in range(2):
+        nxt = torch.randint(0, 1024, (B, 9, 1), generator=torch.Generator().manual_seed(10 + step))
+        want.append(src.step(nxt))
+        got.append(m._decode_one_token(nxt.cuda(), params, 2.0))
+        params.seqlen_offset += 1
+        params.lengths_per_sample[:] += 1
+    for g, w in zip(got, want):
+        g = g.cpu()
+        fin = torch.isfinite(w)
+        assert torch.equal(fin, torch.isfinite(g))
+        d = g[fin] - w[fin]
+        assert float(d.abs().max()) <= logit_max_abs(2.0, w) + 1e-6, float(d.abs().max())
+        assert float(d.pow(2).mean().sqrt() / w[fin].pow(2).mean().sqrt()) <= LOGIT_REL_RMS
+    # hidden states of the backbone alone (all positions), and the cache-overflow assert of the reference
+    hid = torch.randn(2 * B, 5, 512, generator=torch.Generator().manual_seed(3)).bfloat16()
+    p2 = m.setup_cache(2 * B, 16)
+    out = m.backbone(hid.cuda(), p2).cpu()
+    kv = ob.DenseKV(2, 2 * B, 16, 2, 128)
+    ref = ob.backbone_forward(W, "tiny", hid, kv, ob.rope_table(64, 128))
+    assert out.shape == ref.shape and float((out.float() - ref.float()).abs().max()) <= 0.0625
+    p2.seqlen_offset = 60
+    with pytest.raises(AssertionError):
+        m.backbone(hid.cuda(), p2)
+
+
+def test_patch_reference_generate(tiny_model):
+    """zonos_b200.generate(model, ...) for an object that only offers config / state_dict() / device (what
+    zonos_b200.patch_reference installs on the reference class): same tokens as this package's own Zonos.generate."""
+    import types
+
+    import zonos_b200
+
+    B, Lc, N = 2, 6, 8
+    cond = shapes.synth_conditioning(B, Lc, 512, seed=9).cuda()
+    sp = dict(temperature=0.0, repetition_penalty=1.0)
+    want = tiny_model.generate(cond, None, max_new_tokens=N, batch_size=B, progress_bar=False, sampling_params=dict(sp))
+    stand_in = types.SimpleNamespace(config=tiny_model.config, state_dict=tiny_model.state_dict, device=tiny_model.device)
+    got = zonos_b200.generate(stand_in, cond, None, N, 2.0, B, dict(sp), False)
+    assert len(got) == B and all(torch.equal(a, b) for a, b in zip(got, want))
+    with pytest.raises(ValueError):
+        zonos_b200.generate(stand_in, cond, batch_size=3)

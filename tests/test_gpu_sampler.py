@@ -99,3 +99,35 @@ def test_philox_draws_follow_the_distribution():
     assert (freq - p).abs().max() < 0.02, (freq, p)
     # different utterances / codebooks use different streams
     assert len(set(st.tok1.cpu().flatten().tolist())) > 3
+
+
+def test_zero_noise_on_a_zero_probability_token_never_wins():
+    """p / q with p == 0 (masked EOS on codebooks 1-8, the pad slot 1025, tokens cut by min-p) and q == 0
+    would be NaN and could win the race.  Injected noise is 0 exactly on those entries; the draw must still be a token
+    with non-zero probability, for every row."""
+    B, Q, V = 3, 9, 1026
+    g = torch.Generator().manual_seed(5)
+    logits = torch.randn(B, Q, V, generator=g) * 2.0
+    logits[..., 1025] = -torch.inf
+    hist = torch.randint(0, 1024, (B, Q, 6), generator=g)
+    noise = torch.empty(B, Q, V).exponential_(generator=g)
+    noise[:, 1:, 1024] = 0.0   # EOS is masked to -inf on codebooks 1..8 in loop mode (model.py:322-323)
+    noise[..., 1025] = 0.0     # pad slot
+    lowest = logits[..., :1024].argmin(-1, keepdim=True)  # far below min_p * max: removed by the filter
+    noise.scatter_(-1, lowest, 0.0)
+    tok = _run_pass1(logits, hist, 1.0, [], dict(min_p=0.1, temperature=1.0), noise)[..., 0]
+    assert int(tok.max()) <= 1024 and bool((tok[:, 1:] != 1024).all()) and bool((tok != lowest[..., 0]).all())
+    # and the Philox path: never the pad slot, never a masked EOS, finite state
+    from zonos_b200.sampler import LoopState, ST_OFFSET
+    import ctypes
+    from zonos_b200._lib import check, lib, stream_ptr
+
+    delayed = torch.full((B, Q, 12), -1, dtype=torch.int32, device="cuda")
+    delayed[..., :6] = hist.to(torch.int32).cuda()
+    st = LoopState(B, Q, V, delayed, 0, 0, dict(min_p=0.1, temperature=1.0, repetition_penalty=1.0), seed=3)
+    st.state[ST_OFFSET] = 6
+    for draw in range(50):
+        st.state[4] = draw  # ST_DRAW
+        check(lib().zb200_sample(ctypes.byref(st.args(logits.cuda().contiguous(), True)), 1, stream_ptr()))
+        t = st.tok1.cpu()
+        assert int(t.max()) <= 1024 and int(t.min()) >= 0 and bool((t[:, 1:] != 1024).all())

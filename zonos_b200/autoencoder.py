@@ -8,17 +8,52 @@ logger = logging.getLogger(__name__)
 
 
 class DACAutoencoder:
-    """Same attributes as the reference wrapper (num_codebooks / codebook_size / sampling_rate, decode).  Weights are
-    the HF `descript/dac_44khz` decoder + quantizer tensors, given as a state dict (load_dac_state_dict) because this
-    package does not download checkpoints."""
+    """Same attributes as the reference wrapper (num_codebooks / codebook_size / sampling_rate, decode, codes_to_wavs).
 
-    def __init__(self):
+    Weights: like zonos/autoencoder.py:13-19 the constructor loads `descript/dac_44khz` through transformers -- local
+    files first, then the hub.  Where neither is reachable (this build container, the GPU box) the reference would raise
+    in __init__; here the error is kept and raised by the first decode(), so that tests and the benchmark can hand over a
+    state dict with the HF key names instead (load_dac_state_dict).  Only the decoder + quantizer tensors are used: the
+    DAC ENCODER is not built, see encode()."""
+
+    PRETRAINED = "descript/dac_44khz"
+
+    def __init__(self, load_pretrained: bool = True):
         self.codebook_size = 1024
         self.num_codebooks = 9
         self.sampling_rate = 44100
         self._decoder = None
+        self._sd = None  # HF state dict waiting for a CUDA device
+        self._load_error = "no DAC weights given"
         self._postproc = {}
         self._device = torch.device("cpu")
+        if load_pretrained:
+            self._load_pretrained()
+
+    def _load_pretrained(self):
+        try:
+            from transformers.models.dac import DacModel
+
+            try:
+                dac = DacModel.from_pretrained(self.PRETRAINED, local_files_only=True)
+            except Exception:
+                dac = DacModel.from_pretrained(self.PRETRAINED, local_files_only=False)
+            self.codebook_size = dac.config.codebook_size
+            self.num_codebooks = dac.quantizer.n_codebooks
+            self.sampling_rate = dac.config.sampling_rate
+            self._sd = {k: v.detach() for k, v in dac.state_dict().items() if k.startswith(("decoder.", "quantizer."))}
+            self._load_error = None
+        except Exception as e:  # offline and not cached: deferred to the first decode()
+            self._load_error = f"{self.PRETRAINED} could not be loaded through transformers ({type(e).__name__}: {e})"
+
+    # the reference moves the codec with `model.autoencoder.dac.to(device)` (zonos/model.py:80)
+    @property
+    def dac(self):
+        return self
+
+    @property
+    def device(self) -> torch.device:
+        return self._device
 
     def to(self, device):
         self._device = torch.device(device)
@@ -27,16 +62,49 @@ class DACAutoencoder:
         return self
 
     def load_dac_state_dict(self, sd: dict):
+        """HF DacModel key names (`decoder.*`, `quantizer.quantizers.{k}.*`); replaces whatever was loaded before."""
+        self._sd, self._decoder, self._load_error = dict(sd), None, None
+        if self._device.type == "cuda":
+            self._build()
+        return self
+
+    def _build(self):
         from .dac import DacDecoderB200
 
-        self._decoder = DacDecoderB200(sd, self._device)
-        return self
+        if self._sd is None:
+            raise RuntimeError(f"DAC weights not loaded: {self._load_error}; call autoencoder.load_dac_state_dict(state_dict) "
+                               "with the HF descript/dac_44khz tensors")
+        if self._device.type != "cuda":
+            raise RuntimeError("zonos_b200 runs on CUDA (B200) only; move the autoencoder with .to('cuda')")
+        self._decoder = DacDecoderB200(self._sd, self._device)
+
+    def preprocess(self, wav: torch.Tensor, sr: int) -> torch.Tensor:
+        """zonos/autoencoder.py:21-25: resample to 44.1 kHz and zero-pad on the LEFT to a whole number of 512-sample frames."""
+        import torchaudio
+
+        wav = torchaudio.functional.resample(wav, sr, self.sampling_rate)
+        pad = -wav.shape[-1] % 512
+        return torch.nn.functional.pad(wav, (pad, 0))
+
+    def encode(self, wav: torch.Tensor) -> torch.Tensor:
+        """zonos/autoencoder.py:27-28.  NOT BUILT: the DAC encoder + RVQ search is SURVEY 8(f) rank 4 (next row); audio-prefix
+        codes have to come from the reference's DACAutoencoder.encode / HF DacModel.encode for now."""
+        raise NotImplementedError("zonos_b200 does not implement the DAC encoder (SURVEY 8(f) rank 4); encode the audio "
+                                  "prefix with transformers' DacModel.encode and pass the codes to generate()")
+
+    def load_prefix_audio(self, audio_path, device):
+        """zonos/autoencoder.py:30-42 (needs encode(): see there)."""
+        import torchaudio
+
+        wav, sr = torchaudio.load(audio_path)
+        wav = self.preprocess(wav.mean(dim=0, keepdim=True), sr).to(device, dtype=torch.float32)
+        return self.encode(wav.unsqueeze(0))
 
     def decode(self, codes: torch.Tensor) -> torch.Tensor:
         """codes int64 [B, 9, T] -> fp32 [B, 1, 512*T]."""
         assert codes.shape[1] == self.num_codebooks, f"Expected {self.num_codebooks} codebooks, got {codes.shape[1]}"
         if self._decoder is None:
-            raise RuntimeError("DAC weights not loaded: call autoencoder.load_dac_state_dict(state_dict) first")
+            self._build()
         return self._decoder.decode(codes)
 
     # ---- post-processing (autoencoder.py:49-90,172-267), batched on the device -----------------------------------

@@ -60,9 +60,50 @@ class B200ZonosBackbone(nn.Module):
         dev = self.norm_f.weight.device
         return {"paged": PagedKV(self.config.n_layer, batch_size, max_seqlen, self.n_kv_heads, dev)}
 
-    def forward(self, hidden_states, inference_params):
-        raise NotImplementedError(
-            "B200ZonosBackbone runs inside zonos_b200.Zonos (prefill / decode engine); a standalone forward is not exposed")
+    def _pack(self):
+        """Kernel-layout copy of this module's own weights (built on first use, dropped when they are reloaded)."""
+        from .engine import PackedWeights
+
+        if getattr(self, "_packed", None) is None:
+            dev = self.norm_f.weight.device
+            if dev.type != "cuda":
+                raise RuntimeError("zonos_b200 runs on CUDA (B200) only; move the backbone with .to('cuda')")
+            self._packed = PackedWeights(self.state_dict(), self.config.n_layer, 0, dev, prefix="")
+        return self._packed
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self._packed = None
+        return super()._load_from_state_dict(*args, **kwargs)
+
+    def forward(self, hidden_states: torch.Tensor, inference_params) -> torch.Tensor:
+        """The plugin contract of zonos/backbone/_torch.py:73-80: hidden_states bf16 [B2, S, d] -> norm_f(blocks(...)),
+        same shape.  Positions are seqlen_offset .. seqlen_offset + S - 1 (`lengths_per_sample` is uniform over the batch
+        in every caller, zonos/model.py:319,421); the KV rows are written into inference_params.key_value_memory_dict
+        (the paged pool of allocate_inference_cache); the caller advances seqlen_offset, as in the reference.  Runs the
+        session engine's kernels (zb200_engine_forward): S > 1 is the causal prefill, S == 1 the decode step.  With this,
+        the reference's own _prefill / _compute_logits / _decode_one_token run on BACKBONES["b200"] unchanged; the fast
+        path (Zonos.generate of this package) does not go through here -- it keeps the loop on the device."""
+        from .engine import Engine
+
+        if not hidden_states.is_cuda or hidden_states.dtype != torch.bfloat16:
+            raise ValueError("B200ZonosBackbone.forward needs CUDA bf16 hidden states (there is no CPU fallback)")
+        B2, S, d = hidden_states.shape
+        kv = inference_params.key_value_memory_dict["paged"]
+        pos0 = int(inference_params.seqlen_offset)
+        if B2 % 2 or kv.n_seq != B2:
+            raise ValueError(f"hidden_states has {B2} rows; the cache was allocated for {kv.n_seq} (2 x batch) sequences")
+        assert pos0 + S <= kv.max_seq, "KV cache overflow"  # _torch.py:44-45
+        key = (id(kv), B2, S)
+        eng = getattr(self, "_fwd_engine", None)
+        if eng is None or self._fwd_key != key:
+            if eng is not None:
+                eng.close()
+            eng = Engine(self._pack(), self.config, B2 // 2, S, kv.max_seq, 0, None, None, 0.0, kv=kv)
+            self._fwd_engine, self._fwd_key = eng, key
+        eng.x[: B2 * S].view(B2, S, d).copy_(hidden_states)
+        out = torch.empty_like(hidden_states)
+        eng.forward(S, pos0, out)
+        return out
 
 
 BACKBONES = {"b200": B200ZonosBackbone}

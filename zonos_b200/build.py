@@ -27,6 +27,8 @@ for _k in ("SK_SA128", "SK_SW128_KB"):  # ring-depth experiments
         NVCC_FLAGS.append(f"-D{_k}={os.environ[_k]}")
 if os.environ.get("ZB200_TRACE"):
     NVCC_FLAGS.append("-DSK_TRACE")
+if os.environ.get("ZB200_TUNING"):  # experiment builds only: the library then honours its ZB200_* environment switches
+    NVCC_FLAGS.append("-DZB200_TUNING")
 if os.environ.get("ZB200_EXTRA_DEFS"):  # experiment builds: extra -D flags, written to lib/libzonos_b200<ZB200_LIB_SUFFIX>.so
     NVCC_FLAGS += os.environ["ZB200_EXTRA_DEFS"].split()
 if os.environ.get("ZB200_LIB_SUFFIX"):

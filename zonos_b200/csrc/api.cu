@@ -20,7 +20,7 @@ int cuda_fail(cudaError_t e, const char* what) {
   return ZB200_ERR_CUDA;
 }
 bool pdl_enabled() {
-  static const bool on = (getenv("ZB200_NO_PDL") == nullptr);
+  static const bool on = (zb::tuning_env("ZB200_NO_PDL") == nullptr);
   return on;
 }
 }  // namespace zb

@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
 #error "zonos_b200 kernels are written for sm_100a (B200) only"
@@ -269,6 +270,15 @@ cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t sme
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
-bool pdl_enabled();  // api.cu: false when ZB200_NO_PDL is set in the environment
+bool pdl_enabled();  // api.cu: true, unless a tuning build finds ZB200_NO_PDL in the environment
+
+// Experiment switches.  The product library reads NO environment variables (no hidden global state): this
+// returns nullptr unless the library was built with -DZB200_TUNING (ZB200_TUNING=1 python -m zonos_b200.build), which the
+// measurement scripts under scripts/ use for their A/B runs.
+#ifdef ZB200_TUNING
+inline const char* tuning_env(const char* name) { return getenv(name); }
+#else
+inline const char* tuning_env(const char*) { return nullptr; }
+#endif
 
 }  // namespace zb

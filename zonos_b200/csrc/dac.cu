@@ -104,11 +104,11 @@ static int sm_count() {
 // Epilogue traffic through the TMA unit for the layers whose epilogue moves the most bytes per flop: the 1x1 convs that
 // close a residual unit (residual in, raw + activated out).  ZB200_DAC_TE=0 switches back to direct loads / stores.
 static bool dac_te_enabled() {
-  const char* v = getenv("ZB200_DAC_TE");  // read per call: the parity test compares both epilogues in one process
+  const char* v = zb::tuning_env("ZB200_DAC_TE");  // read per call: the parity test compares both epilogues in one process
   return !(v && atoi(v) == 0);
 }
 static bool dac_wide_epilogue_enabled() {  // ZB200_DAC_EW12=0: 8-warp direct epilogue everywhere (A/B switch)
-  const char* v = getenv("ZB200_DAC_EW12");
+  const char* v = zb::tuning_env("ZB200_DAC_EW12");
   return !(v && atoi(v) == 0);
 }
 template <int NT, int MODE>
@@ -261,7 +261,7 @@ extern "C" int zb200_dac_decode(const zb200_dac_plan* p, const int64_t* codes, i
                                : launch_dac_conv<64, DC_DIRECT_RESID>(L, batch, t, regions, st);
     if (rc != ZB200_OK) return rc;
   }
-  static const bool final_scalar = getenv("ZB200_DAC_FINAL_SCALAR") != nullptr;  // A/B switch
+  static const bool final_scalar = zb::tuning_env("ZB200_DAC_FINAL_SCALAR") != nullptr;  // A/B switch
   if (p->final_wp && p->final_bias8 && !final_scalar && p->final_t_mul % 8 == 0 && (8 * p->final_c) % 64 == 0 &&
       p->final_pitch == p->final_c) {
     // last conv on the tensor cores: rows of 8 time steps (8*final_c channels), 3 row taps, 8 output phases, tanh

@@ -100,7 +100,7 @@ SkPlan plan_deferred(int sms, int rows, int n_tiles, int k_blocks, int64_t ws_fl
   const int cap = sms * (rows <= 32 ? 2 : big_m_ctas_per_sm());
   const int mode = skinny_mode(rows, n_tiles, k_blocks);
   const int groups = n_tiles / skinny_tg(mode), kbu = k_blocks / skinny_kg(mode);
-  static const int max_split = getenv("ZB200_DEF_MAXSPLIT") ? atoi(getenv("ZB200_DEF_MAXSPLIT")) : 64;
+  static const int max_split = zb::tuning_env("ZB200_DEF_MAXSPLIT") ? atoi(zb::tuning_env("ZB200_DEF_MAXSPLIT")) : 64;
   int s = 1;
   for (int c = 1; c <= kbu && c <= max_split; ++c)
     if (groups * c <= cap && kbu / c >= 2 && (int64_t)c * rows * n <= ws_floats) s = c;
@@ -120,7 +120,7 @@ SkinnyCore sk_core(const zb200_engine_desc& d, const void* w, int n_tiles, int r
 
 // Descriptors of "the GEMM after this one" for the in-kernel L2 prefetch of its first weight bytes (gemm_skinny.cuh).
 static int nextw_bytes(int rows) {
-  static const int kb = getenv("ZB200_NEXTW_KB") ? atoi(getenv("ZB200_NEXTW_KB")) : -1;
+  static const int kb = zb::tuning_env("ZB200_NEXTW_KB") ? atoi(zb::tuning_env("ZB200_NEXTW_KB")) : -1;
   (void)rows;
   return kb > 0 ? kb * 1024 : 0;  // off by default: measured neutral at batch 64 and batch 1 (experiments)
 }
@@ -156,7 +156,7 @@ cudaError_t gemm_any(const zb200_engine* e, const void* w, int n_tiles, int rows
   if constexpr (std::is_same<ALoader, ARowMajor>::value) {
     // Many row tiles (the batched prefill): the persistent kernel overlaps each tile's epilogue with the next tile's
     // MMAs.  Small problems keep the per-tile kernel (split-K fills the SMs there).
-    static const bool no_big = getenv("ZB200_NO_BIG") != nullptr;
+    static const bool no_big = zb::tuning_env("ZB200_NO_BIG") != nullptr;
     const int m_tiles = ceil_div(rows, GEMM_BM);
     if (!no_big && g.splits == 1 && e->sk_sms > 0 && m_tiles * ceil_div(n_tiles, 4) >= e->sk_sms) {
       const cudaError_t rc = launch_gemm_big<1>(al.base, al.row_bytes, rows, k, w, n_tiles, epi, e->sk_sms, st);
@@ -216,9 +216,9 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
   const int* pos_ptr = d.state + ST_POS;
   bf16 *x = (bf16*)d.x, *xn = (bf16*)d.xn, *q = (bf16*)d.q, *att = (bf16*)d.att, *h = (bf16*)d.h;
   // at <= 8 rows selected projections run on the operand-swapped kernel (bit 0 in_proj, 2 fc1, 3 heads)
-  static const int swap_env = getenv("ZB200_SWAP_MASK") ? atoi(getenv("ZB200_SWAP_MASK")) : 13;
+  static const int swap_env = zb::tuning_env("ZB200_SWAP_MASK") ? atoi(zb::tuning_env("ZB200_SWAP_MASK")) : 13;
   const int swap_mask = (rows <= 8 && dm % 128 == 0) ? swap_env : 0;
-  static const bool no_qkv_def = getenv("ZB200_NO_QKV_DEFERRED") != nullptr;
+  static const bool no_qkv_def = zb::tuning_env("ZB200_NO_QKV_DEFERRED") != nullptr;
   const bool qkv_deferred = rows > 32 && !no_qkv_def && (hd + 2 * kvd) <= 8192;
   const SkPlan p_qkv = plan_deferred(e->sk_sms, rows, (hd + 2 * kvd) / NT, dm / 64, d.gemm_ws_floats, hd + 2 * kvd);
   const SkPlan p_out = plan_deferred(e->sk_sms, rows, dm / NT, hd / 64, d.gemm_ws_floats, dm);
@@ -482,12 +482,16 @@ int run_decode_small(zb200_engine* e, cudaStream_t st) {
 }
 
 // All transformer layers on `rows` rows of x (seq_len positions per sequence), then norm_f + heads + CFG.
-int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream_t st) {
+// decode: one query per sequence at position *state[ST_POS] (+ pos0); otherwise seq_len positions from pos0 (causal).
+// hidden_out != nullptr: the backbone-only form (TorchZonosBackbone.forward, _torch.py:73-80) -- norm_f over ALL rows is
+// written there and the heads are skipped.
+int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream_t st, int pos0 = 0, bf16* hidden_out = nullptr,
+                 bool pos_from_state = true) {
   const zb200_engine_desc& d = e->d;
   const int dm = d.d_model, hd = d.n_heads * ZB200_HEAD_DIM, kvd = d.n_kv_heads * ZB200_HEAD_DIM;
   const int m_tiles = ceil_div(rows, GEMM_BM);
   const int n_seq = 2 * d.batch;
-  const int* pos_ptr = decode ? d.state + ST_POS : nullptr;
+  const int* pos_ptr = (decode && pos_from_state) ? d.state + ST_POS : nullptr;
   bf16 *x = (bf16*)d.x, *xn = (bf16*)d.xn, *q = (bf16*)d.q, *att = (bf16*)d.att, *h = (bf16*)d.h;
   for (int l = 0; l < d.n_layer; ++l) {
     const bf16* ln1w = (const bf16*)d.ln1_w + (size_t)l * dm;
@@ -498,18 +502,18 @@ int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream
     {  // in_proj + RoPE + KV page write
       const int n_tiles = (hd + 2 * kvd) / NT;
       ARowMajor al{(const uint8_t*)xn, (size_t)dm * 2};
-      EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, 0, seq_len, d.n_heads};
+      EpiQkvRope epi{q, kv_of(d, l), d.rope, pos_ptr, pos0, seq_len, d.n_heads};
       ZB_TRY(gemm_any(e, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, n_tiles, rows, dm, al, epi, st));
     }
     if (decode) {
       AttnDecodeArgs a;
-      a.q = q, a.out = att, a.kv = kv_of(d, l), a.pos_ptr = pos_ptr, a.pos_add = 0;
+      a.q = q, a.out = att, a.kv = kv_of(d, l), a.pos_ptr = pos_ptr, a.pos_add = pos0;
       a.n_heads = d.n_heads, a.n_kv_heads = d.n_kv_heads, a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
       a.partial_ws = d.attn_ws, a.tickets = d.attn_tickets;
       ZB_TRY(launch_attn_decode(a, n_seq, d.attn_nsplit, st));
     } else {
       AttnPrefillArgs a;
-      a.q = q, a.out = att, a.kv = kv_of(d, l), a.seq_len = seq_len, a.pos0 = 0, a.n_heads = d.n_heads;
+      a.q = q, a.out = att, a.kv = kv_of(d, l), a.seq_len = seq_len, a.pos0 = pos0, a.n_heads = d.n_heads;
       a.scale = 1.0f / sqrtf((float)ZB200_HEAD_DIM);
       ZB_TRY(launch_attn_prefill(a, n_seq, st));
     }
@@ -533,6 +537,10 @@ int run_backbone(zb200_engine* e, int rows, int seq_len, bool decode, cudaStream
       ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, n_tiles, rows, d.d_ff, al, epi, st));
     }
   }
+  if (hidden_out) {  // backbone-only: norm_f over every row, no heads
+    ZB_TRY(launch_layernorm(x, (const bf16*)d.lnf_w, (const bf16*)d.lnf_b, hidden_out, rows, dm, d.ln_eps, 1, 0, st));
+    return ZB200_OK;
+  }
   // norm_f on the last position of every sequence, heads + CFG (model.py:110-115)
   ZB_TRY(launch_layernorm(x, (const bf16*)d.lnf_w, (const bf16*)d.lnf_b, xn, n_seq, dm, d.ln_eps, seq_len, seq_len - 1, st));
   {
@@ -553,14 +561,17 @@ static int validate(const zb200_engine_desc& d) {
              "engine: unsupported head layout H=%d Hkv=%d (GQA group <= 4)", d.n_heads, d.n_kv_heads);
   ZB_REQUIRE(d.d_model == d.n_heads * ZB200_HEAD_DIM, "engine: head_dim must be 128 (d_model=%d, H=%d)", d.d_model, d.n_heads);
   ZB_REQUIRE(d.d_ff > 0 && d.d_ff % 64 == 0, "engine: d_ff=%d must be a multiple of 64", d.d_ff);
-  ZB_REQUIRE(d.n_q > 0 && d.n_q <= ZB200_MAX_CODEBOOKS && d.vocab > 1025 && d.vocab <= d.head_rows_padded && d.head_rows_padded % 64 == 0,
+  const bool bb_only = (d.flags & ZB200_ENGINE_BACKBONE_ONLY) != 0;
+  ZB_REQUIRE(bb_only || (d.n_q > 0 && d.n_q <= ZB200_MAX_CODEBOOKS && d.vocab > 1025 && d.vocab <= d.head_rows_padded &&
+                         d.head_rows_padded % 64 == 0),
              "engine: bad codebook/vocab layout");
   ZB_REQUIRE(d.batch > 0 && d.rows_max >= 2 * d.batch, "engine: rows_max=%d < 2*batch", d.rows_max);
   ZB_REQUIRE(d.attn_nsplit >= 1 && d.pages_per_seq > 0 && d.num_pages > 0, "engine: bad KV paging");
-  ZB_REQUIRE(d.emb && d.ln1_w && d.ln1_b && d.ln2_w && d.ln2_b && d.lnf_w && d.lnf_b && d.w_qkv && d.w_out && d.w_fc1 &&
-                 d.w_fc2 && d.w_heads && d.rope && d.kv_pool && d.block_table && d.x && d.xn && d.q && d.att && d.h &&
-                 d.logits && d.gemm_ws && d.gemm_tickets && d.state && d.delayed,
+  ZB_REQUIRE(d.ln1_w && d.ln1_b && d.ln2_w && d.ln2_b && d.lnf_w && d.lnf_b && d.w_qkv && d.w_out && d.w_fc1 && d.w_fc2 &&
+                 d.rope && d.kv_pool && d.block_table && d.x && d.xn && d.q && d.att && d.h && d.gemm_ws && d.gemm_tickets,
              "engine: null buffer in descriptor");
+  ZB_REQUIRE(bb_only || (d.emb && d.w_heads && d.logits && d.state && d.delayed),
+             "engine: null embedding / head / logits / loop-state buffer (only a ZB200_ENGINE_BACKBONE_ONLY engine may omit them)");
   ZB_REQUIRE(d.attn_nsplit == 1 || (d.attn_ws && d.attn_tickets), "engine: split-KV attention needs workspace");
   return ZB200_OK;
 }
@@ -574,11 +585,11 @@ extern "C" int zb200_engine_create(const zb200_engine_desc* desc, zb200_engine**
   {
     int sms = SM_COUNT, dev = 0;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (const char* v = getenv("ZB200_SK_SMS")) sms = atoi(v);  // 0 switches the decode step back to the tiled kernel
+    if (const char* v = zb::tuning_env("ZB200_SK_SMS")) sms = atoi(v);  // 0 switches the decode step back to the tiled kernel
     // fix-up workspace per SM: two CTAs x two slots x one 32 KB sub-tile (M <= 32) or one CTA x two slots x two sub-tiles
     const int64_t cap = desc->gemm_ws_floats / (4 * SK_PARTIAL_F4 * 4);
     e->sk_sms = (int)std::max<int64_t>(0, std::min<int64_t>(sms, cap));
-    if (const char* v = getenv("ZB200_L2_PREFETCH")) e->l2_prefetch = atoi(v);
+    if (const char* v = zb::tuning_env("ZB200_L2_PREFETCH")) e->l2_prefetch = atoi(v);
     if (e->l2_prefetch) {
       cudaError_t ce = cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking);
       if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
@@ -603,8 +614,23 @@ extern "C" void zb200_engine_destroy(zb200_engine* e) {
   delete e;
 }
 
+/* TorchZonosBackbone.forward (zonos/backbone/_torch.py:73-80) on its own: x holds hidden [2B * seq_len, d_model]; the KV
+ * cache is written at positions [pos0, pos0 + seq_len) and norm_f of every row goes to `out` (bf16, same shape). */
+extern "C" int zb200_engine_forward(zb200_engine* e, int seq_len, int pos0, void* out, void* stream) {
+  ZB_REQUIRE(e && seq_len > 0 && pos0 >= 0 && out, "engine_forward: bad arguments");
+  const int rows = 2 * e->d.batch * seq_len;
+  ZB_REQUIRE(rows <= e->d.rows_max, "engine_forward: %d rows exceed the workspace (%d)", rows, e->d.rows_max);
+  if (pos0 + seq_len > e->d.pages_per_seq * ZB200_PAGE) {  // the reference asserts on cache overflow (_torch.py:44-45)
+    set_error("engine_forward: positions up to %d exceed the KV cache (%d)", pos0 + seq_len, e->d.pages_per_seq * ZB200_PAGE);
+    return ZB200_ERR_STATE;
+  }
+  e->launches = 0;
+  return run_backbone(e, rows, seq_len, seq_len == 1, (cudaStream_t)stream, pos0, (bf16*)out, false);
+}
+
 extern "C" int zb200_engine_prefill(zb200_engine* e, int seq_len, void* stream) {
   ZB_REQUIRE(e && seq_len > 0, "engine_prefill: bad arguments");
+  ZB_REQUIRE(!(e->d.flags & ZB200_ENGINE_BACKBONE_ONLY), "engine_prefill: backbone-only engine (use zb200_engine_forward)");
   const int rows = 2 * e->d.batch * seq_len;
   ZB_REQUIRE(rows <= e->d.rows_max, "engine_prefill: %d rows exceed the workspace (%d)", rows, e->d.rows_max);
   if (seq_len > e->d.pages_per_seq * ZB200_PAGE) {
@@ -620,7 +646,7 @@ static int decode_logits(zb200_engine* e, cudaStream_t st) {
   // embed the previous frame (column offset-1) for the B conditional rows and duplicate for the unconditional ones
   ZB_TRY(launch_embed_sum(d.delayed, d.n_q * d.t_delayed, d.t_delayed, d.state + ST_OFFSET, -1, 1, (const bf16*)d.emb,
                           (bf16*)d.x, d.batch, d.n_q, d.vocab, d.d_model, 1, 0, d.batch, st));
-  static const bool all_swap = getenv("ZB200_ALL_SWAP") != nullptr;
+  static const bool all_swap = zb::tuning_env("ZB200_ALL_SWAP") != nullptr;
   if (2 * d.batch <= 8 && e->sk_sms > 0 && all_swap && d.d_model % 128 == 0 && d.d_ff % 128 == 0)
     return run_decode_small(e, st);
   if (chain_supported(e)) return run_decode_chain(e, st);
@@ -630,6 +656,7 @@ static int decode_logits(zb200_engine* e, cudaStream_t st) {
 
 extern "C" int zb200_engine_decode_logits(zb200_engine* e, void* stream) {
   ZB_REQUIRE(e, "engine_decode_logits: null engine");
+  ZB_REQUIRE(!(e->d.flags & ZB200_ENGINE_BACKBONE_ONLY), "engine_decode_logits: backbone-only engine (use zb200_engine_forward)");
   e->launches = 0;
   return decode_logits(e, (cudaStream_t)stream);
 }
@@ -659,6 +686,7 @@ static int step(zb200_engine* e, const zb200_sampler_args* smp, cudaStream_t st)
 
 extern "C" int zb200_engine_step(zb200_engine* e, const zb200_sampler_args* smp, void* stream) {
   ZB_REQUIRE(e && smp && smp->loop_mode == 1, "engine_step: needs loop-mode sampler arguments");
+  ZB_REQUIRE(!(e->d.flags & ZB200_ENGINE_BACKBONE_ONLY), "engine_step: backbone-only engine");
   ZB_REQUIRE(smp->state == e->d.state && smp->delayed == e->d.delayed && smp->logits == e->d.logits,
              "engine_step: sampler buffers differ from the engine's");
   return step(e, smp, (cudaStream_t)stream);
@@ -666,6 +694,7 @@ extern "C" int zb200_engine_step(zb200_engine* e, const zb200_sampler_args* smp,
 
 extern "C" int zb200_engine_capture(zb200_engine* e, const zb200_sampler_args* smp, void* stream) {
   ZB_REQUIRE(e && smp && smp->loop_mode == 1, "engine_capture: needs loop-mode sampler arguments");
+  ZB_REQUIRE(!(e->d.flags & ZB200_ENGINE_BACKBONE_ONLY), "engine_capture: backbone-only engine");
   cudaStream_t st = (cudaStream_t)stream;
   if (e->exec) cudaGraphExecDestroy(e->exec), e->exec = nullptr;
   if (e->graph) cudaGraphDestroy(e->graph), e->graph = nullptr;

@@ -485,7 +485,7 @@ cudaError_t launch_gemm_skinny_n16(const SkinnyCore& g, const ALoader& al, const
 inline int skinny_mode(int m, int n_tiles, int k_blocks, bool prefer_k1 = false) {
   // An N <= 128 UMMA costs ~77 cycles whatever N is (scripts/exp_umma_rate.cu): with N = 64 (K2 / K1) the MMAs of a
   // 16 KB stage take 616 cycles, i.e. ~50 GB/s per SM at best; two tiles per MMA (T2) halve that.
-  static const bool small_t2 = getenv("ZB200_SMALL_T2") != nullptr;  // measured slower at batch 1-16: opt-in
+  static const bool small_t2 = zb::tuning_env("ZB200_SMALL_T2") != nullptr;  // measured slower at batch 1-16: opt-in
   if (m <= 32 && !(small_t2 && n_tiles % 2 == 0 && !prefer_k1)) return (k_blocks % 2 == 0) ? MODE_K2 : MODE_K1;
   return (n_tiles % 2 == 0 && !prefer_k1) ? MODE_T2 : MODE_K1;
 }
@@ -520,7 +520,7 @@ struct SkPlan {
   bool prefer_k1;
 };
 inline int big_m_ctas_per_sm() {  // experiment knob: CTAs per SM the planners assume at rows > 32
-  static const int v = getenv("ZB200_SK_CAP2") ? 2 : 1;
+  static const int v = zb::tuning_env("ZB200_SK_CAP2") ? 2 : 1;
   return v;
 }
 inline SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
@@ -540,7 +540,7 @@ inline SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
       }
     p.grid = cap;  // unaligned stream-K: most groups end up with two contributors
   } else {
-    static const int max_split = getenv("ZB200_SK_MAXSPLIT") ? atoi(getenv("ZB200_SK_MAXSPLIT")) : 3;
+    static const int max_split = zb::tuning_env("ZB200_SK_MAXSPLIT") ? atoi(zb::tuning_env("ZB200_SK_MAXSPLIT")) : 3;
     const int s = std::max(1, std::min(max_split, cap / groups));
     p.grid = groups * s;
   }

@@ -553,12 +553,12 @@ extern "C" int zb200_mamba2_ssd_step(void* ssm_state, const void* xbc, int ld_xb
              "mamba2_ssd_step: unsupported head layout H=%d P=%d G=%d", n_heads, head_dim, n_groups);
   ZB_REQUIRE(ld_xbc >= n_heads * head_dim + 2 * n_groups * d_state && ld_xbc % 8 == 0 && dt_col0 + n_heads <= ld,
              "mamba2_ssd_step: row pitches too small");
-  static const bool one_tile = getenv("ZB200_SSD_ONE_TILE") != nullptr;  // A/B switch
+  static const bool one_tile = zb::tuning_env("ZB200_SSD_ONE_TILE") != nullptr;  // A/B switch
   if (head_dim == 64 && !one_tile) {
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int n_tiles = rows * n_heads;
-    static const int per_sm = getenv("ZB200_SSD_CTAS_PER_SM") ? atoi(getenv("ZB200_SSD_CTAS_PER_SM")) : 6;
+    static const int per_sm = zb::tuning_env("ZB200_SSD_CTAS_PER_SM") ? atoi(zb::tuning_env("ZB200_SSD_CTAS_PER_SM")) : 6;
     const int grid = n_tiles < sms * per_sm ? n_tiles : sms * per_sm;
     ZB_CHECK_CUDA(launch_pdl(mamba2_ssd_step_p64_kernel<128>, dim3((unsigned)grid), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(),
                              (bf16*)ssm_state, (const bf16*)xbc, ld_xbc, (const bf16*)zxbcdt, ld, dt_col0, A_log, D, dt_bias,

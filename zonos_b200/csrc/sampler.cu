@@ -75,7 +75,9 @@ __device__ __forceinline__ uint32_t philox_first(uint32_t c0, uint32_t c1, uint3
 // Exp(1) variate for (seed, draw, global row, vocab index)
 __device__ __forceinline__ float exp1_noise(unsigned long long seed, uint32_t draw, uint32_t grow, uint32_t v) {
   const uint32_t x = philox_first(v, draw, grow, 0x5A6F6E6Fu, (uint32_t)seed, (uint32_t)(seed >> 32));
-  const float u = ((float)x + 0.5f) * 2.3283064365386963e-10f;  // (0, 1)
+  // 24 random bits: (k + 0.5) * 2^-24 is exact in fp32 and strictly inside (0, 1), so q = -log(u) > 0 like
+  // torch.exponential_ (which never returns 0).  ((float)x + 0.5f) * 2^-32 rounds to 1.0f for the top 128 values of x.
+  const float u = ((float)(x >> 8) + 0.5f) * 5.9604644775390625e-08f;
   return -logf(u);
 }
 
@@ -214,7 +216,11 @@ __device__ int sample_row(const SamplerArgs& a, int b, int q, int pass, int offs
     const uint32_t grow = (uint32_t)((a.row_base + b) * a.n_q + q);
     q0 = exp1_noise(a.seed, (uint32_t)draw, grow, v0), q1 = exp1_noise(a.seed, (uint32_t)draw, grow, v1);
   }
-  const float r0 = (v0 < V) ? p0 / q0 : -INFINITY, r1 = (v1 < V) ? p1 / q1 : -INFINITY;
+  // p / q (sampling.py:26-28).  A zero-probability entry (masked EOS, the pad slot, anything a filter removed) scores
+  // exactly 0 like in the reference -- also when injected noise is 0 there (0 / 0 would be NaN) -- and a NaN never wins.
+  float r0 = (v0 < V) ? (p0 > 0.f ? p0 / q0 : 0.f) : -INFINITY, r1 = (v1 < V) ? (p1 > 0.f ? p1 / q1 : 0.f) : -INFINITY;
+  if (!(r0 == r0)) r0 = -INFINITY;
+  if (!(r1 == r1)) r1 = -INFINITY;
   return block_argmax(r0, v0, r1, v1 < V ? v1 : SMP_MAXV, red, redi);
 }
 

@@ -68,6 +68,7 @@ class Zonos(nn.Module):
         for w in [*self.embeddings, *self.heads]:
             pad_weight_(w, self.config.pad_vocab_to_multiple_of)
         self._packed = None
+        self._heads_packed = None
 
     @property
     def device(self) -> torch.device:
@@ -126,6 +127,45 @@ class Zonos(nn.Module):
     def embed_codes(self, codes: torch.Tensor) -> torch.Tensor:
         """zonos/model.py:97-98.  codes int [B, 9, S] -> bf16 [B, S, d]."""
         return ops.embed_codes(codes, self.packed().emb)
+
+    # ---- the reference's building blocks, on the registered backbone (compatibility path; generate() below keeps the
+    # ---- whole loop on the device instead)
+    def apply_heads(self, hidden_states: torch.Tensor) -> torch.Tensor:
+        """zonos/model.py:100-101.  hidden bf16 [B2, S, d] -> bf16 [B2, 9, S, V] (tcgen05 GEMM over the concatenated heads)."""
+        B2, S, d = hidden_states.shape
+        if getattr(self, "_heads_packed", None) is None:
+            w = torch.cat([h.weight for h in self.heads]).detach().to(torch.bfloat16).contiguous()  # [9 * V, d]
+            self._heads_packed = (ops.pack_weight(w), w.shape[0])
+        wp, n = self._heads_packed
+        out = ops.gemm_bf16(hidden_states.reshape(B2 * S, d).contiguous(), wp, n)
+        return out.view(B2, S, N_CODEBOOKS, n // N_CODEBOOKS).permute(0, 2, 1, 3)
+
+    def _compute_logits(self, hidden_states: torch.Tensor, inference_params: InferenceParams, cfg_scale: float) -> torch.Tensor:
+        """zonos/model.py:103-116: last position -> heads -> fp32 -> CFG mix -> pad slots -inf.  Returns fp32 [B, 9, V]."""
+        last = self.backbone(hidden_states, inference_params)[:, -1, :].unsqueeze(1)
+        logits = self.apply_heads(last).squeeze(2).float()
+        if cfg_scale != 1.0:
+            cond, uncond = logits.chunk(2)
+            logits = uncond + (cond - uncond) * cfg_scale
+        logits[..., 1025:].fill_(-torch.inf)
+        return logits
+
+    def _prefill(self, prefix_hidden_states: torch.Tensor, input_ids: torch.Tensor, inference_params: InferenceParams,
+                 cfg_scale: float) -> torch.Tensor:
+        """zonos/model.py:181-202."""
+        if prefix_hidden_states.shape[0] != input_ids.shape[0]:
+            assert prefix_hidden_states.shape[0] % input_ids.shape[0] == 0
+            input_ids = input_ids.repeat(prefix_hidden_states.shape[0] // input_ids.shape[0], 1, 1)
+        hidden = torch.cat([prefix_hidden_states, self.embed_codes(input_ids)], dim=1)
+        return self._compute_logits(hidden, inference_params, cfg_scale)
+
+    def _decode_one_token(self, input_ids: torch.Tensor, inference_params: InferenceParams, cfg_scale: float,
+                          allow_cudagraphs: bool = True) -> torch.Tensor:
+        """zonos/model.py:118-142 (eager form; the graph-replayed form of this package lives inside generate())."""
+        hidden = self.embed_codes(input_ids)
+        if cfg_scale != 1.0:
+            hidden = hidden.repeat(2, 1, 1)
+        return self._compute_logits(hidden, inference_params, cfg_scale)
 
     def setup_cache(self, batch_size: int, max_seqlen: int, dtype: torch.dtype = torch.bfloat16) -> InferenceParams:
         """zonos/model.py:204-208 (max_seqlen rounded up to a multiple of 8, lengths_per_sample int32 zeros)."""
