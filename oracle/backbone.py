@@ -17,10 +17,10 @@ import torch.nn.functional as F
 from .shapes import SHAPES, N_CODEBOOKS
 
 
-def rope_table(n_pos: int, head_dim: int, base: float = 10000.0) -> torch.Tensor:
+def rope_table(n_pos: int, head_dim: int, base: float = 10000.0, device=None) -> torch.Tensor:
     """fp32 [n_pos, head_dim/2, 2] of (cos, sin);  theta_i = base^(-2i/head_dim)."""
-    inv = 1.0 / (base ** (torch.arange(0, head_dim, 2)[: head_dim // 2].float() / head_dim))
-    ang = torch.outer(torch.arange(n_pos), inv)
+    inv = 1.0 / (base ** (torch.arange(0, head_dim, 2, device=device)[: head_dim // 2].float() / head_dim))
+    ang = torch.outer(torch.arange(n_pos, device=device), inv)
     unit = torch.polar(torch.ones_like(ang), ang)
     return torch.stack([unit.real, unit.imag], dim=-1)
 
@@ -39,8 +39,8 @@ def rope_interleaved(x: torch.Tensor, cs: torch.Tensor) -> torch.Tensor:
 class DenseKV:
     """Per-layer dense cache [B2, max_seq, 2, Hkv, D] (the reference layout, _torch.py:96-97)."""
 
-    def __init__(self, n_layer, batch2, max_seq, n_kv, head_dim, dtype=torch.bfloat16):
-        self.buf = [torch.zeros(batch2, max_seq, 2, n_kv, head_dim, dtype=dtype) for _ in range(n_layer)]
+    def __init__(self, n_layer, batch2, max_seq, n_kv, head_dim, dtype=torch.bfloat16, device=None):
+        self.buf = [torch.zeros(batch2, max_seq, 2, n_kv, head_dim, dtype=dtype, device=device) for _ in range(n_layer)]
         self.len = 0  # uniform over the batch (SURVEY Appendix B.7)
 
     def append(self, layer, k, v):

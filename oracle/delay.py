@@ -26,8 +26,8 @@ def revert_delay_pattern_np(delayed: np.ndarray) -> np.ndarray:
 
 
 def apply_delay_pattern(codes: torch.Tensor, mask_token: int) -> torch.Tensor:
-    return torch.from_numpy(apply_delay_pattern_np(codes.cpu().numpy(), mask_token))
+    return torch.from_numpy(apply_delay_pattern_np(codes.cpu().numpy(), mask_token)).to(codes.device)
 
 
 def revert_delay_pattern(delayed: torch.Tensor) -> torch.Tensor:
-    return torch.from_numpy(revert_delay_pattern_np(delayed.cpu().numpy()))
+    return torch.from_numpy(revert_delay_pattern_np(delayed.cpu().numpy())).to(delayed.device)

@@ -28,9 +28,11 @@ class ModelLogits:
     def __init__(self, W, shape_name, prefix_cond, max_positions, cfg_scale):
         self.W, self.shape_name, self.cfg = W, shape_name, cfg_scale
         s = SHAPES[shape_name]
+        self.device = prefix_cond.device  # everything follows the conditioning's device (CPU in the tests; bench.py's
+        # eager-GPU baseline leg passes CUDA tensors)
         self.kv = bb.DenseKV(s["n_layer"], prefix_cond.shape[0], ceil_to(max_positions, 8), s["n_kv_heads"],
-                             s["d_model"] // s["n_heads"], dtype=prefix_cond.dtype)
-        self.table = bb.rope_table(ROPE_ROWS, s["d_model"] // s["n_heads"])
+                             s["d_model"] // s["n_heads"], dtype=prefix_cond.dtype, device=self.device)
+        self.table = bb.rope_table(ROPE_ROWS, s["d_model"] // s["n_heads"], device=self.device)
         self.prefix = prefix_cond
 
     def prefill(self, ids):  # ids [B,9,P+1]
@@ -85,9 +87,10 @@ def generate(source, batch: int, l_cond: int, audio_prefix=None, max_new_tokens:
         return smp.sample(logits, history=history, rp=rp, rp_window=win, noise=noise, **sp)
 
     B, Q = batch, N_CODEBOOKS
+    dev = getattr(source, "device", None)
     P = 0 if audio_prefix is None else audio_prefix.shape[2]
     T = P + max_new_tokens
-    codes = torch.full((B, Q, T), UNKNOWN, dtype=torch.int64)
+    codes = torch.full((B, Q, T), UNKNOWN, dtype=torch.int64, device=dev)
     if audio_prefix is not None:
         codes[..., :P] = audio_prefix
     delayed = apply_delay_pattern(codes, MASK_ID)  # [B,Q,T+Q]
@@ -99,17 +102,17 @@ def generate(source, batch: int, l_cond: int, audio_prefix=None, max_new_tokens:
     delayed[..., offset:offset + 1] = torch.where(frame == UNKNOWN, tok, frame)
 
     V = logits.shape[-1]
-    bias = torch.zeros(B, Q, V)
+    bias = torch.zeros(B, Q, V, device=dev)
     bias[:, 1:, EOS_ID] = -torch.inf
     bias[:, 0, EOS_ID] -= torch.log(torch.tensor(1024.0))
 
     max_steps = delayed.shape[2] - offset
-    remaining = torch.full((B,), max_steps, dtype=torch.int64)
-    stopping = torch.zeros(B, dtype=torch.bool)
-    eos_mode = torch.zeros(B, dtype=torch.bool)
-    grace = torch.full((B,), GRACE_STEPS, dtype=torch.int64)
-    rp = torch.full((B,), rp0)
-    kq = torch.arange(Q)[None, :, None]
+    remaining = torch.full((B,), max_steps, dtype=torch.int64, device=dev)
+    stopping = torch.zeros(B, dtype=torch.bool, device=dev)
+    eos_mode = torch.zeros(B, dtype=torch.bool, device=dev)
+    grace = torch.full((B,), GRACE_STEPS, dtype=torch.int64, device=dev)
+    rp = torch.full((B,), rp0, device=dev)
+    kq = torch.arange(Q, device=dev)[None, :, None]
     step = 0
 
     while int(remaining.max()) > 0:

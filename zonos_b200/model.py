@@ -293,6 +293,7 @@ class Zonos(nn.Module):
             loop, eng, delayed = self._open_session(prefix_conditioning, audio_prefix_codes, max_new_tokens, cfg_scale,
                                                     batch_size, sampling_params, seed, row_base, _noise)
             try:
+                prefill_launches = eng.launches_per_step()  # kernels of the prefill just issued by _open_session
                 loop.sample_first(eng.logits)
                 # ---- decode loop (model.py:345-432)
                 max_steps = loop.max_steps
@@ -341,7 +342,8 @@ class Zonos(nn.Module):
                 if progress is not None:
                     progress.close()
                 self.last_generate_stats = dict(steps=steps, launches_per_step=eng.launches_per_step(),
-                                                attn_nsplit=eng.attn_nsplit, prefill_rows=2 * B * S)
+                                                attn_nsplit=eng.attn_nsplit, prefill_rows=2 * B * S,
+                                                prefill_launches=prefill_launches)
                 out = loop.finish()
             finally:
                 eng.close()

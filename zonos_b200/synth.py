@@ -99,3 +99,71 @@ def hybrid_model(shape: dict = HYBRID, device="cuda", seed: int = 0, head_gain: 
     mshape = dict(d_model=d, d_inner=Di, n_heads=Hm, head_dim=shape["head_dim"], d_state=N, n_groups=G)
     net = HybridBackboneB200(layers, dict(weight=nrm((d,), 1, 0.1)), mshape, device, H, Hkv)
     return ZonosHybridB200(sd, net)
+
+
+# ----------------------------------------------------------------------------------------------- DAC 44.1 kHz decoder
+DAC = dict(n_codebooks=9, codebook_size=1024, codebook_dim=8, latent=1024, dec_ch=1536, strides=(8, 8, 4, 2))
+DAC_TINY = dict(n_codebooks=9, codebook_size=1024, codebook_dim=8, latent=64, dec_ch=128, strides=(8, 8, 4, 2))
+
+
+def dac_state_dict(arch: dict = DAC, device="cuda", seed: int = 7) -> dict:
+    """Random decoder + quantizer tensors with the HF DacModel key names, drawn on the device.  HF's own init (std 0.02,
+    alpha = 1) makes the waveform vanish, so the init is variance-preserving: conv sigma^2 = 1 / (C_in k),
+    transposed conv sigma^2 = stride / (C_in k), the residual branch's 1x1 conv at half gain, Snake alpha ~ U(0.5, 2), last
+    conv small enough to keep tanh unsaturated."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    rn = lambda *sh: torch.randn(*sh, generator=g, device=device)
+    alpha = lambda c: 0.5 + 1.5 * torch.rand(1, c, 1, generator=g, device=device)
+    nq, cs, cd, lat = arch["n_codebooks"], arch["codebook_size"], arch["codebook_dim"], arch["latent"]
+    W = {}
+    for k in range(nq):
+        p = f"quantizer.quantizers.{k}."
+        W[p + "codebook.weight"] = rn(cs, cd)
+        W[p + "out_proj.weight"] = rn(lat, cd, 1) / math.sqrt(cd * nq)
+        W[p + "out_proj.bias"] = 0.01 * rn(lat)
+    C = arch["dec_ch"]
+    W["decoder.conv1.weight"] = rn(C, lat, 7) / math.sqrt(lat * 7)
+    W["decoder.conv1.bias"] = 0.01 * rn(C)
+    for j, s in enumerate(arch["strides"]):
+        p, Co = f"decoder.block.{j}.", C // 2
+        W[p + "snake1.alpha"] = alpha(C)
+        W[p + "conv_t1.weight"] = rn(C, Co, 2 * s) * math.sqrt(s / (C * 2 * s))
+        W[p + "conv_t1.bias"] = 0.01 * rn(Co)
+        for r in (1, 2, 3):
+            q = p + f"res_unit{r}."
+            W[q + "snake1.alpha"] = alpha(Co)
+            W[q + "conv1.weight"] = rn(Co, Co, 7) / math.sqrt(Co * 7)
+            W[q + "conv1.bias"] = 0.01 * rn(Co)
+            W[q + "snake2.alpha"] = alpha(Co)
+            W[q + "conv2.weight"] = 0.5 * rn(Co, Co, 1) / math.sqrt(Co)
+            W[q + "conv2.bias"] = 0.01 * rn(Co)
+        C = Co
+    W["decoder.snake1.alpha"] = alpha(C)
+    W["decoder.conv2.weight"] = 0.15 * rn(1, C, 7) / math.sqrt(C * 7)
+    W["decoder.conv2.bias"] = 0.01 * rn(1)
+    return W
+
+
+# ----------------------------------------------------------------------------------------------- Mamba2 mixer (hybrid)
+def mamba2_mixer_params(d_model: int = 2048, expand: int = 2, head_dim: int = 64, d_state: int = 128, n_groups: int = 1,
+                        d_conv: int = 4, device="cuda", seed: int = 0, dtype=torch.bfloat16) -> dict:
+    """One Mamba2 mixer's parameters in the ranges of its own initialisation (dt in [1e-3, 0.1], A in [1, 16], D ~ 1),
+    drawn on the device; keys as mamba_ssm's Mamba2 module plus a `shape` dict."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    rn = lambda *sh: torch.randn(*sh, generator=g, device=device)
+    ru = lambda *sh: torch.rand(*sh, generator=g, device=device)
+    Di = expand * d_model
+    H, cd = Di // head_dim, Di + 2 * n_groups * d_state
+    dt = torch.exp(ru(H) * (math.log(0.1) - math.log(1e-3)) + math.log(1e-3)).clamp(min=1e-4)
+    return {
+        "in_proj.weight": (rn(2 * Di + 2 * n_groups * d_state + H, d_model) / d_model ** 0.5).to(dtype),
+        "conv1d.weight": (rn(cd, d_conv) / d_conv ** 0.5).to(dtype),
+        "conv1d.bias": (0.1 * rn(cd)).to(dtype),
+        "dt_bias": (dt + torch.log(-torch.expm1(-dt))).float(),
+        "A_log": torch.log(1 + 15 * ru(H)).float(),
+        "D": torch.ones(H, device=device) + 0.1 * rn(H),
+        "norm.weight": (1 + 0.1 * rn(Di)).to(dtype),
+        "out_proj.weight": (rn(d_model, Di) / Di ** 0.5).to(dtype),
+        "shape": dict(d_inner=Di, n_heads=H, head_dim=head_dim, d_state=d_state, n_groups=n_groups, eps=1e-5, d_model=d_model,
+                      d_conv=d_conv),
+    }
