@@ -142,6 +142,31 @@ typedef struct {
 } zb200_sampler_args;
 int zb200_sample(const zb200_sampler_args* args, int pass, void* stream);
 
+/* ---- zonos/conditioning.py:373-389 PrefixConditioner.forward ---------------------------------------
+ * One launch: every conditioner's output row at its position of the prefix (rounded to bf16 like the eager reference),
+ * then nn.LayerNorm over d.  The prefix is tiled by `segments` in conditioner order; a segment is one of
+ *   ZB200_COND_ROWS    rows of an embedding table picked by ids: EspeakPhonemeConditioner (conditioning.py:295-312; ids =
+ *                      tokenised phonemes, text -> phonemes stays on the host) and IntegerConditioner (:340-349, id_offset =
+ *                      -min_val).  table bf16 [n][d], x int32 [B][len]
+ *   ZB200_COND_VECTOR  a conditioner called with None: its learned uncond_vector (:38-40, :46-48).  table bf16 [d], len 1
+ *   ZB200_COND_FOURIER FourierConditioner (:318-337): f = bf16(2 pi bf16((x - min) / (max - min))) @ W^T, [cos f | sin f].
+ *                      table = weight bf16 [d/2][in_dim], x fp32 [B][len][in_dim]
+ *   ZB200_COND_LINEAR  PassthroughConditioner (:352-358) + the base class's linear `project` (:26-27): bf16(x W^T + bias).
+ *                      table = project.weight bf16 [d][in_dim], bias bf16 [d] or NULL, x bf16 [B][len][in_dim]
+ * batch_stride: elements between utterances in x (0 = one input broadcast over the batch, like the reference's expand).
+ * out bf16 [batch][l_total][d]. */
+#define ZB200_MAX_COND_SEGMENTS 12
+enum { ZB200_COND_ROWS = 0, ZB200_COND_VECTOR = 1, ZB200_COND_FOURIER = 2, ZB200_COND_LINEAR = 3 };
+typedef struct {
+  int32_t kind, start, len, in_dim, batch_stride, id_offset;
+  float min_val, max_val;
+  const void* table;
+  const void* bias;
+  const void* x;
+} zb200_cond_segment;
+int zb200_prefix_conditioner(const zb200_cond_segment* segs, int n_segs, int batch, int l_total, int d, const void* ln_w,
+                             const void* ln_b, float eps, void* out, void* stream);
+
 /* ---- engine: the transformer backbone + heads behind Zonos._prefill / _decode_one_token / generate ------------------
  * Replaces TorchZonosBackbone.forward (zonos/backbone/_torch.py:73-80), Zonos.embed_codes/apply_heads/_compute_logits
  * (zonos/model.py:97-116), _decode_one_token (:118-179, incl. the CUDA-graph replay) and _prefill (:181-202).

@@ -218,6 +218,64 @@ def gen_postproc():
     torch.save(out, os.path.join(OUT, "postproc.pt"))
 
 
+# The conditioner list of the Zonos-v0.1 checkpoints (SURVEY Appendix A / CONDITIONING_README.md) at a small width.
+COND_D = 512
+COND_LIST = [
+    dict(type="EspeakPhonemeConditioner", name="espeak"),
+    dict(type="PassthroughConditioner", name="speaker", cond_dim=128, projection="linear", uncond_type="learned"),
+    dict(type="FourierConditioner", name="emotion", input_dim=8, uncond_type="learned"),
+    dict(type="FourierConditioner", name="fmax", min_val=0, max_val=24000, uncond_type="learned"),
+    dict(type="FourierConditioner", name="pitch_std", min_val=0, max_val=400, uncond_type="learned"),
+    dict(type="FourierConditioner", name="speaking_rate", min_val=0, max_val=40, uncond_type="learned"),
+    dict(type="IntegerConditioner", name="language_id", min_val=-1, max_val=126, uncond_type="learned"),
+]
+
+
+def cond_inputs():
+    """Seeded cond_dict in the reference's layout (make_cond_dict, zonos/conditioning.py:484-494): every tensor [1, 1, n],
+    broadcast over the batch -- Conditioner.forward star-unpacks its input (:52) -- and phoneme ids [2, 11] in place of the
+    text (eSpeak is not installed)."""
+    g = torch.Generator().manual_seed(21)
+    ids = torch.randint(0, 189, (2, 11), generator=g)
+    ids[1, :3] = 0  # left padding like tokenize_phonemes (zonos/conditioning.py:190)
+    emo = torch.rand(1, 1, 8, generator=g)
+    return dict(espeak=ids, speaker=torch.randn(1, 1, 128, generator=g).to(torch.bfloat16), emotion=emo / emo.sum(-1, keepdim=True),
+                fmax=torch.tensor(22050.0).view(1, 1, 1), pitch_std=torch.tensor(45.0).view(1, 1, 1),
+                speaking_rate=torch.tensor(15.0).view(1, 1, 1), language_id=torch.tensor(24).view(1, 1, 1))
+
+
+def gen_conditioning():
+    """PrefixConditioner.forward of the unmodified reference (zonos/conditioning.py:373-389), bf16 like from_local makes
+    it, for the full cond_dict and for the unconditional dict prepare_conditioning builds (zonos/model.py:216-217)."""
+    import zonos.conditioning as zcond
+    import zonos.config as zc
+
+    assert len(zcond.SPECIAL_TOKEN_IDS) + len(zcond.symbols) == 189
+    torch.manual_seed(11)
+    pc = zcond.PrefixConditioner(zc.PrefixConditionerConfig(conditioners=[dict(c) for c in COND_LIST], projection="none"), COND_D)
+    with torch.no_grad():
+        for c in pc.conditioners:
+            if c.uncond_vector is not None:
+                c.uncond_vector.normal_()
+        pc.norm.weight.normal_(1.0, 0.1)
+        pc.norm.bias.normal_(0.0, 0.05)
+    pc = pc.to(torch.bfloat16).eval()
+    inp = cond_inputs()
+    orig = (zcond.phonemize, zcond.tokenize_phonemes)
+    zcond.phonemize = lambda texts, languages: texts
+    zcond.tokenize_phonemes = lambda ph: (ph, [ph.shape[1]] * ph.shape[0])
+    try:
+        cd = {k: v for k, v in inp.items()}
+        cd["espeak"] = (inp["espeak"], ["en-us", "en-us"])
+        full = pc(cd)
+        uncond = pc({k: cd[k] for k in pc.required_keys})
+        partial = pc({k: cd[k] for k in ("espeak", "speaker", "language_id")})
+    finally:
+        zcond.phonemize, zcond.tokenize_phonemes = orig
+    torch.save(dict(state_dict=pc.state_dict(), required_keys=sorted(pc.required_keys), full=full, uncond=uncond, partial=partial),
+               os.path.join(OUT, "conditioning.pt"))
+
+
 def gen_model_real():
     """Real-shape model file: the reference's bf16 logits, plus the same prefill in fp32 (oracle port, which the CPU test
     pins bit-exactly to the reference at this shape): |bf16 reference - fp32| is the reference's own rounding noise, the
@@ -242,6 +300,10 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     import_reference()
     torch.set_grad_enabled(False)
+    if "--conditioning" in sys.argv:
+        gen_conditioning()
+        print("conditioning.pt", os.path.getsize(os.path.join(OUT, "conditioning.pt")))
+        return
     if "--real" in sys.argv:  # only the real-shape model file (builds the 1.6 B-parameter reference model on the CPU)
         gen_model_real()
         print("model_real.pt", os.path.getsize(os.path.join(OUT, "model_real.pt")))
@@ -253,6 +315,7 @@ def main():
     gen_model(model, "tiny")
     gen_dac()
     gen_postproc()
+    gen_conditioning()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 
