@@ -290,3 +290,49 @@ def test_hybrid_generate_greedy_teacher_forced_logits_vs_oracle():
     a = model.generate(cond.cuda(), None, max_new_tokens=40, batch_size=B, sampling_params=sp, seed=5)
     b = model.generate(cond.cuda(), None, max_new_tokens=40, batch_size=B, sampling_params=sp, seed=5, _graph=False)
     assert all(torch.equal(x, y) for x, y in zip(a, b)) and all(x.shape == (9, 40) for x in a)
+
+
+def test_hybrid_selected_through_the_backbone_registry():
+    """zonos/model.py:70-77: a config with a non-empty ssm_cfg selects the hybrid backbone.  BACKBONES["b200_hybrid"] holds
+    the parameters under mamba_ssm's names; Zonos.generate on it must equal ZonosHybridB200 built from the same tensors, and
+    the KV pool must hold the attention layers only.  (Parity of the hybrid itself: unpinned)"""
+    import math
+
+    from zonos_b200.backbone import BACKBONES, B200HybridZonosBackbone
+    from zonos_b200.config import ZonosConfig
+    from zonos_b200.hybrid import ZonosHybridB200
+    from zonos_b200.model import DEFAULT_BACKBONE_CLS, Zonos
+
+    cfg = dict(backbone=dict(d_model=256, n_layer=5, attn_layer_idx=[2, 4], ssm_cfg=dict(layer="Mamba2"), attn_mlp_d_intermediate=512,
+                             attn_cfg=dict(num_heads=2, num_heads_kv=1), rms_norm=True, norm_epsilon=1e-5),
+               prefix_conditioner=dict(conditioners=[], projection="none"), eos_token_id=1024, masked_token_id=1025,
+               pad_vocab_to_multiple_of=8)
+    zc = ZonosConfig.from_dict(cfg)
+    assert BACKBONES["b200_hybrid"] is B200HybridZonosBackbone and DEFAULT_BACKBONE_CLS is BACKBONES["b200"]
+    torch.manual_seed(0)
+    m = Zonos(zc, BACKBONES["b200_hybrid"])
+    with torch.no_grad():
+        for blk in m.backbone.layers:
+            if hasattr(blk.mixer, "A_log"):
+                H = blk.mixer.A_log.numel()
+                dt = torch.exp(torch.rand(H) * (math.log(0.1) - math.log(1e-3)) + math.log(1e-3))
+                blk.mixer.dt_bias.copy_(dt + torch.log(-torch.expm1(-dt)))
+                blk.mixer.A_log.copy_(torch.log(1 + 15 * torch.rand(H)))
+        for h in m.heads:
+            h.weight.mul_(4.0)
+        m.heads[0].weight[1024].zero_()
+    m.load_state_dict(m.state_dict())
+    m = m.to("cuda", torch.bfloat16)
+    for blk in m.backbone.layers:  # mamba_ssm keeps these in fp32
+        if hasattr(blk.mixer, "A_log"):
+            blk.mixer.dt_bias.data, blk.mixer.A_log.data, blk.mixer.D.data = (t.data.float() for t in (blk.mixer.dt_bias, blk.mixer.A_log, blk.mixer.D))
+    B, Lc, N = 2, 5, 8
+    cond = torch.nn.functional.layer_norm(torch.randn(2 * B, Lc, 256, generator=torch.Generator().manual_seed(1)), (256,)).bfloat16().cuda()
+    sp = dict(temperature=0.0, repetition_penalty=1.0)
+    got = m.generate(cond, None, max_new_tokens=N, batch_size=B, sampling_params=dict(sp), progress_bar=False)
+    net = m.backbone.net()
+    assert sorted(net.kv_slot) == [2, 4]
+    cache = net.allocate_inference_cache(2 * B, 32)
+    assert cache["kv"].pool.shape[0] == 2  # attention layers only, not all 5
+    direct = ZonosHybridB200(m.state_dict(), net).generate(cond, None, max_new_tokens=N, batch_size=B, sampling_params=dict(sp))
+    assert len(got) == B and all(torch.equal(a, b) for a, b in zip(got, direct)) and all(o.shape == (9, N) for o in got)

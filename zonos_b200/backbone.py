@@ -107,3 +107,114 @@ class B200ZonosBackbone(nn.Module):
 
 
 BACKBONES = {"b200": B200ZonosBackbone}
+
+
+# ---------------------------------------------------------------------------------------------------- hybrid
+class _Mamba2Params(nn.Module):
+    """Parameters of one mamba_ssm Mamba2 mixer, under mamba_ssm's names (in_proj, conv1d, dt_bias, A_log, D, norm,
+    out_proj) so that a hybrid checkpoint's `backbone.layers.{i}.mixer.*` tensors load.  PARITY UNPINNED: mamba_ssm 2.2.4 is
+    not installed here; names and shapes are restated from its published module."""
+
+    def __init__(self, d, ssm_cfg):
+        super().__init__()
+        expand, hd = ssm_cfg.get("expand", 2), ssm_cfg.get("headdim", 64)
+        N, G, K = ssm_cfg.get("d_state", 128), ssm_cfg.get("ngroups", 1), ssm_cfg.get("d_conv", 4)
+        Di = expand * d
+        H = Di // hd
+        self.shape = dict(d_model=d, d_inner=Di, n_heads=H, head_dim=hd, d_state=N, n_groups=G, d_conv=K)
+        self.in_proj = nn.Linear(d, 2 * Di + 2 * G * N + H, bias=False)
+        self.conv1d = nn.Conv1d(Di + 2 * G * N, Di + 2 * G * N, K, groups=Di + 2 * G * N, padding=K - 1)
+        self.dt_bias, self.A_log, self.D = nn.Parameter(torch.zeros(H)), nn.Parameter(torch.zeros(H)), nn.Parameter(torch.ones(H))
+        self.norm = nn.Module()
+        self.norm.weight = nn.Parameter(torch.ones(Di))
+        self.out_proj = nn.Linear(Di, d, bias=False)
+
+
+class _HybridBlock(nn.Module):
+    def __init__(self, cfg: BackboneConfig, is_attn: bool):
+        super().__init__()
+        d = cfg.d_model
+        Norm = (lambda: _RMSWeight(d)) if cfg.rms_norm else (lambda: nn.LayerNorm(d, eps=cfg.norm_epsilon))
+        self.norm = Norm()
+        if is_attn:
+            H, Hkv = cfg.attn_cfg["num_heads"], cfg.attn_cfg["num_heads_kv"]
+            self.mixer = _Mixer(d, H, Hkv, d // H)
+            d_mlp = cfg.attn_mlp_d_intermediate
+        else:
+            self.mixer = _Mamba2Params(d, cfg.ssm_cfg)
+            d_mlp = cfg.d_intermediate
+        if d_mlp:
+            self.norm2 = Norm()
+            self.mlp = _Mlp(d, d_mlp)
+
+
+class _RMSWeight(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(d))
+
+
+class B200HybridZonosBackbone(nn.Module):
+    """BACKBONES["b200_hybrid"]: the reference's MambaSSMZonosBackbone (zonos/backbone/_mamba_ssm.py:9-57) as a parameter
+    container whose compute is zonos_b200.hybrid.HybridBackboneB200 (Mamba2 step / scan kernels + the transformer path's
+    attention and GEMM kernels, host-sequenced).  Selected by from_local when `ssm_cfg` is non-empty, like the reference
+    (zonos/model.py:70-77).  PARITY UNPINNED against mamba_ssm (absent here)."""
+
+    supported_architectures = ["transformer", "hybrid"]
+
+    def __init__(self, config: BackboneConfig):
+        super().__init__()
+        self.config = config
+        attn = set(config.attn_layer_idx)
+        self.layers = nn.ModuleList(_HybridBlock(config, i in attn) for i in range(config.n_layer))
+        self.norm_f = _RMSWeight(config.d_model) if config.rms_norm else nn.LayerNorm(config.d_model, eps=config.norm_epsilon)
+        self._net = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self._net = None
+        return super()._load_from_state_dict(*args, **kwargs)
+
+    def net(self):
+        """The kernel-side backbone built from this module's tensors (once per load)."""
+        from .hybrid import HybridBackboneB200
+
+        if self._net is None:
+            cfg, dev = self.config, self.norm_f.weight.device
+            if dev.type != "cuda":
+                raise RuntimeError("zonos_b200 runs on CUDA (B200) only; move the model with .to('cuda')")
+            layers, shape = [], None
+            for blk in self.layers:
+                m = blk.mixer
+                p = {"norm.weight": blk.norm.weight, "norm.bias": getattr(blk.norm, "bias", None),
+                     "in_proj.weight": m.in_proj.weight, "out_proj.weight": m.out_proj.weight}
+                if isinstance(m, _Mamba2Params):
+                    shape = m.shape
+                    p.update({"kind": "mamba2", "conv1d.weight": m.conv1d.weight.squeeze(1), "conv1d.bias": m.conv1d.bias,
+                              "dt_bias": m.dt_bias, "A_log": m.A_log, "D": m.D, "mixer_norm.weight": m.norm.weight})
+                else:
+                    p["kind"] = "attn"
+                if hasattr(blk, "mlp"):
+                    p.update({"norm2.weight": blk.norm2.weight, "norm2.bias": getattr(blk.norm2, "bias", None),
+                              "fc1.weight": blk.mlp.fc1.weight, "fc2.weight": blk.mlp.fc2.weight})
+                layers.append({k: v for k, v in p.items() if v is not None})
+            assert shape is not None, "a hybrid backbone needs at least one Mamba2 layer"
+            nf = {"weight": self.norm_f.weight}
+            if getattr(self.norm_f, "bias", None) is not None:
+                nf["bias"] = self.norm_f.bias
+            self._net = HybridBackboneB200(layers, nf, shape, dev, cfg.attn_cfg["num_heads"], cfg.attn_cfg["num_heads_kv"],
+                                           rms_norm=cfg.rms_norm, eps=cfg.norm_epsilon)
+        return self._net
+
+    def allocate_inference_cache(self, batch_size: int, max_seqlen: int, dtype: torch.dtype = torch.bfloat16):
+        assert dtype == torch.bfloat16, "the B200 caches are bf16"
+        return self.net().allocate_inference_cache(batch_size, max_seqlen)
+
+    def forward(self, hidden_states: torch.Tensor, inference_params) -> torch.Tensor:
+        """[B2, S, d] -> [B2, S, d]; inference_params.key_value_memory_dict is allocate_inference_cache's dict."""
+        B2, S, d = hidden_states.shape
+        cache = inference_params.key_value_memory_dict
+        cache["seqlen_offset"] = int(inference_params.seqlen_offset)
+        return self.net().forward(hidden_states.reshape(B2 * S, d).contiguous(), cache, seq_len=S).view(B2, S, d)
+
+
+BACKBONES["b200_hybrid"] = B200HybridZonosBackbone

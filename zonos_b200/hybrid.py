@@ -130,7 +130,10 @@ class HybridBackboneB200:
 
     def allocate_inference_cache(self, n_seq, max_seqlen):
         s = self.s
-        kv = ops.PagedKV(len(self.layers), n_seq, max_seqlen, self.Hkv, self.device)
+        # the pool holds the ATTENTION layers only (one slot each, like mamba_ssm's per-layer caches, _mamba_ssm.py:33-44):
+        # a Zonos hybrid has an attention block at every ~9th layer, a pool over all layers would be ~7x too large
+        self.kv_slot = {li: n for n, li in enumerate(i for i, L in enumerate(self.layers) if L["kind"] == "attn")}
+        kv = ops.PagedKV(max(1, len(self.kv_slot)), n_seq, max_seqlen, self.Hkv, self.device)
         states = []
         for L in self.layers:
             if L["kind"] == "mamba2":
@@ -167,22 +170,23 @@ class HybridBackboneB200:
                                             use_initial_state=pos0 > 0)
                 mixed = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
             else:
+                slot = self.kv_slot[li]
                 qkv = self._gemm(hn, L["w_in"], (self.H + 2 * self.Hkv) * 128)
                 q, k, v = ops.rope_split(qkv, self.inv_freq, seq_len, pos0, self.H, self.Hkv, pos_ptr=pos_ptr)
                 if pos_ptr is not None:
-                    ops.kv_write_at(cache["kv"], li, k, v, pos_ptr)
-                    mixed = ops.attn_decode_at(q, cache["kv"], li, pos_ptr, self.H)
+                    ops.kv_write_at(cache["kv"], slot, k, v, pos_ptr)
+                    mixed = ops.attn_decode_at(q, cache["kv"], slot, pos_ptr, self.H)
                     hidden = self._gemm(mixed, L["w_out"], s["d_model"])
                     if "w_fc1" in L:
                         hn2, residual = ops.add_norm(hidden, residual, L["n2w"], L["n2b"], self.eps, self.rms)
                         h1 = ops.gated_mlp_act(self._gemm(hn2, L["w_fc1"], 2 * L["d_ff"]))
                         hidden = self._gemm(h1, L["w_fc2"], s["d_model"])
                     continue
-                ops.kv_write(cache["kv"], li, k.view(n_seq, seq_len, self.Hkv, 128), v.view(n_seq, seq_len, self.Hkv, 128), pos0)
+                ops.kv_write(cache["kv"], slot, k.view(n_seq, seq_len, self.Hkv, 128), v.view(n_seq, seq_len, self.Hkv, 128), pos0)
                 if decode:
-                    mixed = ops.attn_decode(q, cache["kv"], li, pos0 + 1, self.H)
+                    mixed = ops.attn_decode(q, cache["kv"], slot, pos0 + 1, self.H)
                 else:
-                    mixed = ops.attn_prefill(q.view(n_seq, seq_len, self.H * 128), cache["kv"], li, pos0, self.H).view(-1, self.H * 128)
+                    mixed = ops.attn_prefill(q.view(n_seq, seq_len, self.H * 128), cache["kv"], slot, pos0, self.H).view(-1, self.H * 128)
             hidden = self._gemm(mixed, L["w_out"], s["d_model"])
             if "w_fc1" in L:
                 hn2, residual = ops.add_norm(hidden, residual, L["n2w"], L["n2b"], self.eps, self.rms)

@@ -92,7 +92,10 @@ class Zonos(nn.Module):
         import safetensors
 
         config = ZonosConfig.from_dict(json.load(open(config_path)))
-        backbone_cls = BACKBONES[backbone] if backbone else DEFAULT_BACKBONE_CLS  # KeyError on an unknown name
+        if backbone:
+            backbone_cls = BACKBONES[backbone]  # KeyError on an unknown name
+        else:  # zonos/model.py:70-77: the transformer backbone unless the checkpoint has Mamba2 layers
+            backbone_cls = DEFAULT_BACKBONE_CLS if not config.backbone.ssm_cfg else BACKBONES["b200_hybrid"]
         model = cls(config, backbone_cls).to(device, torch.bfloat16)
         model.autoencoder.to(device)
         sd = model.state_dict()
@@ -274,6 +277,13 @@ class Zonos(nn.Module):
         assert cfg_scale != 1, "TODO: add support for cfg_scale=1"
         if batch_size * 2 != prefix_conditioning.shape[0]:
             raise ValueError(f"Batch size mismatch: {batch_size} * 2 != {prefix_conditioning.shape[0]}")
+        if hasattr(self.backbone, "net"):  # BACKBONES["b200_hybrid"]: host-sequenced kernels, decode step from a CUDA graph
+            from .hybrid import ZonosHybridB200
+
+            if getattr(self, "_hybrid", None) is None or self._hybrid.backbone is not self.backbone.net():
+                self._hybrid = ZonosHybridB200(self.state_dict(), self.backbone.net())
+            return self._hybrid.generate(prefix_conditioning, audio_prefix_codes, max_new_tokens, cfg_scale, batch_size,
+                                         sampling_params, seed=0 if seed is None else seed, row_base=row_base, _tap=_tap)
         device = self.device
         pw = self.packed()
         cfg = self.config.backbone
