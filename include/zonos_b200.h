@@ -142,6 +142,25 @@ typedef struct {
 } zb200_sampler_args;
 int zb200_sample(const zb200_sampler_args* args, int pass, void* stream);
 
+/* ---- zonos/autoencoder.py:27-28 DACAutoencoder.encode -> HF DacModel.encode (modeling_dac.py:581-605)
+ * The reference encodes in fp32 (no autocast) and the result is integer codes picked by an argmax, so these are plain
+ * fp32 kernels on channels-first tensors [B][C][T] like torch.
+ * zb200_conv1d_f32: nn.Conv1d with stride / dilation / zero padding (DacEncoder convs :442-472, DacEncoderBlock's strided
+ *   conv :222-224, DacResidualUnit's convs :181-185); w_ckn = the weight permuted to [C_in][K][C_out]; resid (optional,
+ *   [B][C_out][T_out]) is added to the result (the residual unit's `hidden_state + output_tensor`, :207).
+ * zb200_snake_f32: Snake1d (:94-99), alpha fp32 [C].
+ * zb200_rvq_encode: DacResidualVectorQuantizer.forward (:300-343) in eval mode with all codebooks -- per codebook in_proj,
+ *   F.normalize, dist = -(|e|^2 - 2 e.c) + |c|^2 over the normalised codebook, first-index argmax (:154-166), out_proj of
+ *   the picked code, residual update.  latent fp32 [B][H][T]; in_w [Q][D][H], in_b [Q][D], codebook [Q][N][D],
+ *   codebook_norm [Q][N][D+1] (F.normalize(codebook) and, last, its squared norm), out_w [Q][H][D], out_b [Q][H];
+ *   codes int64 [B][Q][T]. */
+int zb200_conv1d_f32(const float* x, const float* w_ckn, const float* bias, const float* resid, float* out, int batch, int c_in,
+                     int c_out, int t_in, int t_out, int k, int stride, int dilation, int pad, void* stream);
+int zb200_snake_f32(const float* x, const float* alpha, float* out, int batch, int channels, int t, void* stream);
+int zb200_rvq_encode(const float* latent, const float* in_w, const float* in_b, const float* codebook, const float* codebook_norm,
+                     const float* out_w, const float* out_b, int64_t* codes, int batch, int n_q, int hidden, int dim, int n_codes,
+                     int t, void* stream);
+
 /* ---- zonos/conditioning.py:373-389 PrefixConditioner.forward ---------------------------------------
  * One launch: every conditioner's output row at its position of the prefix (rounded to bf16 like the eager reference),
  * then nn.LayerNorm over d.  The prefix is tiled by `segments` in conditioner order; a segment is one of

@@ -85,3 +85,44 @@ def decode_fp16_storage(W, codes, strides=(8, 8, 4, 2)):
             x = _h(x + y)
     x = _h(F.conv1d(_h(snake(x, W["decoder.snake1.alpha"])), _h(W["decoder.conv2.weight"]), W["decoder.conv2.bias"], padding=3))
     return torch.tanh(x).float()
+
+
+# ----------------------------------------------------------------------------------------------- encoder + RVQ (fp32)
+# Restates zonos/autoencoder.py:27-28 (DACAutoencoder.encode) -> DacModel.encode (modeling_dac.py:581-605): DacEncoder.forward
+# (:462-472), DacEncoderBlock.forward (:226-232), DacResidualUnit.forward (:187-207), DacResidualVectorQuantizer.forward
+# (:300-343, eval mode, all codebooks) and DacVectorQuantize.forward / decode_latents (:128-170).
+def encoder(W, wav, strides=(2, 4, 8, 8)):
+    """wav fp32 [B,1,T] -> latent [B,hidden,T / prod(strides)]."""
+    x = F.conv1d(wav, W["encoder.conv1.weight"], W["encoder.conv1.bias"], padding=3)
+    for j, s in enumerate(strides):
+        p = f"encoder.block.{j}."
+        for r, dil in ((1, 1), (2, 3), (3, 9)):
+            x = _res_unit(W, p + f"res_unit{r}.", x, dil)
+        x = F.conv1d(snake(x, W[p + "snake1.alpha"]), W[p + "conv1.weight"], W[p + "conv1.bias"], stride=s, padding=math.ceil(s / 2))
+    return F.conv1d(snake(x, W["encoder.snake1.alpha"]), W["encoder.conv2.weight"], W["encoder.conv2.bias"], padding=1)
+
+
+def rvq_encode(W, latent, n_q=9, return_margins=False):
+    """latent [B,H,T] -> codes int64 [B,n_q,T] (and, optionally, the gap between the best and the second-best distance of
+    every pick, which is what decides whether a differing code is a tie)."""
+    residual, codes, margins = latent, [], []
+    B, H, T = latent.shape
+    for k in range(n_q):
+        p = f"quantizer.quantizers.{k}."
+        proj = F.conv1d(residual, W[p + "in_proj.weight"], W[p + "in_proj.bias"])
+        enc = F.normalize(proj.permute(0, 2, 1).reshape(B * T, -1))
+        cb = F.normalize(W[p + "codebook.weight"])
+        dist = -(enc.pow(2).sum(1, keepdim=True) - 2 * enc @ cb.t()) + cb.pow(2).sum(1, keepdim=True).t()
+        top2 = dist.topk(2, dim=1)
+        idx = dist.max(1)[1].reshape(B, T)
+        q = F.embedding(idx, W[p + "codebook.weight"]).transpose(1, 2)
+        residual = residual - F.conv1d(q, W[p + "out_proj.weight"], W[p + "out_proj.bias"])
+        codes.append(idx)
+        margins.append((top2.values[:, 0] - top2.values[:, 1]).reshape(B, T))
+    codes = torch.stack(codes, dim=1)
+    return (codes, torch.stack(margins, dim=1)) if return_margins else codes
+
+
+def encode(W, wav, strides=(2, 4, 8, 8), return_margins=False):
+    """wav fp32 [B,1,T] (T a multiple of the hop) -> codes int64 [B,9,T/hop]."""
+    return rvq_encode(W, encoder(W, wav.float(), strides), return_margins=return_margins)

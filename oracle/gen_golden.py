@@ -197,6 +197,35 @@ def gen_dac():
     torch.save(out, os.path.join(OUT, "dac.pt"))
 
 
+def gen_dac_encode():
+    """DacModel.encode (HF, fp32 CPU: the reference's DACAutoencoder.encode, zonos/autoencoder.py:27-28) on seeded
+    waveforms; the codes are the golden.  Tiny and real architecture."""
+    from transformers.models.dac import DacConfig, DacModel
+
+    out = {}
+    for arch_name, enc, dec in (("tiny", shapes.DAC_ENC_TINY, shapes.DAC_TINY), ("real", shapes.DAC_ENC, shapes.DAC)):
+        cfg = DacConfig(sampling_rate=44100, encoder_hidden_size=enc["enc_ch"], hidden_size=enc["latent"],
+                        decoder_hidden_size=dec["dec_ch"])
+        m = DacModel(cfg).eval()
+        W = dict(shapes.synth_dac_weights(seed=7, arch=dec))
+        W.update(shapes.synth_dac_encoder_weights(seed=8, arch=enc))
+        sd = m.state_dict()
+        for k, v in W.items():
+            assert sd[k].shape == v.shape, (k, sd[k].shape, v.shape)
+        sd.update(W)
+        m.load_state_dict(sd)
+        g = torch.Generator().manual_seed(12)
+        cases = [(1, 1), (2, 9), (3, 40)] if arch_name == "tiny" else [(1, 9), (2, 20)]
+        res = []
+        for B, T in cases:
+            wav = 0.3 * torch.randn(B, 1, 512 * T, generator=g)
+            with torch.no_grad():
+                codes = m.encode(wav).audio_codes
+            res.append(dict(wav=wav, codes=codes))
+        out[arch_name] = dict(cases=res, weights_checksum=weights_checksum(W))
+    torch.save(out, os.path.join(OUT, "dac_encode.pt"))
+
+
 def gen_postproc():
     """The reference's codes_to_wavs with decode patched to hand back the test waveform.  pyloudnorm is not installed
     here, so its normalize_loudness takes its own except-branch (audio unchanged): these fixtures pin the trim and the
@@ -300,6 +329,10 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     import_reference()
     torch.set_grad_enabled(False)
+    if "--dac-encode" in sys.argv:
+        gen_dac_encode()
+        print("dac_encode.pt", os.path.getsize(os.path.join(OUT, "dac_encode.pt")))
+        return
     if "--conditioning" in sys.argv:
         gen_conditioning()
         print("conditioning.pt", os.path.getsize(os.path.join(OUT, "conditioning.pt")))
@@ -316,6 +349,7 @@ def main():
     gen_dac()
     gen_postproc()
     gen_conditioning()
+    gen_dac_encode()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -124,3 +124,41 @@ def synth_dac_weights(seed: int = 7, arch: dict = DAC) -> dict:
     W["decoder.conv2.weight"] = 0.15 * torch.randn(1, C, 7, generator=g) / math.sqrt(C * 7)  # keep tanh unsaturated
     W["decoder.conv2.bias"] = 0.01 * torch.randn(1, generator=g)
     return W
+
+
+DAC_ENC = dict(enc_ch=64, strides=(2, 4, 8, 8), latent=1024, n_codebooks=9, codebook_size=1024, codebook_dim=8)
+DAC_ENC_TINY = dict(enc_ch=8, strides=(2, 4, 8, 8), latent=64, n_codebooks=9, codebook_size=1024, codebook_dim=8)
+
+
+def synth_dac_encoder_weights(seed: int = 8, arch: dict = DAC_ENC) -> dict:
+    """fp32 encoder + quantizer-input weights with the HF DacModel key names; variance-preserving like synth_dac_weights
+    (conv sigma^2 = 1/(C_in*k), residual 1x1 at half gain, alpha ~ U(0.5,2)); in_proj rows ~ N(0, 1/H) so the projected
+    latents are O(1) before F.normalize."""
+    g = torch.Generator().manual_seed(seed)
+    W = {}
+    C = arch["enc_ch"]
+    W["encoder.conv1.weight"] = torch.randn(C, 1, 7, generator=g) / math.sqrt(7)
+    W["encoder.conv1.bias"] = 0.01 * torch.randn(C, generator=g)
+    for j, s in enumerate(arch["strides"]):
+        p = f"encoder.block.{j}."
+        for r in (1, 2, 3):
+            q = p + f"res_unit{r}."
+            W[q + "snake1.alpha"] = 0.5 + 1.5 * torch.rand(1, C, 1, generator=g)
+            W[q + "conv1.weight"] = torch.randn(C, C, 7, generator=g) / math.sqrt(C * 7)
+            W[q + "conv1.bias"] = 0.01 * torch.randn(C, generator=g)
+            W[q + "snake2.alpha"] = 0.5 + 1.5 * torch.rand(1, C, 1, generator=g)
+            W[q + "conv2.weight"] = 0.5 * torch.randn(C, C, 1, generator=g) / math.sqrt(C)
+            W[q + "conv2.bias"] = 0.01 * torch.randn(C, generator=g)
+        W[p + "snake1.alpha"] = 0.5 + 1.5 * torch.rand(1, C, 1, generator=g)
+        W[p + "conv1.weight"] = torch.randn(2 * C, C, 2 * s, generator=g) / math.sqrt(C * 2 * s)
+        W[p + "conv1.bias"] = 0.01 * torch.randn(2 * C, generator=g)
+        C *= 2
+    H = arch["latent"]
+    W["encoder.snake1.alpha"] = 0.5 + 1.5 * torch.rand(1, C, 1, generator=g)
+    W["encoder.conv2.weight"] = torch.randn(H, C, 3, generator=g) / math.sqrt(C * 3)
+    W["encoder.conv2.bias"] = 0.01 * torch.randn(H, generator=g)
+    for k in range(arch["n_codebooks"]):
+        p = f"quantizer.quantizers.{k}."
+        W[p + "in_proj.weight"] = torch.randn(arch["codebook_dim"], H, 1, generator=g) / math.sqrt(H)
+        W[p + "in_proj.bias"] = 0.01 * torch.randn(arch["codebook_dim"], generator=g)
+    return W

@@ -13,8 +13,7 @@ class DACAutoencoder:
     Weights: like zonos/autoencoder.py:13-19 the constructor loads `descript/dac_44khz` through transformers -- local
     files first, then the hub.  Where neither is reachable (this build container, the GPU box) the reference would raise
     in __init__; here the error is kept and raised by the first decode(), so that tests and the benchmark can hand over a
-    state dict with the HF key names instead (load_dac_state_dict).  Only the decoder + quantizer tensors are used: the
-    DAC ENCODER is not built, see encode()."""
+    state dict with the HF key names instead (load_dac_state_dict: `decoder.*`, `quantizer.*` and, for encode(), `encoder.*`)."""
 
     PRETRAINED = "descript/dac_44khz"
 
@@ -23,6 +22,7 @@ class DACAutoencoder:
         self.num_codebooks = 9
         self.sampling_rate = 44100
         self._decoder = None
+        self._encoder = None
         self._sd = None  # HF state dict waiting for a CUDA device
         self._load_error = "no DAC weights given"
         self._postproc = {}
@@ -41,7 +41,7 @@ class DACAutoencoder:
             self.codebook_size = dac.config.codebook_size
             self.num_codebooks = dac.quantizer.n_codebooks
             self.sampling_rate = dac.config.sampling_rate
-            self._sd = {k: v.detach() for k, v in dac.state_dict().items() if k.startswith(("decoder.", "quantizer."))}
+            self._sd = {k: v.detach() for k, v in dac.state_dict().items() if k.startswith(("decoder.", "quantizer.", "encoder."))}
             self._load_error = None
         except Exception as e:  # offline and not cached: deferred to the first decode()
             self._load_error = f"{self.PRETRAINED} could not be loaded through transformers ({type(e).__name__}: {e})"
@@ -63,7 +63,7 @@ class DACAutoencoder:
 
     def load_dac_state_dict(self, sd: dict):
         """HF DacModel key names (`decoder.*`, `quantizer.quantizers.{k}.*`); replaces whatever was loaded before."""
-        self._sd, self._decoder, self._load_error = dict(sd), None, None
+        self._sd, self._decoder, self._encoder, self._load_error = dict(sd), None, None, None
         if self._device.type == "cuda":
             self._build()
         return self
@@ -87,13 +87,20 @@ class DACAutoencoder:
         return torch.nn.functional.pad(wav, (pad, 0))
 
     def encode(self, wav: torch.Tensor) -> torch.Tensor:
-        """zonos/autoencoder.py:27-28.  NOT BUILT: the DAC encoder + RVQ search is SURVEY 8(f) rank 4 (next row); audio-prefix
-        codes have to come from the reference's DACAutoencoder.encode / HF DacModel.encode for now."""
-        raise NotImplementedError("zonos_b200 does not implement the DAC encoder (SURVEY 8(f) rank 4); encode the audio "
-                                  "prefix with transformers' DacModel.encode and pass the codes to generate()")
+        """zonos/autoencoder.py:27-28: fp32 [B, 1, T] -> codes int64 [B, 9, T / 512] (HF DacModel.encode(...).audio_codes),
+        fp32 kernels like the reference's un-autocast encode (zonos_b200/dac_encoder.py)."""
+        if self._encoder is None:
+            from .dac_encoder import DacEncoderB200
+
+            if self._sd is None or "encoder.conv1.weight" not in self._sd:
+                raise RuntimeError(f"DAC encoder weights not loaded ({self._load_error or 'the state dict has no encoder.* tensors'})")
+            if self._device.type != "cuda":
+                raise RuntimeError("zonos_b200 runs on CUDA (B200) only; move the autoencoder with .to('cuda')")
+            self._encoder = DacEncoderB200(self._sd, self._device)
+        return self._encoder.encode(wav)
 
     def load_prefix_audio(self, audio_path, device):
-        """zonos/autoencoder.py:30-42 (needs encode(): see there)."""
+        """zonos/autoencoder.py:30-42."""
         import torchaudio
 
         wav, sr = torchaudio.load(audio_path)
