@@ -177,3 +177,4 @@ def test_real_shape_c3_sampling_tokens(real_model, real_weights):
     # among the 2-3 min-p survivors to be closer than the logit perturbation (|dlogit| rms ~0.07, max ~0.25 at this shape,
     # the reference's own bf16 noise), which happens for ~5 % of the draws (observed 22 / 432); gate at 10 %.
     assert flips <= total // 10
+

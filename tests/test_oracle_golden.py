@@ -137,6 +137,18 @@ def test_dac_decode(golden):
             assert 0.05 < float(case["wav"].std()) < 0.9  # the fixture is not degenerate / saturated
 
 
+def test_dac_encode(golden):
+    """oracle.dac.encode (encoder + RVQ, fp32) against HF DacModel.encode's codes (tests/golden/dac_encode.pt): bit-exact."""
+    g = golden("dac_encode.pt")
+    for name, enc, dec in (("tiny", shapes.DAC_ENC_TINY, shapes.DAC_TINY), ("real", shapes.DAC_ENC, shapes.DAC)):
+        W = dict(shapes.synth_dac_weights(seed=7, arch=dec))
+        W.update(shapes.synth_dac_encoder_weights(seed=8, arch=enc))
+        assert weights_checksum(W) == pytest.approx(g[name]["weights_checksum"], rel=1e-9)
+        for case in g[name]["cases"][:2]:
+            codes = odac.encode(W, case["wav"])
+            assert torch.equal(codes, case["codes"]) and len(torch.unique(codes)) > codes.shape[2]  # not degenerate
+
+
 def test_mamba2_oracle_pinned_against_transformers_mixer():
     """oracle/mamba2.py (restating mamba_ssm's Mamba2.step, which is absent here) against the pure-torch statement of the
     same mixer that transformers ships (Mamba2Mixer.torch_forward): chunked prefill of 11 tokens, then 5 cached decode
