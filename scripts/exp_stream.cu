@@ -123,10 +123,10 @@ int main() {
         }
   }
   const int grids[] = {128};
-  const int copies[] = {8192, 16384};
+  const int copies[] = {8192, 16384, 32768};
   const int inflight_kb[] = {128};
   const int streams = 1;
-  for (int mode = 0; mode < 3; mode += 2)  // issuers: 1, 2 lanes, 4 lanes, 2 warps (wait: 64 threads = 2 warps), evict-normal
+  for (int mode = 0; mode < 4; ++mode)  // issuers: 1, 2 lanes, 4 lanes, 2 warps (wait: 64 threads = 2 warps), evict-normal
     for (int g : grids)
       for (int cb : copies)
         for (int fk : inflight_kb) {

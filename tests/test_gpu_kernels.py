@@ -64,7 +64,8 @@ def test_gemm_big_persistent(ops, M, N, K):
 @pytest.mark.parametrize("M,N,K,grid", [(2, 64, 64, 1), (2, 192, 512, 5), (2, 3072, 2048, 148), (128, 3072, 2048, 148),
                                         (128, 2048, 2048, 148), (7, 1026, 512, 37), (100, 256, 8192, 148), (2, 2048, 8192, 148),
                                         (2, 16384, 2048, 148), (20, 2048, 8192, 111), (128, 16384, 2048, 74), (64, 9792, 2048, 148),
-                                        (2, 128, 4096, 128), (9, 64, 8192, 128)])
+                                        (2, 128, 4096, 128), (9, 64, 8192, 128), (64, 8704, 2048, 136), (48, 16384, 2048, 128),
+                                        (64, 2048, 4096, 96), (33, 4352, 2048, 148), (128, 2048, 8192, 144)])
 def test_gemm_skinny_stream_k(ops, M, N, K, grid):
     """Weight-streaming stream-K kernel of the decode step: all three A-row variants, fragments that start / end inside
     a tile, tiles shared by many CTAs (grid > tiles), CTAs spanning several tiles, N not a multiple of 64."""

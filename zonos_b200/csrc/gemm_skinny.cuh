@@ -7,6 +7,9 @@
 //   * Work unit = one 16 KB shared-memory stage of weights:
 //       MODE_K2: two consecutive k-blocks of one 64-row n_tile (one contiguous 16 KB bulk copy)      -- M <= 32
 //       MODE_T2: one k-block of two adjacent n_tiles (UMMA N = 128; the A k-block is reused twice)    -- M  > 32
+//       MODE_T2K2: two k-blocks of two adjacent n_tiles (32 KB) -- M > 32, long streams (fc1, fc2, the hybrid's in_proj):
+//                 a unit costs the MMA issuer and the activation producers ~0.2 us of barrier round trips besides its
+//                 MMAs (per-unit in-kernel trace), so at 8-16 KB per unit that overhead, not HBM, set the pace
 //       MODE_K1: one k-block of one n_tile (8 KB; fallback when K/64 is odd or the tile count is odd)
 //       MODE_N16: eight consecutive k-blocks of one 16-row n_tile (weights packed with tile_n = 16)    -- M <= 8:
 //                 N / 16 >= 128 independent column slices, every CTA runs the whole K of its slice, so no split-K
@@ -17,7 +20,7 @@
 //     the previous kernel, so under programmatic dependent launch it streams while the previous kernels still drain.
 //   * A producer warp(s): cp.async gather of the A k-block(s) (functor, as in gemm_tc.cuh) into a short ring.  The loop
 //     polls: it issues a stage whenever one is free and otherwise retires the oldest landed stage, so the round trip
-//     "MMA done -> stage free -> load -> landed" is off the critical path.  Only A_ROWS (8 / 32 / 128) rows are staged;
+//     "MMA done -> stage free -> load -> landed" is off the critical path.  Only A_ROWS (8 / 32 / 64 / 128) rows are staged;
 //     the tensor core still reads a 128-row operand, the rows past A_ROWS are whatever follows in shared memory and
 //     only ever reach TMEM lanes that nobody reads.
 //   * MMA warp (one lane): tcgen05.mma M=128, two TMEM accumulator sets (ping-pong per fragment).
@@ -38,7 +41,7 @@ namespace zb {
 constexpr int SK_NT = 64;                         // weight rows of one packed tile
 constexpr int SK_TILE_BYTES = SK_NT * 128;        // 8 KB packed (n_tile, k_block) image
 constexpr int SK_PARTIAL_F4 = (SK_NT / 4) * 128;  // float4 per partial sub-tile (32 KB)
-enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2, MODE_N16 = 3 };
+enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2, MODE_N16 = 3, MODE_T2K2 = 4 };
 #ifndef SK_WLANES
 #define SK_WLANES 4     // lanes of the weight-producer warp that issue bulk copies
 #endif
@@ -47,6 +50,19 @@ enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2, MODE_N16 = 3 };
 #endif
 #ifndef SK_SW128_KB
 #define SK_SW128_KB 128  // weight ring at 128 rows
+#endif
+#ifndef SK_SA128_T2K2
+#define SK_SA128_T2K2 3  // activation ring depth at 128 rows with 32 KB stages (two k-blocks per unit)
+#endif
+#ifndef SK_T2K2_MIN_UNITS
+#define SK_T2K2_MIN_UNITS 1184  // 16 KB units of a GEMM (tile pairs x k-blocks) from which 32 KB units are used: 8 per SM
+#endif
+#ifndef SK_A_SLOW_START
+#define SK_A_SLOW_START 1  // activation stages in flight before the first one has landed
+#define SK_A_SLOW_GROW 2   // additional stages allowed per landed stage
+#endif
+#ifndef SK_SA64
+#define SK_SA64 8       // activation ring depth at 33..64 rows (8 KB stages: the same 64 KB in flight as at 128 rows)
 #endif
 
 // Optional in-kernel timeline (build with ZB200_TRACE=1): globaltimer stamps per launch / CTA / event.
@@ -60,8 +76,18 @@ __device__ __forceinline__ void sk_stamp(unsigned long long* trace, int launch, 
   }
 }
 #define SK_STAMP(ev) sk_stamp(g.trace, g.trace_id, ev)
+// per-unit stamps of CTA 0 (launches 0..31): slot 32 + id, flat [unit < 320][6] = {w issued, w wait begins, w ready, a ready, MMAs issued, commits issued}
+__device__ __forceinline__ void sk_ustamp(unsigned long long* trace, int launch, int unit, int what) {
+  if (trace && launch >= 0 && launch < 32 && blockIdx.x == 0 && unit < 320) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[(size_t)(32 + launch) * SKT_CTAS * SKT_EVENTS + unit * 6 + what] = t;
+  }
+}
+#define SK_USTAMP(unit, what) sk_ustamp(g.trace, g.trace_id, unit, what)
 #else
 #define SK_STAMP(ev)
+#define SK_USTAMP(unit, what)
 #endif
 
 // Epilogues with `static constexpr bool kDeferred = true` take every fragment raw through
@@ -115,18 +141,22 @@ struct SkinnyCfg {
   static constexpr int NTILE = (MODE == MODE_N16) ? 16 : SK_NT;  // weight rows of one packed tile
   static constexpr int TILE_BYTES = NTILE * 128;
   static constexpr int PARTIAL_F4 = (NTILE / 4) * 128;
-  static constexpr int TG = (MODE == MODE_T2) ? 2 : 1;  // n_tiles per unit
-  static constexpr int KG = (MODE == MODE_K2) ? 2 : (MODE == MODE_N16) ? 8 : 1;  // k-blocks per unit
+  static constexpr int TG = (MODE == MODE_T2 || MODE == MODE_T2K2) ? 2 : 1;  // n_tiles per unit
+  static constexpr int KG = (MODE == MODE_K2 || MODE == MODE_T2K2) ? 2 : (MODE == MODE_N16) ? 8 : 1;  // k-blocks per unit
   static_assert(MODE != MODE_N16 || A_ROWS <= 8, "16-column slices are the M <= 8 path");
-  static constexpr int PROD_WARPS = (A_ROWS >= 128) ? 4 : 1;
+  static constexpr bool BIG = A_ROWS >= 64;  // one CTA per SM: four activation-producer warps, 128 KB weight ring
+  static constexpr int PROD_WARPS = BIG ? 4 : 1;
   static constexpr int PROD_THREADS = PROD_WARPS * 32;
   static constexpr int THREADS = (4 + PROD_WARPS + 2) * 32;
-  static constexpr int MIN_BLOCKS = (A_ROWS >= 128) ? 1 : 2;
+  static constexpr int MIN_BLOCKS = BIG ? 1 : 2;
   static constexpr int A_SUB_BYTES = A_ROWS * 128;
   static constexpr int A_STAGE_BYTES = KG * A_SUB_BYTES;
   static constexpr int W_STAGE_BYTES = TG * KG * TILE_BYTES;
-  static constexpr int SA = (A_ROWS >= 128) ? SK_SA128 : (A_ROWS <= 8 && MODE != MODE_N16) ? 8 : 4;
-  static constexpr int SW = (A_ROWS >= 128) ? (SK_SW128_KB * 1024 / W_STAGE_BYTES)
+  // The activation gather is a round trip to L2 per stage (~1.2 us under load), so its rate is ring bytes / latency: at
+  // 64 rows a stage holds 8 KB and the ring must be twice as deep as at 128 rows to feed the same weight rate.
+  static constexpr int SA = (MODE == MODE_T2K2) ? (A_ROWS >= 128 ? SK_SA128_T2K2 : SK_SA64 / 2)
+                            : (A_ROWS >= 128) ? SK_SA128 : BIG ? SK_SA64 : (A_ROWS <= 8 && MODE != MODE_N16) ? 8 : 4;
+  static constexpr int SW = BIG ? (SK_SW128_KB * 1024 / W_STAGE_BYTES)
                                             : ((A_ROWS > 8 || MODE == MODE_N16 ? 64 : 80) * 1024 / W_STAGE_BYTES);
   static constexpr int A_BYTES = SA * A_STAGE_BYTES;
   static constexpr int W_BYTES = SW * W_STAGE_BYTES;
@@ -143,6 +173,28 @@ struct SkinnyCfg {
 __host__ __device__ __forceinline__ int sk_first_unit(int c, int units, int grid) { return (int)((long long)c * units / grid); }
 __host__ __device__ __forceinline__ int sk_owner(int u, int units, int grid) {
   return (int)((((long long)u + 1) * grid + units - 1) / units) - 1;
+}
+
+// Order of the units inside a fragment.  Every CTA that walks the same k range reads the SAME activation lines from L2
+// at the same moment (with one whole-K fragment per CTA -- fc1 at batch 64, the hybrid's in_proj -- that is every CTA of
+// the grid on 64-128 lines: a handful of L2 slices serve all SMs while the rest idle, and the gather, not HBM, sets the
+// pace).  So CTA c starts its fragment `rot` units in and wraps around: unit i of the CTA (u = u0 + i in memory order)
+// is processed as k-unit  begin + (u - fragment start + rot) % length.  The weight producer, the activation producers
+// and the MMA issuer all walk this order; the accumulation order of a tile therefore depends on the CTA index (fixed for
+// a given shape and grid: results stay bitwise reproducible).
+#ifndef SK_ROTATE
+#define SK_ROTATE 0
+#endif
+__device__ __forceinline__ int sk_unit_ku(int u, int u0, int u1, int KBU, int cta, int& grp) {
+  grp = u / KBU;
+  const int g0 = grp * KBU;
+#if SK_ROTATE
+  const int fs = max(u0, g0), fe = min(u1, g0 + KBU), len = fe - fs;
+  return fs - g0 + (u - fs + cta % len) % len;
+#else
+  (void)u0, (void)u1, (void)cta;
+  return u - g0;
+#endif
 }
 
 __device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {  // non-blocking
@@ -220,20 +272,38 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
     if (lane < SK_WLANES) {
       const uint64_t pol = l2_policy_evict_first();
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(g.Wp);
-      for (int i = lane; i < n_units; i += SK_WLANES) {
-        const int s = i % SW;
-        const int u = u0 + i, grp = u / KBU, ku = u - grp * KBU;
-        mbar_wait(&empty_w[s], ((i / SW) & 1) ^ 1);
-        mbar_arrive_expect_tx(&full_w[s], C::W_STAGE_BYTES);
-        uint8_t* dst = w_ring + s * C::W_STAGE_BYTES;
-        if (MODE == MODE_T2) {
-          const uint8_t* src = wp + ((size_t)(2 * grp) * KB + ku) * C::TILE_BYTES;
-          bulk_g2s_hint(dst, src, C::TILE_BYTES, &full_w[s], pol);
-          bulk_g2s_hint(dst + C::TILE_BYTES, src + (size_t)KB * C::TILE_BYTES, C::TILE_BYTES, &full_w[s], pol);
-        } else {  // units are contiguous in memory
-          bulk_g2s_hint(dst, wp + (size_t)u * C::W_STAGE_BYTES, C::W_STAGE_BYTES, &full_w[s], pol);
+      if constexpr (TG == 2) {
+        // A unit is 2 * KG separate 8 KB blocks (stage layout [k-block of the unit][tile]: the two tiles of a k-block
+        // form one N = 128 operand).  Each of its copies comes from a different lane, so a unit's bytes are requested at
+        // once instead of one copy per ~0.3 us: lane l issues copy l % NCOPY of unit (iteration * UPI + l / NCOPY).
+        constexpr int NCOPY = 2 * KG, UPI = SK_WLANES / NCOPY;
+        static_assert(SK_WLANES % NCOPY == 0 && UPI >= 1, "lanes must be a multiple of the copies per unit");
+        const int sub = lane % NCOPY, kk = sub >> 1, j = sub & 1, uo = lane / NCOPY;
+        const unsigned peers = ((1u << NCOPY) - 1u) << (uo * NCOPY);
+        for (int i = uo; i < n_units; i += UPI) {
+          const int s = i % SW;
+          int grp;
+          const int ku = sk_unit_ku(u0 + i, u0, u1, KBU, cta, grp);
+          mbar_wait(&empty_w[s], ((i / SW) & 1) ^ 1);
+          if (sub == 0) mbar_arrive_expect_tx(&full_w[s], C::W_STAGE_BYTES);
+          __syncwarp(peers);  // the transaction count is armed before any of the unit's copies can complete
+          bulk_g2s_hint(w_ring + s * C::W_STAGE_BYTES + sub * C::TILE_BYTES,
+                        wp + ((size_t)(2 * grp + j) * KB + (size_t)ku * KG + kk) * C::TILE_BYTES, C::TILE_BYTES, &full_w[s], pol);
+          if (i == 0 && sub == 0) SK_STAMP(2);
+          if (sub == 0) SK_USTAMP(i, 0);
         }
-        if (i == 0) SK_STAMP(2);
+      } else {
+        for (int i = lane; i < n_units; i += SK_WLANES) {  // a unit is contiguous in memory: one copy
+          const int s = i % SW;
+          int grp;
+          const int ku = sk_unit_ku(u0 + i, u0, u1, KBU, cta, grp);
+          mbar_wait(&empty_w[s], ((i / SW) & 1) ^ 1);
+          mbar_arrive_expect_tx(&full_w[s], C::W_STAGE_BYTES);
+          bulk_g2s_hint(w_ring + s * C::W_STAGE_BYTES, wp + ((size_t)grp * KBU + ku) * C::W_STAGE_BYTES, C::W_STAGE_BYTES,
+                        &full_w[s], pol);
+          if (i == 0) SK_STAMP(2);
+          SK_USTAMP(i, 0);
+        }
       }
       if (lane == 0) {
         SK_STAMP(10);
@@ -254,28 +324,38 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
         const uint32_t tmem_d = tmem_base + (uint32_t)(b * TG * C::NTILE);
         for (int ku = ku_begin; ku < ku_end; ++ku, ++i) {
           const int sa = i % SA, sw = i % SW;
+          SK_USTAMP(i, 1);
           mbar_wait(&full_w[sw], (i / SW) & 1);
           if (i == 0) SK_STAMP(3);
+          SK_USTAMP(i, 2);
           mbar_wait(&full_a[sa], (i / SA) & 1);
           if (i == 0) SK_STAMP(5);
+          SK_USTAMP(i, 3);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(a_ring + sa * C::A_STAGE_BYTES);
           const uint32_t w_addr = smem_u32(w_ring + sw * C::W_STAGE_BYTES);
 #pragma unroll
           for (int kk = 0; kk < KG; ++kk) {
             const uint64_t adesc = umma_desc_sw128(a_addr + kk * C::A_SUB_BYTES);
-            const uint64_t bdesc = umma_desc_sw128(w_addr + kk * C::TILE_BYTES);
+            const uint64_t bdesc = umma_desc_sw128(w_addr + kk * TG * C::TILE_BYTES);
 #ifndef SK_DBG_NOMMA
 #pragma unroll
             for (int k = 0; k < GEMM_BK / 16; ++k)
               umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
-                       (ku != ku_begin) || (kk != 0) || (k != 0));
+                       (ku != ku_begin) || (kk != 0) || (k != 0));  // (ku counts the fragment's units in processing order)
 #else
             (void)adesc, (void)bdesc;
 #endif
           }
+          SK_USTAMP(i, 4);
+#ifdef SK_DBG_ARRIVE  // what-if (with SK_DBG_NOMMA): plain arrives instead of tcgen05.commit
+          mbar_arrive(&empty_a[sa]);
+          mbar_arrive(&empty_w[sw]);
+#else
           umma_commit(&empty_a[sa]);
           umma_commit(&empty_w[sw]);
+#endif
+          SK_USTAMP(i, 5);
         }
         umma_commit(&tmem_full[b]);
         u += ku_end - ku_begin;
@@ -293,9 +373,11 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
     constexpr int PER_THREAD = (CHUNKS + C::PROD_THREADS - 1) / C::PROD_THREADS;
     constexpr int MAXPEND = (SA < 8) ? SA : 8;
     int issued = 0, arrived = 0;
-    int ku = u0 % KBU;
     while (arrived < n_units) {
-      bool can_issue = issued < n_units && (issued - arrived) < MAXPEND;
+      // Slow start: every CTA of the grid asks L2 for the same activations at the same moment, so with the whole ring
+      // requested up front the FIRST stage lands only when the whole burst (64-96 KB per CTA, 10+ MB per grid: 2-3 us)
+      // has been served.  The first stage goes out alone, then the ring fills as stages land.
+      bool can_issue = issued < n_units && (issued - arrived) < min(MAXPEND, SK_A_SLOW_START + arrived * SK_A_SLOW_GROW);
       if (can_issue) {
         uint64_t* eb = &empty_a[issued % SA];
         const uint32_t par = ((issued / SA) & 1) ^ 1;
@@ -304,6 +386,8 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
       }
       if (can_issue) {
         uint8_t* a_tile = a_ring + (issued % SA) * C::A_STAGE_BYTES;
+        int grp_unused;
+        const int ku = sk_unit_ku(u0 + issued, u0, u1, KBU, cta, grp_unused);
 #pragma unroll
         for (int j = 0; j < PER_THREAD; ++j) {
           const int idx = j * C::PROD_THREADS + ptid;
@@ -321,7 +405,6 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
         }
         cp_async_commit();
         ++issued;
-        if (++ku == KBU) ku = 0;
       } else {
         switch (issued - arrived) {  // wait for the OLDEST pending group only
           case 1: cp_async_wait<0>(); break;
@@ -487,10 +570,14 @@ inline int skinny_mode(int m, int n_tiles, int k_blocks, bool prefer_k1 = false)
   // 16 KB stage take 616 cycles, i.e. ~50 GB/s per SM at best; two tiles per MMA (T2) halve that.
   static const bool small_t2 = zb::tuning_env("ZB200_SMALL_T2") != nullptr;  // measured slower at batch 1-16: opt-in
   if (m <= 32 && !(small_t2 && n_tiles % 2 == 0 && !prefer_k1)) return (k_blocks % 2 == 0) ? MODE_K2 : MODE_K1;
-  return (n_tiles % 2 == 0 && !prefer_k1) ? MODE_T2 : MODE_K1;
+  if (n_tiles % 2 != 0 || prefer_k1) return MODE_K1;
+  // Every unit costs the MMA issuer and the activation producers ~0.2 us of barrier round trips on top of its MMAs
+  // (in-kernel trace): long streams take two k-blocks of the tile pair per unit (32 KB of weights), short
+  // ones keep 16 KB units so that a CTA's share still splits into a few pipeline stages.
+  return (m > 32 && k_blocks % 2 == 0 && (int64_t)(n_tiles / 2) * k_blocks >= SK_T2K2_MIN_UNITS) ? MODE_T2K2 : MODE_T2;
 }
-inline int skinny_tg(int mode) { return mode == MODE_T2 ? 2 : 1; }
-inline int skinny_kg(int mode) { return mode == MODE_K2 ? 2 : 1; }
+inline int skinny_tg(int mode) { return (mode == MODE_T2 || mode == MODE_T2K2) ? 2 : 1; }
+inline int skinny_kg(int mode) { return (mode == MODE_K2 || mode == MODE_T2K2) ? 2 : 1; }
 
 // grid: number of CTAs wanted (clamped to the unit count).  Ticketed epilogues: ws must hold grid*2*tg 32 KB slots and
 // tickets n_tiles ints.  Deferred epilogues: grid must be n_groups * splits with splits | units-per-group.
@@ -506,8 +593,13 @@ cudaError_t launch_gemm_skinny(const SkinnyCore& g, const ALoader& al, const Epi
     return mode == MODE_K2   ? launch_gemm_skinny_cfg<32, MODE_K2>(g, al, epi, grid, st)
            : mode == MODE_T2 ? launch_gemm_skinny_cfg<32, MODE_T2>(g, al, epi, grid, st)
                              : launch_gemm_skinny_cfg<32, MODE_K1>(g, al, epi, grid, st);
-  return mode == MODE_T2 ? launch_gemm_skinny_cfg<128, MODE_T2>(g, al, epi, grid, st)
-                         : launch_gemm_skinny_cfg<128, MODE_K1>(g, al, epi, grid, st);
+  if (g.m_valid <= 64)
+    return mode == MODE_T2K2 ? launch_gemm_skinny_cfg<64, MODE_T2K2>(g, al, epi, grid, st)
+           : mode == MODE_T2 ? launch_gemm_skinny_cfg<64, MODE_T2>(g, al, epi, grid, st)
+                             : launch_gemm_skinny_cfg<64, MODE_K1>(g, al, epi, grid, st);
+  return mode == MODE_T2K2 ? launch_gemm_skinny_cfg<128, MODE_T2K2>(g, al, epi, grid, st)
+         : mode == MODE_T2 ? launch_gemm_skinny_cfg<128, MODE_T2>(g, al, epi, grid, st)
+                           : launch_gemm_skinny_cfg<128, MODE_K1>(g, al, epi, grid, st);
 }
 
 // ---- grid planning for ticketed epilogues (shared by the engine and the single-GEMM hooks) ----------------------------
