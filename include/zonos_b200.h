@@ -274,6 +274,13 @@ int zb200_mamba2_gated_rmsnorm(const void* y, const void* zxbcdt, int ld, const 
  * norm(residual) * w (+ b); rms != 0: RMSNorm, else LayerNorm.  b may be NULL. */
 int zb200_add_norm(const void* x, float* residual, int has_residual, const void* w, const void* b, void* out, int rows,
                    int d, float eps, int rms, void* stream);
+/* The same block wiring with the GEMM in front of it (decode rows, m <= 128): hidden = a * w^T in bf16 (the mixer's out_proj,
+ * MHA's out_proj or the GatedMLP's fc2: mamba_ssm Block, _mamba_ssm.py:46-57), then residual <- hidden + residual and
+ * out = norm(residual) of the NEXT block (or norm_f).  One deferred split-K weight-streaming GEMM whose fp32 partial sums
+ * (ws, >= m*n floats; more capacity allows more splits) are added up, in split order, by the add + norm kernel. */
+int zb200_gemm_add_norm(const void* a, int m, int lda, const void* w_packed, int n, int k, float* ws, int64_t ws_floats,
+                        float* residual, int has_residual, const void* norm_w, const void* norm_b, void* out, float eps, int rms,
+                        void* stream);
 
 /* Hybrid attention layers (mamba_ssm MHA; _mamba_ssm.py:18-31 with attn_layer_idx / attn_cfg): splits the Wqkv output
  * [rows][(H + 2*Hkv)*128] into q [rows][H*128], k and v [rows][Hkv*128] and applies the non-interleaved rotary embedding

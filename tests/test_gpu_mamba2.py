@@ -336,3 +336,34 @@ def test_hybrid_selected_through_the_backbone_registry():
     assert cache["kv"].pool.shape[0] == 2  # attention layers only, not all 5
     direct = ZonosHybridB200(m.state_dict(), net).generate(cond, None, max_new_tokens=N, batch_size=B, sampling_params=dict(sp))
     assert len(got) == B and all(torch.equal(a, b) for a, b in zip(got, direct)) and all(o.shape == (9, N) for o in got)
+
+
+@pytest.mark.parametrize("rows", [5, 64, 128])
+@pytest.mark.parametrize("rms", [True, False])
+def test_gemm_add_norm_matches_gemm_then_add_norm(rows, rms):
+    """zb200_gemm_add_norm (out_proj / fc2 of the hybrid's decode rows as a deferred split-K GEMM whose partial sums the
+    add + norm kernel reduces) against the ticketed GEMM followed by zb200_add_norm, over several steps on a running fp32
+    residual: the two differ only by the fp32 summation order in front of the bf16 rounding of the GEMM output."""
+    from zonos_b200 import ops
+
+    d, k = 2048, 4096
+    g = torch.Generator().manual_seed(rows + int(rms))
+    w = (torch.randn(d, k, generator=g) / k ** 0.5).to(BF).cuda()
+    wp = ops.pack_weight(w)
+    nw = (1 + 0.1 * torch.randn(d, generator=g)).to(BF).cuda()
+    nb = None if rms else (0.1 * torch.randn(d, generator=g)).to(BF).cuda()
+    res_a = torch.randn(rows, d, generator=g).cuda()
+    res_b = res_a.clone()
+    ws = torch.full((296 * 2 * 32768,), float("nan"), device="cuda")
+    tickets = torch.zeros(1024, dtype=torch.int32, device="cuda")
+    ws2 = torch.full((12 * 128 * 2048,), float("nan"), device="cuda")  # stale partials must never be read
+    for step in range(3):
+        a = torch.randn(rows, k, generator=g).to(BF).cuda()
+        hid = ops.gemm_skinny_bf16(a, wp, d, 0, ws, tickets)
+        out_a, _ = ops.add_norm(hid, res_a, nw, nb, 1e-5, rms)
+        out_b = ops.gemm_add_norm(a, wp, d, res_b, nw, nb, 1e-5, rms, ws2)
+        ref = a.float() @ w.float().t()
+        assert (hid.float() - ref).abs().max() < 2e-2 * max(1.0, float(ref.abs().max()))
+        # the residual stream is fp32: it sees the bf16 rounding of the GEMM output (1 ulp of |hid| <= 8 is 0.03)
+        assert (res_b - res_a).abs().max() <= 0.0625 and _rel_rms(res_b, res_a) < 2e-3
+        assert _rel_rms(out_b, out_a) < 4e-3

@@ -96,16 +96,6 @@ KvLayout kv_of(const zb200_engine_desc& d, int layer) {
 //     shared by at most 3 CTAs (the last one to arrive reduces, so the contributor count is the fix-up latency);
 //   deferred epilogues (out_proj, fc2): n_groups * splits CTAs, the split sums are reduced by resid_ln_kernel.
 // `sms` CTAs are resident at M > 32 (192 KB of shared memory each), 2 * sms at M <= 32.
-SkPlan plan_deferred(int sms, int rows, int n_tiles, int k_blocks, int64_t ws_floats, int n) {
-  const int cap = sms * (rows <= 32 ? 2 : big_m_ctas_per_sm());
-  const int mode = skinny_mode(rows, n_tiles, k_blocks);
-  const int groups = n_tiles / skinny_tg(mode), kbu = k_blocks / skinny_kg(mode);
-  static const int max_split = zb::tuning_env("ZB200_DEF_MAXSPLIT") ? atoi(zb::tuning_env("ZB200_DEF_MAXSPLIT")) : 64;
-  int s = 1;
-  for (int c = 1; c <= kbu && c <= max_split; ++c)
-    if (groups * c <= cap && kbu / c >= 2 && (int64_t)c * rows * n <= ws_floats) s = c;
-  return SkPlan{groups * s, s, false};
-}
 
 SkinnyCore sk_core(const zb200_engine_desc& d, const void* w, int n_tiles, int rows, int k) {
   SkinnyCore g{};

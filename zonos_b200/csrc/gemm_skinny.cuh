@@ -639,4 +639,17 @@ inline SkPlan plan_ticketed(int sms, int rows, int n_tiles, int k_blocks) {
   return p;
 }
 
+// Deferred epilogues (out_proj, fc2, the hybrid's out_proj): n_groups * splits CTAs, every CTA one fragment; the split
+// sums are reduced by the consumer kernel (resid_ln_kernel / add_norm_kernel).  ws_floats: fp32 capacity of the partials.
+inline SkPlan plan_deferred(int sms, int rows, int n_tiles, int k_blocks, int64_t ws_floats, int n) {
+  const int cap = sms * (rows <= 32 ? 2 : big_m_ctas_per_sm());
+  const int mode = skinny_mode(rows, n_tiles, k_blocks);
+  const int groups = n_tiles / skinny_tg(mode), kbu = k_blocks / skinny_kg(mode);
+  static const int max_split = zb::tuning_env("ZB200_DEF_MAXSPLIT") ? atoi(zb::tuning_env("ZB200_DEF_MAXSPLIT")) : 64;
+  int s = 1;
+  for (int c = 1; c <= kbu && c <= max_split; ++c)
+    if (groups * c <= cap && kbu / c >= 2 && (int64_t)c * rows * n <= ws_floats) s = c;
+  return SkPlan{groups * s, s, false};
+}
+
 }  // namespace zb

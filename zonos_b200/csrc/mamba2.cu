@@ -403,9 +403,12 @@ __global__ void __launch_bounds__(256) mamba2_gated_rmsnorm_kernel(const bf16* _
 // mamba_ssm Block with fused_add_norm (layer_norm_fn, prenorm=True, residual_in_fp32=True; _mamba_ssm.py:18-31,46-57):
 //   residual <- x + residual (fp32, written back; residual = x for the first layer),  out = norm(residual) * w (+ b)  in bf16
 // rms != 0: RMSNorm (no mean subtraction, bias optional), else LayerNorm.  One CTA per row, fp32 statistics.
+// With `ws` (deferred split-K GEMM, EpiPartial layout [splits][rows][d] fp32) the kernel is also the GEMM's reduction:
+//   x = bf16(sum_s ws[s][row][:])   (splits added in order: the nn.Linear output, rounded like the eager reference)
 __global__ void __launch_bounds__(256) add_norm_kernel(const bf16* __restrict__ x, float* __restrict__ residual, int has_residual,
                                                        const bf16* __restrict__ w, const bf16* __restrict__ b,
-                                                       bf16* __restrict__ out, int d, float eps, int rms) {
+                                                       bf16* __restrict__ out, int d, float eps, int rms,
+                                                       const float* __restrict__ ws, int splits, int rows) {
   pdl_launch_dependents();
   __shared__ float red[8];
   __shared__ float bcast;
@@ -427,7 +430,26 @@ __global__ void __launch_bounds__(256) add_norm_kernel(const bf16* __restrict__ 
   for (int i = 0; i < MAXV; ++i) {
     const int c = (i * 256 + tid) * 8;
     if (c < d) {
-      const uint4 xu = *reinterpret_cast<const uint4*>(x + (size_t)row * d + c);
+      uint4 xu;
+      if (ws != nullptr) {
+        float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        constexpr int BATCH = 12;  // independent loads in flight (the planner uses <= 12 splits here: one round trip)
+        for (int s0 = 0; s0 < splits; s0 += BATCH) {
+          float4 a0[BATCH], a1[BATCH];
+#pragma unroll
+          for (int sp = 0; sp < BATCH; ++sp)
+            if (s0 + sp < splits) ldg256_cg(reinterpret_cast<const float4*>(ws + ((size_t)(s0 + sp) * rows + row) * d + c), a0[sp], a1[sp]);
+#pragma unroll
+          for (int sp = 0; sp < BATCH; ++sp)
+            if (s0 + sp < splits) {
+              o[0] += a0[sp].x, o[1] += a0[sp].y, o[2] += a0[sp].z, o[3] += a0[sp].w;
+              o[4] += a1[sp].x, o[5] += a1[sp].y, o[6] += a1[sp].z, o[7] += a1[sp].w;
+            }
+        }
+        xu = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+      } else {
+        xu = *reinterpret_cast<const uint4*>(x + (size_t)row * d + c);
+      }
       const uint32_t xw[4] = {xu.x, xu.y, xu.z, xu.w};
       float4* rp = reinterpret_cast<float4*>(residual + (size_t)row * d + c);
       float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0;
@@ -529,6 +551,12 @@ __global__ void __launch_bounds__(256) gated_mlp_act_kernel(const bf16* __restri
   }
 }
 
+cudaError_t launch_add_norm(const bf16* x, float* residual, int has_residual, const bf16* w, const bf16* b, bf16* out, int rows,
+                            int d, float eps, int rms, const float* ws, int splits, cudaStream_t st) {
+  return launch_pdl(add_norm_kernel, dim3((unsigned)rows), dim3(256), 0, st, pdl_enabled(), x, residual, has_residual, w, b, out, d,
+                    eps, rms, ws, splits, rows);
+}
+
 }  // namespace zb
 
 using namespace zb;
@@ -615,8 +643,8 @@ extern "C" int zb200_add_norm(const void* x, float* residual, int has_residual, 
                               int d, float eps, int rms, void* stream) {
   ZB_REQUIRE(x && residual && w && out && rows > 0, "add_norm: bad arguments");
   ZB_REQUIRE(d > 0 && d % 8 == 0 && d <= 8192, "add_norm: d=%d must be a multiple of 8 (<= 8192)", d);
-  ZB_CHECK_CUDA(launch_pdl(add_norm_kernel, dim3((unsigned)rows), dim3(256), 0, (cudaStream_t)stream, pdl_enabled(), (const bf16*)x,
-                           residual, has_residual, (const bf16*)w, (const bf16*)b, (bf16*)out, d, eps, rms));
+  ZB_CHECK_CUDA(launch_add_norm((const bf16*)x, residual, has_residual, (const bf16*)w, (const bf16*)b, (bf16*)out, rows, d, eps, rms,
+                                nullptr, 0, (cudaStream_t)stream));
   return ZB200_OK;
 }
 

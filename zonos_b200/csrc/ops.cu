@@ -456,6 +456,32 @@ extern "C" int zb200_gemm_resid_ln(const void* a, int m, int lda, const void* w_
   return ZB200_OK;
 }
 
+/* Hybrid blocks (mamba_ssm Block with fused_add_norm): hidden = a * w^T (bf16), residual <- hidden + residual (fp32),
+ * out = norm(residual): the mixer's out_proj (or the MLP's fc2) together with the NEXT block's add + norm, as a deferred
+ * split-K weight-streaming GEMM whose partial sums are reduced by the add + norm kernel.  ws: fp32 partials, the split count
+ * is planned from its capacity (>= m*n floats). */
+extern "C" int zb200_gemm_add_norm(const void* a, int m, int lda, const void* w_packed, int n, int k, float* ws, int64_t ws_floats,
+                                   float* residual, int has_residual, const void* norm_w, const void* norm_b, void* out, float eps,
+                                   int rms, void* stream) {
+  ZB_REQUIRE(a && w_packed && ws && residual && norm_w && out, "gemm_add_norm: null argument");
+  ZB_REQUIRE(m > 0 && m <= GEMM_BM && n > 0 && n % 128 == 0 && n <= 8192 && k > 0 && k % 64 == 0 && lda % 8 == 0,
+             "gemm_add_norm: bad shape m=%d n=%d k=%d lda=%d (m <= 128, n %% 128 == 0)", m, n, k, lda);
+  ZB_REQUIRE(ws_floats >= (int64_t)m * n, "gemm_add_norm: workspace too small (needs >= m*n floats)");
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int n_tiles = n / SK_NT;
+  const SkPlan p = plan_deferred(sms, m, n_tiles, k / 64, ws_floats, n);
+  SkinnyCore g{};
+  g.Wp = w_packed, g.n_tiles = n_tiles, g.k_blocks = k / 64, g.m_valid = m, g.partial_ws = nullptr, g.tickets = nullptr;
+  g.n_splits = p.splits, g.trace = g_trace_buf, g.trace_id = g_trace_buf ? g_trace_next++ : -1;
+  ARowMajor al{(const uint8_t*)a, (size_t)lda * 2};
+  EpiPartial epi{ws, m, n};
+  ZB_CHECK_CUDA(launch_gemm_skinny(g, al, epi, p.grid, (cudaStream_t)stream));
+  ZB_CHECK_CUDA(launch_add_norm(nullptr, residual, has_residual, (const bf16*)norm_w, (const bf16*)norm_b, (bf16*)out, m, n, eps, rms,
+                                ws, p.splits, (cudaStream_t)stream));
+  return ZB200_OK;
+}
+
 extern "C" int zb200_gemm_swap_bf16(const void* a, int m, int lda, const void* w_packed, int n, int k, void* out, int ldo,
                                     int grid, float* ws, int64_t ws_floats, int* tickets, int n_tickets, void* stream) {
   ZB_REQUIRE(m > 0 && m <= 8 && n > 0 && k > 0 && k % 128 == 0 && lda % 8 == 0,

@@ -13,4 +13,7 @@ cudaError_t launch_qkv_finish(const float* ws, int splits, int rows, int n_cols,
 cudaError_t launch_embed_sum(const int32_t* ids, int ids_stride_b, int ids_stride_q, const int* col_ptr, int col_add,
                              int n_cols, const bf16* emb, bf16* out, int batch, int n_q, int vocab, int d,
                              int out_stride_b, int out_off, int dup_off, cudaStream_t st);
+// mamba2.cu: fused residual add + (RMS|Layer)Norm of the hybrid blocks; with `ws` it also reduces a deferred split-K GEMM
+cudaError_t launch_add_norm(const bf16* x, float* residual, int has_residual, const bf16* w, const bf16* b, bf16* out, int rows,
+                            int d, float eps, int rms, const float* ws, int splits, cudaStream_t st);
 }  // namespace zb

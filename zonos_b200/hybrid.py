@@ -8,7 +8,8 @@ Per layer (mamba_ssm Block with fused_add_norm, residual_in_fp32):  (hidden, res
 `Mamba2StackB200` is the Mamba2-only stack (its `step()` is capturable with `torch.cuda.graph`: it allocates through torch
 and never synchronises); `HybridBackboneB200` adds the attention layers (`attn_layer_idx`: mamba_ssm MHA with
 non-interleaved rotary, paged-KV attention of the transformer path) and their GatedMLP, sequenced eagerly with
-host-side positions.  Not here yet: a C-side engine with its own CUDA graph for the hybrid, `generate` on it.
+host-side positions.  On decode rows the out_proj (and fc2) run as one deferred split-K GEMM + the next block's add + norm
+(zb200_gemm_add_norm).
 There is no CPU fallback: every operation is a kernel of libzonos_b200.so.
 """
 import torch
@@ -66,23 +67,46 @@ class Mamba2StackB200:
             return ops.gemm_skinny_bf16(a, w, n, 0, self._ws, self._tickets)  # grid planned like the engine's GEMMs
         return ops.gemm_bf16(a, w, n)
 
+    def _ensure_ws2(self):
+        if getattr(self, "_ws2", None) is None:  # fp32 partials of the deferred split-K GEMMs
+            self._ws2 = torch.empty(12 * 128 * 2048, dtype=torch.float32, device=self.device)
+
+    def _mixer_step(self, hn, L, st):
+        """Mamba2.step on the normed rows: in_proj -> conv update -> SSD state update -> gated RMSNorm (the out_proj follows in
+        _proj_norm)."""
+        s = self.s
+        Di, G, N = s["d_inner"], s["n_groups"], s["d_state"]
+        zx = self._gemm(hn, L["w_in"], self.n_in)
+        xbc = ops.mamba2_conv_update(st["conv"], zx, Di, L["cw"], L["cb"])
+        y = ops.mamba2_ssd_step(st["ssm"], xbc, zx, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G)
+        return ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
+
+    def _proj_norm(self, a, w, n, residual, norm):
+        """Block boundary: hidden = a @ W^T, residual += hidden (fp32, in place), returns norm(residual) for the next block.
+        Decode rows: one deferred split-K GEMM whose partial sums the add + norm kernel reduces (zb200_gemm_add_norm)."""
+        nw, nb = norm
+        if a.shape[0] <= 128:
+            self._ensure_ws2()
+            if self._ws2.numel() >= a.shape[0] * n:
+                return ops.gemm_add_norm(a, w, n, residual, nw, nb, self.eps, self.rms, self._ws2)
+        hn, _ = ops.add_norm(self._gemm(a, w, n), residual, nw, nb, self.eps, self.rms)
+        return hn
+
     def _forward(self, x, states, seq_len):
         s = self.s
         Di, G, N = s["d_inner"], s["n_groups"], s["d_state"]
-        residual, hidden = None, x
-        for L, st in zip(self.layers, states):
-            hn, residual = ops.add_norm(hidden, residual, L["nw"], L["nb"], self.eps, self.rms)
-            zx = self._gemm(hn, L["w_in"], self.n_in)
+        norms = [(L["nw"], L["nb"]) for L in self.layers[1:]] + [(self.fw, self.fb)]  # the norm BEHIND every layer
+        hn, residual = ops.add_norm(x, None, self.layers[0]["nw"], self.layers[0]["nb"], self.eps, self.rms)
+        for L, st, nxt in zip(self.layers, states, norms):
             if seq_len is None:
-                xbc = ops.mamba2_conv_update(st["conv"], zx, Di, L["cw"], L["cb"])
-                y = ops.mamba2_ssd_step(st["ssm"], xbc, zx, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G)
+                yn = self._mixer_step(hn, L, st)
             else:
+                zx = self._gemm(hn, L["w_in"], self.n_in)
                 xbc = ops.mamba2_conv_seq(st["conv"], zx, seq_len, Di, L["cw"], L["cb"])
                 y = ops.mamba2_ssd_scan(st["ssm"], xbc, zx, seq_len, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G)
-            yn = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
-            hidden = self._gemm(yn, L["w_out"], s["d_model"])
-        out, _ = ops.add_norm(hidden, residual, self.fw, self.fb, self.eps, self.rms)
-        return out
+                yn = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
+            hn = self._proj_norm(yn, L["w_out"], s["d_model"], residual, nxt)
+        return hn
 
     def prefill(self, x, states, seq_len):
         """x bf16 [n_seq*seq_len, d_model] (sequence-major) -> norm_f output for every row; states receive the final
@@ -127,6 +151,9 @@ class HybridBackboneB200:
 
     _gemm = Mamba2StackB200._gemm
     _ensure_ws = Mamba2StackB200._ensure_ws
+    _proj_norm = Mamba2StackB200._proj_norm
+    _ensure_ws2 = Mamba2StackB200._ensure_ws2
+    _mixer_step = Mamba2StackB200._mixer_step
 
     def allocate_inference_cache(self, n_seq, max_seqlen):
         s = self.s
@@ -156,19 +183,19 @@ class HybridBackboneB200:
         assert pos_ptr is None or seq_len == 1
         if pos0 + seq_len > cache["max_seqlen"]:
             raise AssertionError(f"sequence length {pos0 + seq_len} exceeds the KV cache ({cache['max_seqlen']})")
-        residual, hidden = None, x
+        norms = [(L["nw"], L["nb"]) for L in self.layers[1:]] + [(self.fw, self.fb)]  # the norm BEHIND every layer
+        d = s["d_model"]
+        hn, residual = ops.add_norm(x, None, self.layers[0]["nw"], self.layers[0]["nb"], self.eps, self.rms)
         for li, (L, st) in enumerate(zip(self.layers, cache["layers"])):
-            hn, residual = ops.add_norm(hidden, residual, L["nw"], L["nb"], self.eps, self.rms)
             if L["kind"] == "mamba2":
-                zx = self._gemm(hn, L["w_in"], self.n_in)
                 if decode:
-                    xbc = ops.mamba2_conv_update(st["conv"], zx, Di, L["cw"], L["cb"])
-                    y = ops.mamba2_ssd_step(st["ssm"], xbc, zx, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G)
+                    mixed = self._mixer_step(hn, L, st)
                 else:
+                    zx = self._gemm(hn, L["w_in"], self.n_in)
                     xbc = ops.mamba2_conv_seq(st["conv"], zx, seq_len, Di, L["cw"], L["cb"], use_initial_state=pos0 > 0)
                     y = ops.mamba2_ssd_scan(st["ssm"], xbc, zx, seq_len, 2 * Di + 2 * G * N, L["A"], L["D"], L["dtb"], G,
                                             use_initial_state=pos0 > 0)
-                mixed = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
+                    mixed = ops.mamba2_gated_rmsnorm(y, zx, L["gw"], self.eps, G)
             else:
                 slot = self.kv_slot[li]
                 qkv = self._gemm(hn, L["w_in"], (self.H + 2 * self.Hkv) * 128)
@@ -176,23 +203,19 @@ class HybridBackboneB200:
                 if pos_ptr is not None:
                     ops.kv_write_at(cache["kv"], slot, k, v, pos_ptr)
                     mixed = ops.attn_decode_at(q, cache["kv"], slot, pos_ptr, self.H)
-                    hidden = self._gemm(mixed, L["w_out"], s["d_model"])
-                    if "w_fc1" in L:
-                        hn2, residual = ops.add_norm(hidden, residual, L["n2w"], L["n2b"], self.eps, self.rms)
-                        h1 = ops.gated_mlp_act(self._gemm(hn2, L["w_fc1"], 2 * L["d_ff"]))
-                        hidden = self._gemm(h1, L["w_fc2"], s["d_model"])
-                    continue
-                ops.kv_write(cache["kv"], slot, k.view(n_seq, seq_len, self.Hkv, 128), v.view(n_seq, seq_len, self.Hkv, 128), pos0)
-                if decode:
-                    mixed = ops.attn_decode(q, cache["kv"], slot, pos0 + 1, self.H)
                 else:
-                    mixed = ops.attn_prefill(q.view(n_seq, seq_len, self.H * 128), cache["kv"], slot, pos0, self.H).view(-1, self.H * 128)
-            hidden = self._gemm(mixed, L["w_out"], s["d_model"])
+                    ops.kv_write(cache["kv"], slot, k.view(n_seq, seq_len, self.Hkv, 128), v.view(n_seq, seq_len, self.Hkv, 128), pos0)
+                    if decode:
+                        mixed = ops.attn_decode(q, cache["kv"], slot, pos0 + 1, self.H)
+                    else:
+                        mixed = ops.attn_prefill(q.view(n_seq, seq_len, self.H * 128), cache["kv"], slot, pos0, self.H).view(-1, self.H * 128)
             if "w_fc1" in L:
-                hn2, residual = ops.add_norm(hidden, residual, L["n2w"], L["n2b"], self.eps, self.rms)
+                hn2 = self._proj_norm(mixed, L["w_out"], d, residual, (L["n2w"], L["n2b"]))
                 h1 = ops.gated_mlp_act(self._gemm(hn2, L["w_fc1"], 2 * L["d_ff"]))
-                hidden = self._gemm(h1, L["w_fc2"], s["d_model"])
-        out, _ = ops.add_norm(hidden, residual, self.fw, self.fb, self.eps, self.rms)
+                hn = self._proj_norm(h1, L["w_fc2"], d, residual, norms[li])
+            else:
+                hn = self._proj_norm(mixed, L["w_out"], d, residual, norms[li])
+        out = hn
         if pos_ptr is None:  # (with a device-side position the caller advances the host copy: graph replays do not pass here)
             cache["seqlen_offset"] = pos0 + seq_len
         return out

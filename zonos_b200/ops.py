@@ -292,6 +292,21 @@ def add_norm(x: torch.Tensor, residual, w: torch.Tensor, b, eps: float, rms: boo
     return out, residual
 
 
+def gemm_add_norm(a: torch.Tensor, w_packed: torch.Tensor, n: int, residual: torch.Tensor, w: torch.Tensor, b, eps: float,
+                  rms: bool, ws: torch.Tensor):
+    """Decode rows of the hybrid blocks: (a @ W^T in bf16) -> residual += . (fp32, in place) -> norm of the next block, as a
+    deferred split-K weight-streaming GEMM + the add-norm kernel reducing its partial sums.  Returns the normed bf16 rows."""
+    a = _cuda(a, torch.bfloat16)
+    m, k = a.shape
+    assert residual.dtype == torch.float32 and residual.is_contiguous() and residual.shape == (m, n)
+    assert ws.dtype == torch.float32 and ws.numel() >= m * n
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=a.device)
+    check(lib().zb200_gemm_add_norm(ptr(a), m, k, ptr(w_packed), n, k, ptr(ws), ctypes.c_int64(ws.numel()), ptr(residual), 1,
+                                    ptr(_cuda(w, torch.bfloat16)), ptr(None if b is None else _cuda(b, torch.bfloat16)), ptr(out),
+                                    ctypes.c_float(eps), int(rms), stream_ptr()), "gemm_add_norm")
+    return out
+
+
 def rope_split(qkv: torch.Tensor, inv_freq: torch.Tensor, seq_len: int, pos0: int, n_heads: int, n_kv_heads: int, pos_ptr=None):
     """Hybrid attention layers: Wqkv output bf16 [rows, (H+2Hkv)*128] -> rotated q [rows, H*128], rotated k and v
     [rows, Hkv*128] (non-interleaved rotary at position pos0 + row % seq_len)."""
