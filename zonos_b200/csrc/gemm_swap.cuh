@@ -95,28 +95,27 @@ __global__ void __launch_bounds__(SWP_THREADS, 2) gemm_swap_kernel(SwapCore g, A
 
   if (warp == 5) {
     // ------------------------------------------------------------------ weight producer (independent of prior kernels)
-    // SWP_WLANES lanes issue in parallel (one thread gets ~2.7 bulk copies / us through the TMA unit: gemm_skinny.cuh).
-    // A lane must never run two ring revolutions ahead of the consumer (the parity wait cannot tell 0 from 2
-    // completions): lanes <= ring slots guarantees it, here every lane simply owns one slot.
-    constexpr int SWP_WLANES = SWP_SW;
+    // One thread gets ~2.7 bulk copies / us through the TMA unit (gemm_skinny.cuh), and a unit is four separate 8 KB blocks:
+    // every ring slot has FOUR lanes, one per copy, so a unit's bytes are requested at once (the first unit of a launch lands
+    // ~1 us earlier than with one lane issuing its four copies in turn).  Lane l serves slot l / 4 (units slot, slot + SW,
+    // ...) and issues copy l % 4 = 2 * kk + tile.  A slot's lanes never run two ring revolutions ahead of the consumer (the
+    // parity wait cannot tell 0 from 2 completions): every group simply owns one slot.
+    constexpr int SWP_WLANES = 4 * SWP_SW;
+    static_assert(SWP_WLANES <= 32, "four lanes per ring slot");
     if (lane < SWP_WLANES) {
       const uint64_t pol = l2_policy_evict_first();
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(g.Wp);
-      for (int i = lane; i < n_units; i += SWP_WLANES) {
-        const int s = i % SWP_SW;
+      const int slot = lane >> 2, sub = lane & 3, kk = sub >> 1, tile = sub & 1;
+      const unsigned peers = 0xFu << (slot * 4);
+      for (int i = slot; i < n_units; i += SWP_SW) {
         const int u = u0 + i, grp = u / KBU, ku = u - grp * KBU;
-        mbar_wait(&empty_w[s], ((i / SWP_SW) & 1) ^ 1);
+        mbar_wait(&empty_w[slot], ((i / SWP_SW) & 1) ^ 1);
         const bool two = (2 * grp + 1) < g.n_tiles;  // the last group of an odd tile count has one tile
-        mbar_arrive_expect_tx(&full_w[s], two ? SWP_W_STAGE : SWP_W_STAGE / 2);
-        uint8_t* dst = w_ring + s * SWP_W_STAGE;
-        const uint8_t* src = wp + ((size_t)(2 * grp) * KB + 2 * ku) * SK_TILE_BYTES;
-#pragma unroll
-        for (int kk = 0; kk < 2; ++kk) {
-          bulk_g2s_hint(dst + kk * 2 * SK_TILE_BYTES, src + kk * SK_TILE_BYTES, SK_TILE_BYTES, &full_w[s], pol);
-          if (two)
-            bulk_g2s_hint(dst + kk * 2 * SK_TILE_BYTES + SK_TILE_BYTES, src + ((size_t)KB + kk) * SK_TILE_BYTES, SK_TILE_BYTES,
-                          &full_w[s], pol);
-        }
+        if (sub == 0) mbar_arrive_expect_tx(&full_w[slot], two ? SWP_W_STAGE : SWP_W_STAGE / 2);
+        __syncwarp(peers);  // the transaction count is armed before any of the unit's copies can complete
+        if (tile == 0 || two)
+          bulk_g2s_hint(w_ring + slot * SWP_W_STAGE + sub * SK_TILE_BYTES,
+                        wp + ((size_t)(2 * grp + tile) * KB + 2 * ku + kk) * SK_TILE_BYTES, SK_TILE_BYTES, &full_w[slot], pol);
       }
       if (lane == 0) prefetch_next_weights(g.next, cta);
     }
