@@ -305,6 +305,68 @@ def gen_conditioning():
                os.path.join(OUT, "conditioning.pt"))
 
 
+SPEAKER_CASES = {  # name: (in_planes, blocks per stage, seed, seconds, sample rate of the input, channels)
+    "tiny_16k": (8, (1, 2, 2, 1), 11, 0.64, 16000, 1),
+    "tiny_44k_stereo": (8, (1, 2, 2, 1), 12, 0.5, 44100, 2),
+    "resnet293_16k": (64, (10, 20, 64, 3), 13, 1.0, 16000, 1),
+}
+
+
+def speaker_wav(seed, seconds, sr, channels):
+    """Seeded test signal: a few decaying partials + noise, [channels, n] in [-1, 1]."""
+    g = torch.Generator().manual_seed(seed)
+    n = int(seconds * sr)
+    t = torch.arange(n, dtype=torch.float64) / sr
+    wav = torch.zeros(channels, n, dtype=torch.float64)
+    for c in range(channels):
+        for f0 in (110.0 * (c + 1), 440.0, 1730.0, 5200.0):
+            wav[c] += float(torch.rand(1, generator=g)) * torch.sin(2 * torch.pi * f0 * t + float(torch.rand(1, generator=g)))
+        wav[c] += 0.1 * torch.randn(n, generator=g, dtype=torch.float64)
+    return (0.25 * wav).float()
+
+
+def gen_speaker():
+    """Speaker encoder (zonos/speaker_cloning.py): the reference's own modules on the seeded weights of
+    oracle.speaker.synth_speaker_weights.  The tiny cases compose the reference's ResNet / ASP classes with fewer, narrower
+    blocks through the reference's own ResNet293_based.forward; the third case is ResNet293_based as shipped."""
+    from zonos import speaker_cloning as ref
+
+    from . import speaker as osp
+
+    out = {}
+    for name, (ip, blocks, seed, seconds, sr, ch) in SPEAKER_CASES.items():
+        sd, lda = osp.synth_speaker_weights(ip, blocks, seed)
+        if blocks == osp.RESNET293_BLOCKS and ip == 64:
+            m = ref.ResNet293_based()
+        else:
+            m = ref.ResNet293_based.__new__(ref.ResNet293_based)
+            torch.nn.Module.__init__(m)
+            m.front = ref.ResNet(ip, ref.SimAMBasicBlock, list(blocks))
+            m.pooling = ref.ASP(ip * ref.SimAMBasicBlock.expansion, 80)
+            m.bottleneck = torch.nn.Linear(m.pooling.out_dim, 256)
+            m.drop = None
+        m.featCal = None
+        m.load_state_dict(sd, strict=True)
+        m.featCal = ref.logFbankCal()
+        m.eval()
+        lin = torch.nn.Linear(256, 128)
+        lin.load_state_dict(lda)
+        wav = speaker_wav(seed, seconds, sr, ch)
+        # SpeakerEmbedding.prepare_input + forward, SpeakerEmbeddingLDA.forward (speaker_cloning.py:375-384, 409-411)
+        x = wav.mean(0, keepdim=True)
+        if sr != 16000:
+            import torchaudio
+
+            x = torchaudio.transforms.Resample(sr, 16000)(x)
+        feat = m.featCal(x)
+        emb = m(x).to(torch.float32)
+        out[name] = dict(in_planes=ip, blocks=tuple(blocks), seed=seed, seconds=seconds, sample_rate=sr, channels=ch,
+                         wav16k=x.clone(), feat=feat.clone(), emb=emb.clone(), lda=lin(emb).clone(),
+                         weights_checksum=float(sum(float(v.double().abs().sum()) for v in sd.values())))
+        print(name, "feat", tuple(feat.shape), "emb |max|", float(emb.abs().max()))
+    torch.save(out, os.path.join(OUT, "speaker.pt"))
+
+
 def gen_model_real():
     """Real-shape model file: the reference's bf16 logits, plus the same prefill in fp32 (oracle port, which the CPU test
     pins bit-exactly to the reference at this shape): |bf16 reference - fp32| is the reference's own rounding noise, the
@@ -333,6 +395,10 @@ def main():
         gen_dac_encode()
         print("dac_encode.pt", os.path.getsize(os.path.join(OUT, "dac_encode.pt")))
         return
+    if "--speaker" in sys.argv:
+        gen_speaker()
+        print("speaker.pt", os.path.getsize(os.path.join(OUT, "speaker.pt")))
+        return
     if "--conditioning" in sys.argv:
         gen_conditioning()
         print("conditioning.pt", os.path.getsize(os.path.join(OUT, "conditioning.pt")))
@@ -350,6 +416,7 @@ def main():
     gen_postproc()
     gen_conditioning()
     gen_dac_encode()
+    gen_speaker()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -149,6 +149,35 @@ def test_dac_encode(golden):
             assert torch.equal(codes, case["codes"]) and len(torch.unique(codes)) > codes.shape[2]  # not degenerate
 
 
+def test_speaker_encoder(golden):
+    """oracle.speaker (resample, log mel filterbank, ResNet293 of SimAM blocks, ASP, bottleneck, LDA; fp32) against the
+    reference's own modules (tests/golden/speaker.pt): two narrow stacks -- one from 44.1 kHz stereo, through the restated
+    torchaudio resampler -- and the shipped ResNet293 architecture."""
+    from oracle import speaker as osp
+    from oracle.gen_golden import SPEAKER_CASES, speaker_wav
+
+    g = golden("speaker.pt")
+    for name, (ip, blocks, seed, seconds, sr, ch) in SPEAKER_CASES.items():
+        c = g[name]
+        sd, lda = osp.synth_speaker_weights(ip, blocks, seed)
+        assert float(sum(float(v.double().abs().sum()) for v in sd.values())) == pytest.approx(c["weights_checksum"], rel=1e-9)
+        wav = speaker_wav(seed, seconds, sr, ch)
+        x = osp.resample(wav.mean(0, keepdim=True), sr, 16000)
+        assert x.shape == c["wav16k"].shape and float((x - c["wav16k"]).abs().max()) < 2e-6
+        # the log of small mel energies amplifies the 1e-6 of the resampler's summation order: features are compared on the
+        # golden file's own 16 kHz signal, the whole path (from the raw signal) with the tolerance that noise needs
+        feat = osp.log_fbank(c["wav16k"])
+        assert float((feat - c["feat"]).abs().max()) < 2e-5
+        emb = osp.embedding_from_features(feat, sd, blocks)
+        scale = float(c["emb"].abs().max())
+        assert float((emb - c["emb"]).abs().max()) < 2e-4 * scale, name
+        emb, out = osp.speaker_embedding(wav, sr, sd, lda, blocks)
+        tol = 2e-4 if sr == 16000 else 5e-3
+        assert float((emb - c["emb"]).abs().max()) < tol * scale, name
+        assert float((out - c["lda"]).abs().max()) < tol * float(c["lda"].abs().max()), name
+        assert float(c["emb"].std()) > 0.05  # the fixture is not degenerate
+
+
 def test_mamba2_oracle_pinned_against_transformers_mixer():
     """oracle/mamba2.py (restating mamba_ssm's Mamba2.step, which is absent here) against the pure-torch statement of the
     same mixer that transformers ships (Mamba2Mixer.torch_forward): chunked prefill of 11 tokens, then 5 cached decode
