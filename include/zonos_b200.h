@@ -161,6 +161,36 @@ int zb200_rvq_encode(const float* latent, const float* in_w, const float* in_b, 
                      const float* out_w, const float* out_b, int64_t* codes, int batch, int n_q, int hidden, int dim, int n_codes,
                      int t, void* stream);
 
+/* ---- zonos/speaker_cloning.py:387-411 SpeakerEmbeddingLDA.forward: the speaker encoder, fp32 like the
+ * reference, channels-first tensors like torch.  Once per new speaker; csrc/speaker.cu.
+ * zb200_resample_f32: torchaudio.transforms.Resample as SpeakerEmbedding.prepare_input uses it (:371-380): out[b][j*new + q] =
+ *   sum_k kernel[q][k] * x[b][j*orig + k - width], kernel fp32 [new][2*width + orig] from torchaudio's sinc_interp_hann
+ *   formula (orig, new already divided by their gcd); n_out <= ceil(n_in * new / orig).
+ * zb200_logfbank_f32: logFbankCal.forward (:12-34) = MelSpectrogram(16 kHz, n_fft 512, win 400, hop 160, 80 HTK mels, power 2,
+ *   centre + reflect padding) -> log(. + 1e-6) -> minus the mean over time.  window fp32 [400] (periodic Hann), mel_fb fp32
+ *   [257][80]; out fp32 [batch][80][n_frames], n_frames = 1 + n / 160.
+ * zb200_conv2d_f32: nn.Conv2d 3x3 (padding 1) or 1x1, stride 1 or 2, no bias, followed by an eval-mode BatchNorm2d folded into
+ *   scale / shift per output channel (NULL: none) and an optional ReLU (SimAMBasicBlock's conv1+bn1+relu, conv2+bn2 and the
+ *   downsample branch, :68-88; ResNet.conv1, :169-171).  w_ckn = the weight permuted to [C_in][k*k][C_out].
+ * zb200_simam_residual_f32: SimAM (:90-95) on every (sample, channel) plane of hw values, + shortcut, ReLU (:85-87).
+ * zb200_relu_affine_f32: ReLU then a per-channel affine (ASP's ReLU + BatchNorm1d, :46-47) on [batch][channels][t].
+ * zb200_asp_pool_f32: softmax over time of the attention logits, weighted mean and standard deviation (:54-57):
+ *   x, logits fp32 [batch][channels][t] -> out fp32 [batch][2*channels] = (mu | sg).
+ * zb200_linear_f32: nn.Linear on one vector per sample (the bottleneck :213,222 and the LDA :404-411): out[b] = bias + x[b] W^T,
+ *   w_t = the weight transposed to [c_in][c_out].
+ * ASP's 1x1 Conv1d layers run on zb200_conv1d_f32. */
+int zb200_resample_f32(const float* x, const float* kernel, float* out, int batch, int n_in, int n_out, int orig_freq, int new_freq,
+                       int width, void* stream);
+int zb200_logfbank_f32(const float* wav16k, const float* window, const float* mel_fb, float* out, int batch, int n, int n_frames,
+                       void* stream);
+int zb200_conv2d_f32(const float* x, const float* w_ckn, const float* scale, const float* shift, float* out, int batch, int c_in,
+                     int h, int w, int c_out, int k, int stride, int relu, void* stream);
+int zb200_simam_residual_f32(const float* x, const float* shortcut, float* out, int planes, int hw, float lambda_p, void* stream);
+int zb200_relu_affine_f32(const float* x, const float* scale, const float* shift, float* out, int batch, int channels, int t,
+                          void* stream);
+int zb200_asp_pool_f32(const float* x, const float* logits, float* out, int batch, int channels, int t, void* stream);
+int zb200_linear_f32(const float* x, const float* w_t, const float* bias, float* out, int batch, int c_in, int c_out, void* stream);
+
 /* ---- zonos/conditioning.py:373-389 PrefixConditioner.forward ---------------------------------------
  * One launch: every conditioner's output row at its position of the prefix (rounded to bf16 like the eager reference),
  * then nn.LayerNorm over d.  The prefix is tiled by `segments` in conditioner order; a segment is one of
