@@ -430,6 +430,38 @@ def dac_section(device, batch, frames, world=1):
                                       "waveforms copied to pinned host memory"}}
 
 
+def speaker_section(device, seconds=10.0):
+    """Speaker encoder, ResNet293 architecture with seeded weights: one clip, host signal -> embedding
+    on the host through SpeakerEmbeddingLDA.forward, CUDA events; the CPU oracle on this box's cores beside it."""
+    from oracle import speaker as osp
+    from oracle.gen_golden import speaker_wav
+    from zonos_b200.speaker_cloning import SpeakerEmbeddingLDA
+
+    sd, lda = osp.synth_speaker_weights(64, osp.RESNET293_BLOCKS, 13)
+    enc = SpeakerEmbeddingLDA(str(device), state_dict=sd, lda_state_dict=lda)
+    wav = speaker_wav(5, seconds, 44100, 2)
+    for _ in range(2):
+        emb, out = enc(wav, 44100)
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = 5
+    e0.record()
+    for _ in range(n):
+        emb, out = enc(wav, 44100)
+        host = out.cpu()
+    e1.record()
+    torch.cuda.synchronize(device)
+    ms = e0.elapsed_time(e1) / n
+    t0 = time.perf_counter()
+    emb_ref, _ = osp.speaker_embedding(wav, 44100, sd, lda)
+    cpu_ms = (time.perf_counter() - t0) * 1e3
+    del enc
+    return {"workload": f"SpeakerEmbeddingLDA.forward, ResNet293 architecture (seeded weights), one {seconds:.0f} s stereo clip at 44.1 kHz",
+            "ms": round(ms, 2), "launches": 3 + 1 + 3 * 97 + 3 + 6, "dtype": "f32",
+            "cpu_oracle_ms": round(cpu_ms, 1), "cpu_threads": torch.get_num_threads(),
+            "rel_max_error_vs_cpu_oracle": float((emb.cpu() - emb_ref).abs().max() / emb_ref.abs().max())}
+
+
 def postproc_section(device, hbm_peak, batch, frames, cpu_utts=2, chunk=None):
     """codes_to_wavs' post-processing (loudness normalisation, trim, fades) over a batch of decoded
     waveforms already in HBM, against the reference's per-utterance CPU loop (oracle/postproc.py, bounded sample).
@@ -906,6 +938,12 @@ def main_b200(args, world, rank, local):
         line["hybrid_mamba2"] = {"generate_c5_like": hybrid_generate_section(device, world)}
     if extras and world == 1 and not args.no_dac:
         line["postprocess"] = postproc_section(device, hbm_peak, B, args.max_new_tokens)
+        torch.cuda.empty_cache()
+    if extras and world == 1:
+        try:
+            line["speaker_encoder"] = speaker_section(device)
+        except Exception as e:
+            line["speaker_encoder"] = {"error": f"{type(e).__name__}: {e}"}
         torch.cuda.empty_cache()
     if extras:
         # LAST, on a fresh model: the CUPTI pass behind `roofline.groups`.  Once torch.profiler has attached CUPTI, every

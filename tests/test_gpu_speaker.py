@@ -59,3 +59,20 @@ def test_speaker_encoder_batch_vs_oracle():
     emb2 = net(wav.cuda())
     assert float((emb2.cpu() - emb_ref).abs().max()) < 1e-2 * scale
     assert float((emb_ref[0] - emb_ref[1]).abs().max()) > 1e-2 * scale  # the two signals do not collapse
+
+
+def test_make_speaker_embedding_on_the_model(golden):
+    """Zonos.make_speaker_embedding (zonos/model.py:90-95): bf16 [1, 1, 128] = the LDA output of the clip."""
+    from oracle import shapes
+    from zonos_b200.config import ZonosConfig
+    from zonos_b200.model import Zonos
+    from zonos_b200.speaker_cloning import SpeakerEmbeddingLDA
+
+    ip, blocks, seed, seconds, sr, ch = SPEAKER_CASES["tiny_44k_stereo"]
+    c = golden("speaker.pt")["tiny_44k_stereo"]
+    sd, lda = osp.synth_speaker_weights(ip, blocks, seed)
+    m = Zonos.from_state_dict(ZonosConfig.from_dict(shapes.reference_config_dict("tiny")), shapes.synth_transformer_weights("tiny"), "cuda")
+    m.spk_clone_model = SpeakerEmbeddingLDA("cuda", state_dict=sd, lda_state_dict=lda)
+    e = m.make_speaker_embedding(speaker_wav(seed, seconds, sr, ch), sr)
+    assert e.shape == (1, 1, 128) and e.dtype == torch.bfloat16
+    assert float((e.float().cpu()[0] - c["lda"]).abs().max()) < 2e-2 * float(c["lda"].abs().max())  # bf16 rounding of the output

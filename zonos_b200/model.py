@@ -127,6 +127,17 @@ class Zonos(nn.Module):
         return self._packed
 
     # ------------------------------------------------------------------------------------------------ small API
+    def make_speaker_embedding(self, wav: torch.Tensor, sr: int) -> torch.Tensor:
+        """zonos/model.py:90-95: speaker embedding of an audio clip -> bf16 [1, 1, 128] (the `speaker` conditioner's input).
+        The encoder (zonos_b200.speaker_cloning over csrc/speaker.cu) is built on first use; assign `spk_clone_model` a
+        `SpeakerEmbeddingLDA(device, state_dict=..., lda_state_dict=...)` beforehand when the checkpoint is local."""
+        if self.spk_clone_model is None:
+            from .speaker_cloning import SpeakerEmbeddingLDA
+
+            self.spk_clone_model = SpeakerEmbeddingLDA(device=str(self.device))
+        _, spk_embedding = self.spk_clone_model(wav.to(self.spk_clone_model.device), sr)
+        return spk_embedding.unsqueeze(0).bfloat16()
+
     def embed_codes(self, codes: torch.Tensor) -> torch.Tensor:
         """zonos/model.py:97-98.  codes int [B, 9, S] -> bf16 [B, S, d]."""
         return ops.embed_codes(codes, self.packed().emb)
