@@ -55,7 +55,8 @@ enum { MODE_K2 = 0, MODE_T2 = 1, MODE_K1 = 2, MODE_N16 = 3, MODE_T2K2 = 4 };
 #define SK_SA128_T2K2 3  // activation ring depth at 128 rows with 32 KB stages (two k-blocks per unit)
 #endif
 #ifndef SK_T2K2_MIN_UNITS
-#define SK_T2K2_MIN_UNITS 1184  // 16 KB units of a GEMM (tile pairs x k-blocks) from which 32 KB units are used: 8 per SM
+#define SK_T2K2_MIN_UNITS 512  // 16 KB units of a GEMM (tile pairs x k-blocks) from which 32 KB units are used (measured: every
+                               // projection of the decode step gains, out_proj with 512 included; 3.02 -> 2.97 ms at batch 64)
 #endif
 #ifndef SK_A_SLOW_START
 #define SK_A_SLOW_START 1  // activation stages in flight before the first one has landed
@@ -154,7 +155,7 @@ struct SkinnyCfg {
   static constexpr int W_STAGE_BYTES = TG * KG * TILE_BYTES;
   // The activation gather is a round trip to L2 per stage (~1.2 us under load), so its rate is ring bytes / latency: at
   // 64 rows a stage holds 8 KB and the ring must be twice as deep as at 128 rows to feed the same weight rate.
-  static constexpr int SA = (MODE == MODE_T2K2) ? (A_ROWS >= 128 ? SK_SA128_T2K2 : SK_SA64 / 2)
+  static constexpr int SA = (MODE == MODE_T2K2) ? (A_ROWS >= 128 ? SK_SA128_T2K2 : BIG ? SK_SA64 / 2 : 4)
                             : (A_ROWS >= 128) ? SK_SA128 : BIG ? SK_SA64 : (A_ROWS <= 8 && MODE != MODE_N16) ? 8 : 4;
   static constexpr int SW = BIG ? (SK_SW128_KB * 1024 / W_STAGE_BYTES)
                                             : ((A_ROWS > 8 || MODE == MODE_N16 ? 64 : 80) * 1024 / W_STAGE_BYTES);
@@ -268,7 +269,7 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
     // (scripts/exp_stream.cu: 22 GB/s with 8 KB copies, 44 GB/s with 16 KB), less than an SM's share of HBM.  SK_WLANES
     // lanes therefore issue in parallel, lane l owning units l, l + SK_WLANES, ...  A lane must never run two ring
     // revolutions ahead of the consumer (the parity wait cannot tell 0 from 2 completions): lanes <= slots guarantees it.
-    static_assert(SK_WLANES <= SW, "weight-producer lanes must not outnumber the ring slots");
+    static_assert(SK_WLANES / (TG == 2 ? 2 * KG : 1) <= SW, "units issued per round must not outnumber the ring slots");
     if (lane < SK_WLANES) {
       const uint64_t pol = l2_policy_evict_first();
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(g.Wp);
