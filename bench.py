@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 FRAME_RATE = 44100 / 512  # 86.1328 frames per audio second
 # attn_decode_kernel DRAM traffic per launch measured by ncu: key (sequences incl. CFG, kv heads, context)
-NCU_ATTN_TRAFFIC = {(128, 4, 1432, 1): (390_587_000, "profiles/r01f_ncu_full.txt"),
+NCU_ATTN_TRAFFIC = {(128, 4, 1432, 1): (390_396_160, "profiles/r02d_ncu_full_decode_b64.txt"),
                     (128, 4, 1432, 2): (390_500_000, "profiles/r01b_ncu_full_decode_b64.txt")}
 C3_SAMPLING = dict(top_p=0, top_k=0, min_p=0.1, linear=0, conf=0, quad=0, repetition_penalty=3.0,
                    repetition_penalty_window=2, temperature=1.0)
@@ -433,13 +433,12 @@ def dac_section(device, batch, frames, world=1):
 def speaker_section(device, seconds=10.0):
     """Speaker encoder, ResNet293 architecture with seeded weights: one clip, host signal -> embedding
     on the host through SpeakerEmbeddingLDA.forward, CUDA events; the CPU oracle on this box's cores beside it."""
-    from oracle import speaker as osp
-    from oracle.gen_golden import speaker_wav
+    from zonos_b200 import synth
     from zonos_b200.speaker_cloning import SpeakerEmbeddingLDA
 
-    sd, lda = osp.synth_speaker_weights(64, osp.RESNET293_BLOCKS, 13)
+    sd, lda = synth.speaker_state_dicts(device=device, seed=13)
     enc = SpeakerEmbeddingLDA(str(device), state_dict=sd, lda_state_dict=lda)
-    wav = speaker_wav(5, seconds, 44100, 2)
+    wav = synth.speaker_clip(seconds, 44100, 2)
     for _ in range(2):
         emb, out = enc(wav, 44100)
     torch.cuda.synchronize(device)
@@ -452,8 +451,11 @@ def speaker_section(device, seconds=10.0):
     e1.record()
     torch.cuda.synchronize(device)
     ms = e0.elapsed_time(e1) / n
+    from oracle import speaker as osp  # the checker / CPU baseline of this section
+
+    sd_cpu, lda_cpu = {k: v.cpu() for k, v in sd.items()}, {k: v.cpu() for k, v in lda.items()}
     t0 = time.perf_counter()
-    emb_ref, _ = osp.speaker_embedding(wav, 44100, sd, lda)
+    emb_ref, _ = osp.speaker_embedding(wav, 44100, sd_cpu, lda_cpu)
     cpu_ms = (time.perf_counter() - t0) * 1e3
     del enc
     return {"workload": f"SpeakerEmbeddingLDA.forward, ResNet293 architecture (seeded weights), one {seconds:.0f} s stereo clip at 44.1 kHz",

@@ -167,3 +167,62 @@ def mamba2_mixer_params(d_model: int = 2048, expand: int = 2, head_dim: int = 64
         "shape": dict(d_inner=Di, n_heads=H, head_dim=head_dim, d_state=d_state, n_groups=n_groups, eps=1e-5, d_model=d_model,
                       d_conv=d_conv),
     }
+
+
+RESNET293_BLOCKS = (10, 20, 64, 3)
+
+
+def speaker_state_dicts(in_planes: int = 64, num_blocks=RESNET293_BLOCKS, device="cuda", seed: int = 0, embd_dim: int = 256,
+                        lda_dim: int = 128):
+    """Random-init state dicts of the speaker encoder (`ResNet293_based` + the LDA Linear, zonos/speaker_cloning.py:198-223,
+    404-405) under the reference's key names, drawn on the device: He-scaled convolutions, perturbed BatchNorm affine /
+    running statistics, a small second BatchNorm weight per block so the residual stream stays O(1) over 97 blocks."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    sd = {}
+    rn = lambda *sh: torch.randn(*sh, generator=g, device=device)
+
+    def bn(name, c, w_mean=1.0):
+        sd[name + ".weight"] = w_mean * (1 + 0.1 * rn(c))
+        sd[name + ".bias"] = 0.1 * rn(c)
+        sd[name + ".running_mean"] = 0.1 * rn(c)
+        sd[name + ".running_var"] = 1 + 0.2 * torch.rand(c, generator=g, device=device)
+
+    sd["front.conv1.weight"] = rn(in_planes, 1, 3, 3) * math.sqrt(2.0 / 9)
+    bn("front.bn1", in_planes)
+    cin = in_planes
+    for li, (mult, n) in enumerate(zip((1, 2, 4, 8), num_blocks)):
+        planes = in_planes * mult
+        for bi in range(n):
+            stride = (1 if li == 0 else 2) if bi == 0 else 1
+            p = f"front.layer{li + 1}.{bi}"
+            sd[p + ".conv1.weight"] = rn(planes, cin, 3, 3) * math.sqrt(2.0 / (cin * 9))
+            bn(p + ".bn1", planes)
+            sd[p + ".conv2.weight"] = rn(planes, planes, 3, 3) * math.sqrt(2.0 / (planes * 9))
+            bn(p + ".bn2", planes, w_mean=0.3)
+            if stride != 1 or cin != planes:
+                sd[p + ".downsample.0.weight"] = rn(planes, cin, 1, 1) * math.sqrt(2.0 / cin)
+                bn(p + ".downsample.1", planes)
+            cin = planes
+    feat = in_planes * 8 * 10
+    sd["pooling.attention.0.weight"] = rn(128, feat, 1) / math.sqrt(feat)
+    sd["pooling.attention.0.bias"] = 0.1 * rn(128)
+    bn("pooling.attention.2", 128)
+    sd["pooling.attention.3.weight"] = rn(feat, 128, 1) / math.sqrt(128)
+    sd["pooling.attention.3.bias"] = 0.1 * rn(feat)
+    sd["bottleneck.weight"] = rn(embd_dim, 2 * feat) / math.sqrt(2 * feat)
+    sd["bottleneck.bias"] = 0.1 * rn(embd_dim)
+    lda = {"weight": rn(lda_dim, embd_dim) / math.sqrt(embd_dim), "bias": 0.1 * rn(lda_dim)}
+    return sd, lda
+
+
+def speaker_clip(seconds: float = 10.0, sample_rate: int = 44100, channels: int = 2, seed: int = 5) -> torch.Tensor:
+    """A synthetic clip on the HOST (a few partials + noise), fp32 [channels, n] in [-1, 1]: what torchaudio.load returns."""
+    g = torch.Generator().manual_seed(seed)
+    n = int(seconds * sample_rate)
+    t = torch.arange(n, dtype=torch.float64) / sample_rate
+    wav = torch.zeros(channels, n, dtype=torch.float64)
+    for c in range(channels):
+        for f0 in (110.0 * (c + 1), 440.0, 1730.0, 5200.0):
+            wav[c] += float(torch.rand(1, generator=g)) * torch.sin(2 * torch.pi * f0 * t + float(torch.rand(1, generator=g)))
+        wav[c] += 0.1 * torch.randn(n, generator=g, dtype=torch.float64)
+    return (0.25 * wav).float()
