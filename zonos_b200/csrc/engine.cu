@@ -1,6 +1,7 @@
 // Session engine: sequences the kernels of the prefill and of one decode step, and owns the captured CUDA graph.
 // Reference control flow being replaced: zonos/model.py:103-116 (_compute_logits), :118-179 (_decode_one_token),
 // :181-202 (_prefill); zonos/backbone/_torch.py:73-80,99-102 (backbone / block forward).
+#include <cstdio>
 #include "../../include/zonos_b200.h"
 #include "attention.cuh"
 #include "chain.cuh"
@@ -134,12 +135,13 @@ NextW next_swap(const zb200_engine* e, const void* w, int rows, int n_tiles, int
 // Ticketed-epilogue GEMM: the weight-streaming kernel for the decode step (rows <= 128), the tiled kernel otherwise.
 template <class ALoader, class Epilogue>
 cudaError_t gemm_any(const zb200_engine* e, const void* w, int n_tiles, int rows, int k, const ALoader& al,
-                     const Epilogue& epi, cudaStream_t st, const NextW& nx = NextW{}) {
+                     const Epilogue& epi, cudaStream_t st, const NextW& nx = NextW{}, const KvPrefetch& kvpf = KvPrefetch{}) {
   const zb200_engine_desc& d = e->d;
   if (rows <= GEMM_BM && e->sk_sms > 0) {
     const SkPlan p = plan_ticketed(e->sk_sms, rows, n_tiles, k / 64);
     SkinnyCore g = sk_core(d, w, n_tiles, rows, k);
     g.next = nx;
+    g.kvpf = kvpf;
     return launch_gemm_skinny(g, al, epi, p.grid, st, p.prefer_k1);
   }
   GemmCore g = make_core(d, w, n_tiles, rows, k);
@@ -236,6 +238,29 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
     const SkPlan p = plan_ticketed(e->sk_sms, rows, qkv_tiles, dm / 64);
     return next_skinny(w, rows, qkv_tiles, dm, p.grid, p.prefer_k1);
   };
+  // KV pages of the next attention kernel pulled into L2 from the tails of the GEMMs in front of it (gemm_skinny.cuh):
+  // pages per CTA for out_proj, fc1, fc2 (layer l + 1's pages) and in_proj (its own layer's).  Measured at batch 64
+  // (ms per frame): none 2.97, {1,0,1,0} 2.86, {0,1,1,1} 2.81 (54 MB of the layer's 376 MB), {2,0,2,1} 2.86, {3,0,3,2}
+  // 2.91 (141 MB: more than L2 keeps); batch 32: 2.05 -> 1.91.
+  static int kvpf_n[4] = {-1, 1, 1, 1};
+  if (kvpf_n[0] < 0) {
+    kvpf_n[0] = 0;
+    if (const char* v = zb::tuning_env("ZB200_KVPF")) sscanf(v, "%d,%d,%d,%d", &kvpf_n[0], &kvpf_n[1], &kvpf_n[2], &kvpf_n[3]);
+  }
+  const int kv_page_bytes = 2 * d.n_kv_heads * 64 * ZB200_HEAD_DIM * 2;
+  const int fc1_grid = plan_ticketed(e->sk_sms, rows, d.d_ff / (NT / 2), dm / 64).grid;
+  const int kvpf_grid[4] = {p_out.grid, fc1_grid, p_fc2.grid, p_qkv.grid};
+  auto kvpf = [&](int which, int layer, int grid) {
+    KvPrefetch k{};
+    if (kvpf_n[which] <= 0 || rows <= 32) return k;  // (<= 32 rows: two CTAs per SM already keep HBM busy; measured slower)
+    int first = 0;
+    for (int j = 0; j < which; ++j) first += kvpf_n[j] * kvpf_grid[j];
+    (void)grid;
+    k.layer_base = (const uint8_t*)d.kv_pool + (size_t)(layer % d.n_layer) * d.num_pages * kv_page_bytes;
+    k.block_table = d.block_table, k.pos_ptr = pos_ptr, k.pos_add = 0, k.pages_per_seq = d.pages_per_seq, k.n_seq = n_seq;
+    k.page_bytes = kv_page_bytes, k.first_item = first, k.items_per_cta = kvpf_n[which];
+    return k;
+  };
   ZB_TRY(launch_layernorm(x, (const bf16*)d.ln1_w, (const bf16*)d.ln1_b, xn, rows, dm, d.ln_eps, 1, 0, st));
   for (int l = 0; l < d.n_layer; ++l) {
     {  // in_proj + RoPE + KV page write
@@ -247,6 +272,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       } else if (qkv_deferred) {  // split-K partials, finished (sum + RoPE + q / KV write) by a row x column kernel
         SkinnyCore g = sk_core(d, (const uint8_t*)d.w_qkv + (size_t)l * d.qkv_stride, (hd + 2 * kvd) / NT, rows, dm);
         g.n_splits = p_qkv.splits;
+        g.kvpf = kvpf(3, l, p_qkv.grid);
         EpiPartial epi{d.gemm_ws, rows, hd + 2 * kvd};
         ZB_TRY(launch_gemm_skinny(g, al, epi, p_qkv.grid, st));
         ZB_TRY(launch_qkv_finish(d.gemm_ws, p_qkv.splits, rows, hd + 2 * kvd, q, kv_of(d, l), d.rope, pos_ptr, d.n_heads, st));
@@ -267,6 +293,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_out + (size_t)l * d.out_stride, dm / NT, rows, hd);
       g.n_splits = p_out.splits;
       g.next = nx_fc1(l);
+      g.kvpf = kvpf(0, l + 1, p_out.grid);
       ARowMajor al{(const uint8_t*)att, (size_t)hd * 2};
       EpiPartial epi{d.gemm_ws, rows, dm};
       ZB_TRY(launch_gemm_skinny(g, al, epi, p_out.grid, st));
@@ -281,7 +308,8 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
         ZB_TRY(gemm_swap(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st, nx_fc2(l)));
       } else {
         EpiSwiGLU<NT> epi{h, d.d_ff};
-        ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st, nx_fc2(l)));
+        ZB_TRY(gemm_any(e, (const uint8_t*)d.w_fc1 + (size_t)l * d.fc1_stride, d.d_ff / (NT / 2), rows, dm, al, epi, st, nx_fc2(l),
+                        kvpf(1, l + 1, fc1_grid)));
       }
     }
     {  // fc2 (split-K partials) -> residual + the next layer's norm (norm_f after the last layer)
@@ -292,6 +320,7 @@ int run_decode_skinny(zb200_engine* e, cudaStream_t st) {
       SkinnyCore g = sk_core(d, (const uint8_t*)d.w_fc2 + (size_t)l * d.fc2_stride, dm / NT, rows, d.d_ff);
       g.n_splits = p_fc2.splits;
       g.next = nx_qkv(l + 1);
+      g.kvpf = kvpf(2, l + 1, p_fc2.grid);
       ARowMajor al{(const uint8_t*)h, (size_t)d.d_ff * 2};
       EpiPartial epi{d.gemm_ws, rows, dm};
       ZB_TRY(launch_gemm_skinny(g, al, epi, p_fc2.grid, st));

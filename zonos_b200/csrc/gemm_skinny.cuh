@@ -125,6 +125,29 @@ __device__ __forceinline__ void prefetch_next_weights(const NextW& nx, int cta) 
   }
 }
 
+// KV pages of the NEXT attention kernel, pulled into L2 by the weight-producer lane once its last weight copy is out: the
+// CTA's HBM queue would otherwise run dry through the MMAs' tail, the epilogue and the next kernel's ramp, and the decode
+// attention is bound by exactly that HBM stream.  Item i = (sequence i / pages, page i % pages) of the layer's pages in use;
+// CTA c takes items first_item + c * items_per_cta ...  A page is contiguous ([K|V][kv head][64][128] bf16).
+struct KvPrefetch {
+  const uint8_t* layer_base;  // pool + layer * num_pages * page_bytes; nullptr: nothing to prefetch
+  const int* block_table;     // [n_seq][pages_per_seq]
+  const int* pos_ptr;         // device-side position of the frame
+  int pos_add, pages_per_seq, n_seq, page_bytes, first_item, items_per_cta;
+};
+__device__ __forceinline__ void prefetch_kv(const KvPrefetch& k, int cta) {
+  if (k.layer_base == nullptr || k.items_per_cta <= 0) return;
+  const int n_pages = min(k.pages_per_seq, (*k.pos_ptr + k.pos_add) / 64 + 1);
+  const int total = k.n_seq * n_pages;
+  for (int j = 0; j < k.items_per_cta; ++j) {
+    const int item = k.first_item + cta * k.items_per_cta + j;
+    if (item >= total) return;
+    const int seq = item / n_pages, pg = item - seq * n_pages;
+    const uint8_t* p = k.layer_base + (size_t)k.block_table[seq * k.pages_per_seq + pg] * k.page_bytes;
+    for (int off = 0; off < k.page_bytes; off += 32768) bulk_prefetch_l2(p + off, (uint32_t)min(32768, k.page_bytes - off));
+  }
+}
+
 struct SkinnyCore {
   const void* Wp;     // packed weights [n_tiles][k_blocks][8 KB]
   int n_tiles, k_blocks;
@@ -135,6 +158,7 @@ struct SkinnyCore {
   unsigned long long* trace;  // debug timeline [64][160][12] (trace builds), else nullptr
   int trace_id;               // launch slot of the debug timeline
   NextW next;                 // weights of the GEMM that follows in the step
+  KvPrefetch kvpf;            // KV pages of the attention kernel that follows in the step
 };
 
 template <int A_ROWS, int MODE>
@@ -309,6 +333,7 @@ __global__ void __launch_bounds__(SkinnyCfg<A_ROWS, MODE>::THREADS, SkinnyCfg<A_
       if (lane == 0) {
         SK_STAMP(10);
         prefetch_next_weights(g.next, cta);
+        prefetch_kv(g.kvpf, cta);
       }
     }
   } else if (warp == MMA_WARP) {
