@@ -803,6 +803,10 @@ def main_b200(args, world, rank, local):
     steps_per_gen = model.last_generate_stats["steps"]
 
     # ---- end to end through the public API with HOST buffers: pinned conditioning in, codes out
+    if world > 1:  # warm-up of the result collective (NCCL sets its point-to-point channels up on first use: ~1.5 s at 8 ranks)
+        from zonos_b200.parallel import gather_codes
+
+        gather_codes([torch.zeros(9, 2, dtype=torch.int64, device=device) for _ in range(B)], B * world, dst=0)
     barrier(world)
     torch.cuda.synchronize()
     h2d = cond_host.numel() * cond_host.element_size() + (0 if prefix_host is None else prefix_host.numel() * 8)
