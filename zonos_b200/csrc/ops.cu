@@ -93,8 +93,7 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
 #ifdef SK_TRACE
   if (threadIdx.x == 0) sk_stamp(trace, trace_id, 0);
 #endif
-  __shared__ float red[RLN_THREADS / 32];
-  __shared__ float bcast;
+  __shared__ float red[RLN_THREADS / 32], red2[RLN_THREADS / 32];
   const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int MAXV = 2;  // d <= 4096
   // the LayerNorm parameters do not depend on the previous kernel: fetch them before the dependency resolves
@@ -146,21 +145,17 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
 #ifdef SK_TRACE
   if (threadIdx.x == 0) sk_stamp(trace, trace_id, 5);
 #endif
-  auto block_sum = [&](float t) {
+  // one barrier per reduction: each of the two uses its own slots, and every thread adds the warp sums in the same order
+  auto block_sum = [&](float t, float* slots) {
     t = warp_sum(t);
+    if (lane == 0) slots[warp] = t;
     __syncthreads();
-    if (lane == 0) red[warp] = t;
-    __syncthreads();
-    if (tid == 0) {
-      float a = 0.f;
+    float a = 0.f;
 #pragma unroll
-      for (int k = 0; k < RLN_THREADS / 32; ++k) a += red[k];
-      bcast = a;
-    }
-    __syncthreads();
-    return bcast;
+    for (int k = 0; k < RLN_THREADS / 32; ++k) a += slots[k];
+    return a;
   };
-  const float mean = block_sum(sum) / (float)d;
+  const float mean = block_sum(sum, red) / (float)d;
   float sq = 0.f;
 #pragma unroll
   for (int i = 0; i < MAXV; ++i)
@@ -170,7 +165,7 @@ __global__ void __launch_bounds__(RLN_THREADS) resid_ln_kernel(bf16* __restrict_
         const float t = v[i][j] - mean;
         sq += t * t;
       }
-  const float rstd = 1.0f / sqrtf(block_sum(sq) / (float)d + eps);
+  const float rstd = 1.0f / sqrtf(block_sum(sq, red2) / (float)d + eps);
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
     const int col = (i * RLN_THREADS + tid) * 8;
